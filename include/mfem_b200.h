@@ -1,0 +1,148 @@
+/* mfem_b200.h — C ABI of the B200-native mixed-stretch hot path (drop-in for mixed-fem's MixedStretch<DIM>).
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to evouga/mixed-fem).
+ * Conventions: return 0 on success, a negative mfb_error otherwise (never exit()); the caller owns every input
+ * buffer; the context owns all device memory; one context is used from one host thread; calls are ordered on the
+ * context's CUDA stream and are synchronous at the ABI unless the name ends in _dev (device pointers, asynchronous
+ * on the stream).  All reals are FP64, all indices int32 (Eigen's default StorageIndex).
+ *
+ * Host-side layouts are the reference's: x[d*v+l]; per-element vectors N*e+k (N = 6 in 3D, 3 in 2D);
+ * R, dSdF, H, Hinv column-major per element (src/variables/mixed_stretch.h:150-159).
+ */
+#ifndef MFEM_B200_H
+#define MFEM_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mfb_ctx mfb_ctx;
+
+enum mfb_error {
+  MFB_OK = 0,
+  MFB_ERR_INVALID = -1,      /* bad argument */
+  MFB_ERR_CUDA = -2,         /* CUDA runtime failure (mfb_last_error_string has the text) */
+  MFB_ERR_NO_DEVICE = -3,    /* no CUDA device: there is NO CPU fallback */
+  MFB_ERR_TOO_LARGE = -4,    /* nnz does not fit int32 */
+  MFB_ERR_UNSUPPORTED = -5,  /* e.g. Neohookean/Fung on a 2D mesh (the reference has no 3-vector form either) */
+  MFB_ERR_STATE = -6         /* call order (e.g. solve() before rhs()) */
+};
+
+/* src/factories/material_model_factory.cpp:11-47 names: "Stable-Neohookean","Neohookean","Corot","FixedCorot","ARAP","Fung" */
+enum mfb_model { MFB_SNH = 0, MFB_NH = 1, MFB_COROT = 2, MFB_FCR = 3, MFB_ARAP = 4, MFB_FUNG = 5 };
+enum mfb_elem { MFB_TET = 0, MFB_TRI2D = 1 };
+
+typedef struct {          /* src/config.h:143-151 MaterialConfig (the fields the path reads) */
+  int32_t model;
+  double mu, la;
+} mfb_material;
+
+typedef struct {          /* what MixedStretch pulls from Mesh: src/mesh/mesh.h:82-105,151-171 */
+  int32_t elem_kind;      /* MFB_TET (TetrahedralMesh) or MFB_TRI2D (Tri2DMesh) */
+  int32_t nV, nE;
+  const int32_t* T;       /* nE x (d+1) row-major vertex ids      (Mesh::T_) */
+  const double* Vref;     /* nV x d row-major reference positions (Mesh::Vref_) */
+  const int32_t* free_map;/* nV, -1 = pinned, else ascending free id (Mesh::free_map_, mesh.cpp:95-101) */
+  const int32_t* mat_id;  /* nE or NULL (all 0)                   (Mesh::elements_[i].material_) */
+  int32_t n_mat;
+  const mfb_material* materials;
+  int32_t device;         /* CUDA device ordinal */
+} mfb_mesh_desc;
+
+typedef struct {          /* SURVEY.md §5 failure detection: counts since the last update/reset */
+  int64_t polar_maxiter;  /* elements whose procrustes hit max_iter (newton_procrustes.h:158) */
+  int64_t polar_hfail;    /* elements with |H| < 1e-6, where the reference calls exit(1) (newton_procrustes.h:171-174) */
+  int64_t nonfinite;      /* elements that produced a non-finite value */
+  int64_t polar_iters;    /* total procrustes iterations */
+  int64_t eig_sweeps;     /* total Jacobi sweeps */
+} mfb_status;
+
+/* per-element / per-dof fields for mfb_get / mfb_set / mfb_field_dev (names = members of MixedStretch, mixed_stretch.h:141-162) */
+enum mfb_field {
+  MFB_F_S = 0,      /* s_      N*nE   (value())   settable */
+  MFB_F_DS,         /* ds_     N*nE   (delta())   settable */
+  MFB_F_LA,         /* la_     N*nE   (lambda())  settable */
+  MFB_F_R,          /* R_      d*d*nE col-major   settable */
+  MFB_F_SROT,       /* S_      N*nE */
+  MFB_F_G,          /* g_      N*nE */
+  MFB_F_H,          /* H_      N*N*nE */
+  MFB_F_HINV,       /* Hinv_   N*N*nE */
+  MFB_F_HLOC,       /* Hloc_   N*N*nE   (= vol^2 Sym H_ Sym) */
+  MFB_F_DSDF,       /* dSdF_   M*N*nE col-major M x N */
+  MFB_F_EVALS,      /* evals_  nE     (max_stresses()) */
+  MFB_F_GL,         /* gl_     N*nE */
+  MFB_F_GRAD,       /* grad_   N*nE   (gradient_mixed()) */
+  MFB_F_GRAD_LA,    /* grad_la_ N*nE  (gradient_dual()) */
+  MFB_F_GRAD_X,     /* grad_x_ d*nF   (gradient()) */
+  MFB_F_RHS,        /* rhs_    d*nF */
+  MFB_F_VOLS,       /* Mesh::volumes() nE */
+  MFB_F_ITERS,      /* procrustes iterations of the last update, as doubles, nE */
+  MFB_F_COUNT
+};
+
+/* ---- lifetime -------------------------------------------------------------------------------------------------
+ * mfb_create: MixedStretch(mesh) ctor + the Mesh::init() products the variable reads (mesh.cpp:44-83: volumes,
+ * dphi/dX of tet_mesh.cpp:43-75 / tri2d_mesh.cpp:44-77) + Assembler ctor (sparse_utils.cpp:19-117).  One-time
+ * host->device upload happens here. */
+int mfb_create(mfb_ctx** out, const mfb_mesh_desc* desc);
+void mfb_destroy(mfb_ctx* ctx);
+int mfb_set_stream(mfb_ctx* ctx, void* cuda_stream);          /* default: stream 0 */
+const char* mfb_last_error_string(void);
+const char* mfb_version(void);
+
+/* ---- sizes ---- */
+int mfb_dims(const mfb_ctx* ctx, int32_t* dim, int32_t* nV, int32_t* nE, int32_t* nF, int32_t* N, int64_t* nnz);
+
+/* ---- Assembler products: Assembler::A pattern (sparse_utils.cpp:101-116) and the element->nonzero map implied by
+ * update_matrix (sparse_utils.cpp:140-163).  Host pointers owned by ctx, valid until destroy.
+ * map[e*(d+1)^2 + j*(d+1) + k] = value index of entry (0,0) of block (j,k) (-1 if either vertex is pinned);
+ * entry (r,c) of that block lives at map + r*stride[e*(d+1)+j] + c. */
+int mfb_csr_pattern(mfb_ctx* ctx, const int32_t** outer, const int32_t** inner, int64_t* nnz, int32_t* nrows);
+int mfb_scatter_map(mfb_ctx* ctx, const int32_t** map, const int32_t** stride);
+
+/* ---- MixedVariable<DIM> virtuals (src/variables/mixed_variable.h:11-69, mixed_stretch.h:25-83) ---- */
+int mfb_reset(mfb_ctx* ctx, const double* x_or_null);          /* reset()  mixed_stretch.cpp:294-338 (NULL: x = vec(Vref)) */
+int mfb_update(mfb_ctx* ctx, const double* x, double dt);      /* update() mixed_stretch.cpp:158-164 ; x is host, d*nV */
+int mfb_update_dev(mfb_ctx* ctx, const double* x_dev, double dt);
+int mfb_rhs(mfb_ctx* ctx, double* out);                        /* rhs()    mixed_stretch.cpp:245-275 ; out host d*nF */
+int mfb_rhs_dev(mfb_ctx* ctx, const double** out_dev);
+int mfb_solve(mfb_ctx* ctx, const double* dx);                 /* solve()  mixed_stretch.cpp:277-292 ; dx host d*nF */
+int mfb_solve_dev(mfb_ctx* ctx, const double* dx_dev);
+int mfb_post_solve(mfb_ctx* ctx);                              /* post_solve() mixed_stretch.cpp:340-343 : la_ = 0 */
+int mfb_energy(mfb_ctx* ctx, const double* x, const double* s, double* e);            /* mixed_stretch.cpp:93-107 */
+int mfb_constraint_value(mfb_ctx* ctx, const double* x, const double* s, double* e);  /* mixed_stretch.cpp:109-136 */
+int mfb_energy_dev(mfb_ctx* ctx, const double* s_dev_soa_or_null, double* e);
+int mfb_constraint_value_dev(mfb_ctx* ctx, const double* x_dev, const double* s_dev_soa_or_null, double* e);
+int mfb_evaluate_constraint(mfb_ctx* ctx, const double* x, double* c);                /* mixed_stretch.cpp:345-366 */
+int mfb_lhs_values(mfb_ctx* ctx, double* values);              /* lhs().valuePtr() mixed_stretch.h:37-39 ; host, nnz */
+int mfb_lhs_values_dev(mfb_ctx* ctx, const double** values_dev);
+
+/* matrix-free operators, out += ... / out -= ... exactly as mixed_stretch.cpp:406-468.  which: 0 product_hessian,
+ * 1 product_hessian_inv, 2 product_jacobian_mixed, 3 product_jacobian_x (transposed selects the branch). host buffers. */
+int mfb_product(mfb_ctx* ctx, int which, const double* x, double* out, int transposed);
+
+/* ---- state access ---- */
+int64_t mfb_field_size(const mfb_ctx* ctx, int field);
+int mfb_get(mfb_ctx* ctx, int field, double* out);             /* host copy in the reference layout */
+int mfb_set(mfb_ctx* ctx, int field, const double* in);        /* S, DS, LA, R only */
+/* device pointer of the structure-of-arrays storage: component c of element e at ptr[c*ld + e] */
+int mfb_field_dev(mfb_ctx* ctx, int field, double** ptr, int64_t* ld, int32_t* ncomp);
+int mfb_last_status(mfb_ctx* ctx, mfb_status* st);
+
+/* ---- linear-solver side (src/linear_solvers/linear_system.h:9-62 SystemMatrixPD, eigen_iterative_solver.h:27-65,
+ * pcg.h:11-80).  All pointers are DEVICE pointers; the matrix is  M_vals (same CSR pattern, may be NULL) + A. ---- */
+int mfb_spmv_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* x_dev, double* y_dev);
+/* precond: 0 none, 1 diagonal (Eigen DiagonalPreconditioner), 2 block-Jacobi d x d (preconditioners/block_jacobi.h:45-60).
+ * Solves (M + A) x = b from the initial guess in x; stops when |r| <= tol*|b| (Eigen ConjugateGradient criterion). */
+int mfb_pcg_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* b_dev, double* x_dev, int precond,
+                double tol, int max_iters, int* iters_out, double* relres_out);
+
+/* ---- instrumentation ---- */
+int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
+int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "assembly" 0 atomic / 1 gather */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MFEM_B200_H */

@@ -1,0 +1,348 @@
+"""mixed-fem_b200 — B200-native (sm_100a, FP64) mixed-stretch hot path of evouga/mixed-fem.
+
+This package is a thin ctypes binding over the C-ABI shared library `libmfem_b200.so` (include/mfem_b200.h)
+plus `MixedStretch`, a host-side mirror of `mfem::MixedStretch<DIM>` (src/variables/mixed_stretch.h:12-164)
+with the reference's method names.  There is NO CPU fallback: if the library or a CUDA device is missing the
+calls raise.  The package directory name contains a hyphen; import it as `mixed_fem_b200` (repo-root shim).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from . import meshgen  # noqa: F401
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmfem_b200.so")
+
+MODELS = {"Stable-Neohookean": 0, "Neohookean": 1, "Corot": 2, "FixedCorot": 3, "ARAP": 4, "Fung": 5}
+FIELDS = {n: i for i, n in enumerate(
+    ["s", "ds", "la", "R", "S", "g", "H", "Hinv", "Hloc", "dSdF", "evals", "gl", "grad", "grad_la", "grad_x", "rhs",
+     "vols", "iters"])}
+
+EXPORTS = [
+    "mfb_create", "mfb_destroy", "mfb_set_stream", "mfb_last_error_string", "mfb_version", "mfb_dims",
+    "mfb_csr_pattern", "mfb_scatter_map", "mfb_reset", "mfb_update", "mfb_update_dev", "mfb_rhs", "mfb_rhs_dev",
+    "mfb_solve", "mfb_solve_dev", "mfb_post_solve", "mfb_energy", "mfb_constraint_value", "mfb_energy_dev",
+    "mfb_constraint_value_dev", "mfb_evaluate_constraint", "mfb_lhs_values", "mfb_lhs_values_dev", "mfb_product",
+    "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
+    "mfb_num_kernel_launches", "mfb_set_option",
+]
+
+
+class MfbError(RuntimeError):
+    pass
+
+
+class _Material(C.Structure):
+    _fields_ = [("model", C.c_int32), ("mu", C.c_double), ("la", C.c_double)]
+
+
+class _MeshDesc(C.Structure):
+    _fields_ = [("elem_kind", C.c_int32), ("nV", C.c_int32), ("nE", C.c_int32),
+                ("T", C.POINTER(C.c_int32)), ("Vref", C.POINTER(C.c_double)), ("free_map", C.POINTER(C.c_int32)),
+                ("mat_id", C.POINTER(C.c_int32)), ("n_mat", C.c_int32), ("materials", C.POINTER(_Material)),
+                ("device", C.c_int32)]
+
+
+class _Status(C.Structure):
+    _fields_ = [("polar_maxiter", C.c_int64), ("polar_hfail", C.c_int64), ("nonfinite", C.c_int64),
+                ("polar_iters", C.c_int64), ("eig_sweeps", C.c_int64)]
+
+
+def build(force=False, verbose=False):
+    """Compile csrc/*.cu into libmfem_b200.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    srcdir = os.path.join(_HERE, "csrc")
+    srcs = [os.path.join(srcdir, f) for f in os.listdir(srcdir) if f.endswith((".cu", ".cuh"))]
+    srcs.append(os.path.join(_HERE, "..", "include", "mfem_b200.h"))
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
+        return LIB_PATH
+    r = subprocess.run(["make", "-C", srcdir, "-j4"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise MfbError("nvcc build failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+    if verbose:
+        print(r.stdout[-2000:])
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    """Load the C-ABI library (fails loudly when it is missing: no CPU path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MfbError("libmfem_b200.so not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(LIB_PATH)
+    vp, dp, ip = C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32)
+    L.mfb_create.argtypes = [C.POINTER(vp), C.POINTER(_MeshDesc)]
+    L.mfb_destroy.argtypes = [vp]
+    L.mfb_destroy.restype = None
+    L.mfb_set_stream.argtypes = [vp, vp]
+    L.mfb_last_error_string.restype = C.c_char_p
+    L.mfb_version.restype = C.c_char_p
+    L.mfb_dims.argtypes = [vp, ip, ip, ip, ip, ip, C.POINTER(C.c_int64)]
+    L.mfb_csr_pattern.argtypes = [vp, C.POINTER(ip), C.POINTER(ip), C.POINTER(C.c_int64), ip]
+    L.mfb_scatter_map.argtypes = [vp, C.POINTER(ip), C.POINTER(ip)]
+    L.mfb_reset.argtypes = [vp, dp]
+    L.mfb_update.argtypes = [vp, dp, C.c_double]
+    L.mfb_update_dev.argtypes = [vp, vp, C.c_double]
+    L.mfb_rhs.argtypes = [vp, dp]
+    L.mfb_rhs_dev.argtypes = [vp, C.POINTER(vp)]
+    L.mfb_solve.argtypes = [vp, dp]
+    L.mfb_solve_dev.argtypes = [vp, vp]
+    L.mfb_post_solve.argtypes = [vp]
+    L.mfb_energy.argtypes = [vp, dp, dp, dp]
+    L.mfb_constraint_value.argtypes = [vp, dp, dp, dp]
+    L.mfb_energy_dev.argtypes = [vp, vp, dp]
+    L.mfb_constraint_value_dev.argtypes = [vp, vp, vp, dp]
+    L.mfb_evaluate_constraint.argtypes = [vp, dp, dp]
+    L.mfb_lhs_values.argtypes = [vp, dp]
+    L.mfb_lhs_values_dev.argtypes = [vp, C.POINTER(vp)]
+    L.mfb_product.argtypes = [vp, C.c_int, dp, dp, C.c_int]
+    L.mfb_field_size.argtypes = [vp, C.c_int]
+    L.mfb_field_size.restype = C.c_int64
+    L.mfb_get.argtypes = [vp, C.c_int, dp]
+    L.mfb_set.argtypes = [vp, C.c_int, dp]
+    L.mfb_field_dev.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(C.c_int64), ip]
+    L.mfb_last_status.argtypes = [vp, C.POINTER(_Status)]
+    L.mfb_spmv_dev.argtypes = [vp, vp, vp, vp]
+    L.mfb_pcg_dev.argtypes = [vp, vp, vp, vp, C.c_int, C.c_double, C.c_int, ip, dp]
+    L.mfb_num_kernel_launches.argtypes = [vp, C.POINTER(C.c_int64), C.c_int]
+    L.mfb_set_option.argtypes = [vp, C.c_char_p, C.c_int]
+    _lib = L
+    return L
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class MixedStretch:
+    """Host-side mirror of mfem::MixedStretch<DIM> over the C ABI (same method names and argument meaning).
+
+    materials: list of (model_name, mu, la); mat_id: per-element index or None.
+    """
+
+    name = "mixed-stretch"   # src/variables/mixed_stretch.h:21-23
+
+    def __init__(self, V, T, free_map, materials, mat_id=None, device=0):
+        self.L = lib()
+        V = _f64(V)
+        T = np.ascontiguousarray(T, dtype=np.int32)
+        fm = np.ascontiguousarray(free_map, dtype=np.int32)
+        self.dim = V.shape[1]
+        self.nV, self.nE = V.shape[0], T.shape[0]
+        self.N = 6 if self.dim == 3 else 3
+        self.M = self.dim * self.dim
+        mats = (_Material * len(materials))()
+        for i, (model, mu, la) in enumerate(materials):
+            mats[i].model = MODELS[model] if isinstance(model, str) else int(model)
+            mats[i].mu, mats[i].la = float(mu), float(la)
+        mid = None if mat_id is None else np.ascontiguousarray(mat_id, dtype=np.int32)
+        d = _MeshDesc()
+        d.elem_kind = 0 if self.dim == 3 else 1
+        d.nV, d.nE = self.nV, self.nE
+        d.T, d.Vref, d.free_map = _ip(T), _dp(V), _ip(fm)
+        d.mat_id = _ip(mid) if mid is not None else None
+        d.n_mat, d.materials, d.device = len(materials), mats, device
+        self.h = C.c_void_p()
+        self._check(self.L.mfb_create(C.byref(self.h), C.byref(d)))
+        nF, nnz = C.c_int32(), C.c_int64()
+        self.L.mfb_dims(self.h, None, None, None, C.byref(nF), None, C.byref(nnz))
+        self.nfree, self.nnz = nF.value, nnz.value
+
+    def _check(self, rc):
+        if rc != 0:
+            raise MfbError("mfem_b200 error %d: %s" % (rc, self.L.mfb_last_error_string().decode()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.mfb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- MixedVariable interface ----
+    def reset(self, x=None):
+        if x is None:
+            self._check(self.L.mfb_reset(self.h, None))
+        else:
+            x = _f64(x)
+            self._check(self.L.mfb_reset(self.h, _dp(x)))
+
+    def update(self, x, dt):
+        x = _f64(x)
+        self._check(self.L.mfb_update(self.h, _dp(x), float(dt)))
+
+    def update_dev(self, x_ptr, dt):
+        self._check(self.L.mfb_update_dev(self.h, C.c_void_p(x_ptr), float(dt)))
+
+    def rhs(self, out=None):
+        out = np.empty(self.dim * self.nfree) if out is None else out
+        self._check(self.L.mfb_rhs(self.h, _dp(out)))
+        return out
+
+    def rhs_dev(self):
+        p = C.c_void_p()
+        self._check(self.L.mfb_rhs_dev(self.h, C.byref(p)))
+        return p.value
+
+    def solve(self, dx):
+        dx = _f64(dx)
+        self._check(self.L.mfb_solve(self.h, _dp(dx)))
+
+    def solve_dev(self, dx_ptr):
+        self._check(self.L.mfb_solve_dev(self.h, C.c_void_p(dx_ptr)))
+
+    def post_solve(self):
+        self._check(self.L.mfb_post_solve(self.h))
+
+    def energy(self, x, s):
+        s = _f64(s)
+        e = C.c_double()
+        self._check(self.L.mfb_energy(self.h, None, _dp(s), C.byref(e)))
+        return e.value
+
+    def constraint_value(self, x, s):
+        x, s = _f64(x), _f64(s)
+        e = C.c_double()
+        self._check(self.L.mfb_constraint_value(self.h, _dp(x), _dp(s), C.byref(e)))
+        return e.value
+
+    def energy_dev(self, s_ptr=None):
+        e = C.c_double()
+        self._check(self.L.mfb_energy_dev(self.h, C.c_void_p(s_ptr) if s_ptr else None, C.byref(e)))
+        return e.value
+
+    def constraint_value_dev(self, x_ptr, s_ptr=None):
+        e = C.c_double()
+        self._check(self.L.mfb_constraint_value_dev(self.h, C.c_void_p(x_ptr), C.c_void_p(s_ptr) if s_ptr else None, C.byref(e)))
+        return e.value
+
+    def evaluate_constraint(self, x):
+        x = _f64(x)
+        out = np.empty(self.N * self.nE)
+        self._check(self.L.mfb_evaluate_constraint(self.h, _dp(x), _dp(out)))
+        return out
+
+    def gradient(self):
+        return self.get("grad_x")
+
+    def gradient_mixed(self):
+        return self.get("grad")
+
+    def gradient_dual(self):
+        return self.get("grad_la")
+
+    def value(self):
+        return self.get("s")
+
+    def delta(self):
+        return self.get("ds")
+
+    def lambda_(self):
+        return self.get("la")
+
+    def max_stresses(self):
+        return self.get("evals")
+
+    def size(self):
+        return self.N * self.nE
+
+    def size_dual(self):
+        return self.N * self.nE
+
+    def lhs(self):
+        """(outer, inner, values) of the RowMajor CSR matrix A_ (mixed_stretch.h:37-39)."""
+        outer, inner = self.csr_pattern()
+        vals = np.empty(self.nnz)
+        self._check(self.L.mfb_lhs_values(self.h, _dp(vals)))
+        return outer, inner, vals
+
+    def lhs_values_dev(self):
+        p = C.c_void_p()
+        self._check(self.L.mfb_lhs_values_dev(self.h, C.byref(p)))
+        return p.value
+
+    def product(self, which, x, out, transposed=False):
+        idx = {"hessian": 0, "hessian_inv": 1, "jacobian_mixed": 2, "jacobian_x": 3}[which]
+        x = _f64(x)
+        out = _f64(out).copy()
+        self._check(self.L.mfb_product(self.h, idx, _dp(x), _dp(out), int(transposed)))
+        return out
+
+    # ---- assembler products ----
+    def csr_pattern(self):
+        po, pi = C.POINTER(C.c_int32)(), C.POINTER(C.c_int32)()
+        nnz, nrows = C.c_int64(), C.c_int32()
+        self._check(self.L.mfb_csr_pattern(self.h, C.byref(po), C.byref(pi), C.byref(nnz), C.byref(nrows)))
+        outer = np.ctypeslib.as_array(po, shape=(nrows.value + 1,)).copy()
+        inner = np.ctypeslib.as_array(pi, shape=(max(nnz.value, 1),)).copy()[:nnz.value]
+        return outer, inner
+
+    def scatter_map(self):
+        pm, ps = C.POINTER(C.c_int32)(), C.POINTER(C.c_int32)()
+        self._check(self.L.mfb_scatter_map(self.h, C.byref(pm), C.byref(ps)))
+        npe = self.dim + 1
+        m = np.ctypeslib.as_array(pm, shape=(self.nE, npe, npe)).copy()
+        st = np.ctypeslib.as_array(ps, shape=(self.nE, npe)).copy()
+        return m, st
+
+    # ---- state ----
+    def get(self, name):
+        f = FIELDS[name]
+        n = self.L.mfb_field_size(self.h, f)
+        out = np.empty(n)
+        self._check(self.L.mfb_get(self.h, f, _dp(out)))
+        return out
+
+    def set(self, name, val):
+        val = _f64(val)
+        self._check(self.L.mfb_set(self.h, FIELDS[name], _dp(val)))
+
+    def field_dev(self, name):
+        p, ld, nc = C.c_void_p(), C.c_int64(), C.c_int32()
+        self._check(self.L.mfb_field_dev(self.h, FIELDS[name], C.byref(p), C.byref(ld), C.byref(nc)))
+        return p.value, ld.value, nc.value
+
+    def status(self):
+        st = _Status()
+        self._check(self.L.mfb_last_status(self.h, C.byref(st)))
+        return {k: getattr(st, k) for k, _ in _Status._fields_}
+
+    def set_stream(self, stream_ptr):
+        self._check(self.L.mfb_set_stream(self.h, C.c_void_p(stream_ptr)))
+
+    def set_option(self, name, value):
+        self._check(self.L.mfb_set_option(self.h, name.encode(), int(value)))
+
+    def launches(self, reset=False):
+        n = C.c_int64()
+        self._check(self.L.mfb_num_kernel_launches(self.h, C.byref(n), int(reset)))
+        return n.value
+
+    # ---- linear solver side (device pointers) ----
+    def spmv_dev(self, x_ptr, y_ptr, M_ptr=None):
+        self._check(self.L.mfb_spmv_dev(self.h, C.c_void_p(M_ptr) if M_ptr else None, C.c_void_p(x_ptr), C.c_void_p(y_ptr)))
+
+    def pcg_dev(self, b_ptr, x_ptr, M_ptr=None, precond=1, tol=1e-4, max_iters=500):
+        it, rr = C.c_int32(), C.c_double()
+        self._check(self.L.mfb_pcg_dev(self.h, C.c_void_p(M_ptr) if M_ptr else None, C.c_void_p(b_ptr), C.c_void_p(x_ptr),
+                                       precond, tol, max_iters, C.byref(it), C.byref(rr)))
+        return it.value, rr.value

@@ -1,0 +1,315 @@
+// C ABI entry points of the mixed-stretch path (see include/mfem_b200.h for the reference interface each replaces).
+#include "mfb_ctx.cuh"
+#include <cstring>
+
+using namespace mfb;
+
+#define CHECK_CTX(c) do { if (!(c)) { g_last_error = "null context"; return MFB_ERR_INVALID; } cudaSetDevice((c)->device); } while (0)
+#define LAUNCHED(c, n) ((c)->launches += (n))
+
+static inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
+
+extern "C" const char* mfb_last_error_string(void) { return g_last_error.c_str(); }
+extern "C" const char* mfb_version(void) { return "mfem_b200 0.1 (sm_100a, FP64)"; }
+
+extern "C" int mfb_set_stream(mfb_ctx* c, void* s) { CHECK_CTX(c); c->stream = (cudaStream_t)s; return MFB_OK; }
+
+extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
+  CHECK_CTX(c);
+  if (!name) return MFB_ERR_INVALID;
+  if (!strcmp(name, "fuse_rhs")) { c->fuse_rhs = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "assembly")) { c->assembly = value; return MFB_OK; }
+  g_last_error = "unknown option";
+  return MFB_ERR_INVALID;
+}
+
+extern "C" int mfb_dims(const mfb_ctx* c, int32_t* dim, int32_t* nV, int32_t* nE, int32_t* nF, int32_t* N, int64_t* nnz) {
+  if (!c) return MFB_ERR_INVALID;
+  if (dim) *dim = c->dim; if (nV) *nV = c->nV; if (nE) *nE = c->nE; if (nF) *nF = c->nF; if (N) *N = c->N; if (nnz) *nnz = c->nnz;
+  return MFB_OK;
+}
+
+extern "C" int mfb_num_kernel_launches(mfb_ctx* c, int64_t* n, int reset) {
+  if (!c || !n) return MFB_ERR_INVALID;
+  *n = c->launches;
+  if (reset) c->launches = 0;
+  return MFB_OK;
+}
+
+extern "C" int mfb_csr_pattern(mfb_ctx* c, const int32_t** outer, const int32_t** inner, int64_t* nnz, int32_t* nrows) {
+  CHECK_CTX(c);
+  if (c->h_outer.empty()) {
+    c->h_outer.resize((size_t)c->dim * c->nF + 1);
+    c->h_inner.resize((size_t)c->nnz);
+    MFB_CUDA(cudaMemcpy(c->h_outer.data(), c->outer.p, c->h_outer.size() * 4, cudaMemcpyDeviceToHost));
+    if (c->nnz) MFB_CUDA(cudaMemcpy(c->h_inner.data(), c->inner.p, c->h_inner.size() * 4, cudaMemcpyDeviceToHost));
+  }
+  if (outer) *outer = c->h_outer.data();
+  if (inner) *inner = c->h_inner.data();
+  if (nnz) *nnz = c->nnz;
+  if (nrows) *nrows = c->dim * c->nF;
+  return MFB_OK;
+}
+
+// host layout [e][j][k] / [e][j] from the device component-major arrays
+extern "C" int mfb_scatter_map(mfb_ctx* c, const int32_t** map, const int32_t** stride) {
+  CHECK_CTX(c);
+  if (c->h_smap.empty()) {
+    const int nn = c->npe * c->npe;
+    std::vector<int32_t> a((size_t)nn * c->ld), b((size_t)c->npe * c->ld);
+    MFB_CUDA(cudaMemcpy(a.data(), c->smap.p, a.size() * 4, cudaMemcpyDeviceToHost));
+    MFB_CUDA(cudaMemcpy(b.data(), c->sstride.p, b.size() * 4, cudaMemcpyDeviceToHost));
+    c->h_smap.resize((size_t)c->nE * nn);
+    c->h_sstride.resize((size_t)c->nE * c->npe);
+    for (int e = 0; e < c->nE; ++e) {
+      for (int q = 0; q < nn; ++q) c->h_smap[(size_t)e * nn + q] = a[(size_t)q * c->ld + e];
+      for (int j = 0; j < c->npe; ++j) c->h_sstride[(size_t)e * c->npe + j] = b[(size_t)j * c->ld + e];
+    }
+  }
+  if (map) *map = c->h_smap.data();
+  if (stride) *stride = c->h_sstride.data();
+  return MFB_OK;
+}
+
+static int upload_x(mfb_ctx* c, const double* x) {
+  MFB_CUDA(cudaMemcpyAsync(c->xdev.p, x, (size_t)c->dim * c->nV * 8, cudaMemcpyHostToDevice, c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_reset(mfb_ctx* c, const double* x_or_null) {
+  CHECK_CTX(c);
+  const double* xd = nullptr;
+  if (x_or_null) { int rc = upload_x(c, x_or_null); if (rc) return rc; xd = c->xdev.p; }
+  else xd = c->vref.p;   // x = vec(V_^T) (mixed_stretch.cpp:314-317); row-major Vref is the same interleaving
+  MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, c->stream));
+  if (c->dim == 3) k_reset<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), xd);
+  else k_reset<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), xd);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  MFB_CUDA(cudaMemsetAsync(c->grad_x.p, 0, ((size_t)c->dim * c->nF + 1) * 8, c->stream));
+  MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, ((size_t)c->dim * c->nF + 1) * 8, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  c->rhs_valid = false; c->updated = false;
+  return MFB_OK;
+}
+
+// update(): one fused kernel (plus the zero-fill of the accumulation targets)
+extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
+  CHECK_CTX(c);
+  if (!x_dev) return MFB_ERR_INVALID;
+  cudaStream_t st = c->stream;
+  const double h2 = dt * dt;
+  MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
+  MFB_CUDA(cudaMemsetAsync(c->grad_x.p, 0, (size_t)c->dim * c->nF * 8, st));
+  if (c->fuse_rhs) MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, (size_t)c->dim * c->nF * 8, st));
+  if (c->nnz) MFB_CUDA(cudaMemsetAsync(c->Avals.p, 0, (size_t)c->nnz * 8, st));
+  const DevMesh m = c->mesh();
+  const DevState s = c->state();
+  if (c->dim == 3) {
+    if (c->fuse_rhs) k_update_tet<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+    else k_update_tet<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+  } else {
+    if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+    else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+  }
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  c->rhs_valid = c->fuse_rhs != 0;
+  c->updated = true;
+  return MFB_OK;
+}
+
+extern "C" int mfb_update(mfb_ctx* c, const double* x, double dt) {
+  CHECK_CTX(c);
+  if (!x) return MFB_ERR_INVALID;
+  int rc = upload_x(c, x);
+  if (rc) return rc;
+  rc = mfb_update_dev(c, c->xdev.p, dt);
+  if (rc) return rc;
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+static int ensure_rhs(mfb_ctx* c) {
+  if (c->rhs_valid) return MFB_OK;
+  MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, (size_t)c->dim * c->nF * 8, c->stream));
+  if (c->dim == 3) k_rhs<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state());
+  else k_rhs<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state());
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  c->rhs_valid = true;
+  return MFB_OK;
+}
+
+extern "C" int mfb_rhs_dev(mfb_ctx* c, const double** out_dev) {
+  CHECK_CTX(c);
+  int rc = ensure_rhs(c);
+  if (rc) return rc;
+  if (out_dev) *out_dev = c->rhs.p;
+  return MFB_OK;
+}
+extern "C" int mfb_rhs(mfb_ctx* c, double* out) {
+  CHECK_CTX(c);
+  if (!out) return MFB_ERR_INVALID;
+  int rc = ensure_rhs(c);
+  if (rc) return rc;
+  MFB_CUDA(cudaMemcpyAsync(out, c->rhs.p, (size_t)c->dim * c->nF * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_solve_dev(mfb_ctx* c, const double* dx_dev) {
+  CHECK_CTX(c);
+  if (!dx_dev) return MFB_ERR_INVALID;
+  int rc = ensure_rhs(c);   // solve() reads gl_, which rhs() produces (mixed_stretch.cpp:281)
+  if (rc) return rc;
+  if (c->dim == 3) k_solve<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dx_dev);
+  else k_solve<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dx_dev);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
+extern "C" int mfb_solve(mfb_ctx* c, const double* dx) {
+  CHECK_CTX(c);
+  if (!dx) return MFB_ERR_INVALID;
+  MFB_CUDA(cudaMemcpyAsync(c->vecF.p, dx, (size_t)c->dim * c->nF * 8, cudaMemcpyHostToDevice, c->stream));
+  int rc = mfb_solve_dev(c, c->vecF.p);
+  if (rc) return rc;
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_post_solve(mfb_ctx* c) {
+  CHECK_CTX(c);
+  MFB_CUDA(cudaMemsetAsync(c->la.p, 0, (size_t)c->N * c->ld * 8, c->stream));
+  return MFB_OK;
+}
+
+static int finish_sum(mfb_ctx* c, double* e) {
+  k_sum_partials<<<1, 256, 0, c->stream>>>(c->partials.p, c->grid(), c->scal.p);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  *e = c->h_scal[0];
+  return MFB_OK;
+}
+static int aos_to_soa(mfb_ctx* c, const double* host_aos, mfb::DBuf<double>& soa, int ncomp) {
+  int rc = c->aos.n < (size_t)ncomp * c->nE ? c->aos.alloc((size_t)c->M * c->N * c->nE) : MFB_OK;
+  if (rc) return rc;
+  MFB_CUDA(cudaMemcpyAsync(c->aos.p, host_aos, (size_t)ncomp * c->nE * 8, cudaMemcpyHostToDevice, c->stream));
+  k_aos_to_soa<<<nblk((int64_t)ncomp * c->nE), 256, 0, c->stream>>>(c->aos.p, soa.p, ncomp, c->nE, c->ld);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
+
+extern "C" int mfb_energy_dev(mfb_ctx* c, const double* s_soa, double* e) {
+  CHECK_CTX(c);
+  if (!e) return MFB_ERR_INVALID;
+  const double* sp = s_soa ? s_soa : c->s.p;
+  if (c->dim == 3) k_energy<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
+  else k_energy<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  return finish_sum(c, e);
+}
+extern "C" int mfb_energy(mfb_ctx* c, const double* /*x*/, const double* s, double* e) {
+  CHECK_CTX(c);
+  if (!s || !e) return MFB_ERR_INVALID;
+  int rc = aos_to_soa(c, s, c->soa_tmp, c->N);
+  if (rc) return rc;
+  return mfb_energy_dev(c, c->soa_tmp.p, e);
+}
+extern "C" int mfb_constraint_value_dev(mfb_ctx* c, const double* x_dev, const double* s_soa, double* e) {
+  CHECK_CTX(c);
+  if (!x_dev || !e) return MFB_ERR_INVALID;
+  const double* sp = s_soa ? s_soa : c->s.p;
+  if (c->dim == 3) k_constraint<3, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
+  else k_constraint<2, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  return finish_sum(c, e);
+}
+extern "C" int mfb_constraint_value(mfb_ctx* c, const double* x, const double* s, double* e) {
+  CHECK_CTX(c);
+  if (!x || !s || !e) return MFB_ERR_INVALID;
+  int rc = upload_x(c, x);
+  if (rc) return rc;
+  rc = aos_to_soa(c, s, c->soa_tmp, c->N);
+  if (rc) return rc;
+  return mfb_constraint_value_dev(c, c->xdev.p, c->soa_tmp.p, e);
+}
+extern "C" int mfb_evaluate_constraint(mfb_ctx* c, const double* x, double* out) {
+  CHECK_CTX(c);
+  if (!x || !out) return MFB_ERR_INVALID;
+  int rc = upload_x(c, x);
+  if (rc) return rc;
+  if (c->dim == 3) k_constraint<3, true><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), c->xdev.p, c->s.p, nullptr, c->soa_tmp.p);
+  else k_constraint<2, true><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), c->xdev.p, c->s.p, nullptr, c->soa_tmp.p);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaGetLastError());
+  if (c->aos.n < (size_t)c->N * c->nE) { rc = c->aos.alloc((size_t)c->M * c->N * c->nE); if (rc) return rc; }
+  k_soa_to_aos<<<nblk((int64_t)c->N * c->nE), 256, 0, c->stream>>>(c->soa_tmp.p, c->aos.p, c->N, c->nE, c->ld);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaMemcpyAsync(out, c->aos.p, (size_t)c->N * c->nE * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_lhs_values_dev(mfb_ctx* c, const double** v) { CHECK_CTX(c); if (v) *v = c->Avals.p; return MFB_OK; }
+extern "C" int mfb_lhs_values(mfb_ctx* c, double* values) {
+  CHECK_CTX(c);
+  if (!values) return MFB_ERR_INVALID;
+  if (c->nnz) MFB_CUDA(cudaMemcpyAsync(values, c->Avals.p, (size_t)c->nnz * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_product(mfb_ctx* c, int which, const double* x, double* out, int transposed) {
+  CHECK_CTX(c);
+  if (!x || !out || which < 0 || which > 3) return MFB_ERR_INVALID;
+  const size_t nEl = (size_t)c->N * c->nE, nVx = (size_t)c->dim * c->nF;
+  const bool x_is_elem = (which != 3) || transposed;
+  const bool out_is_elem = (which != 3) || !transposed;
+  int rc;
+  const double* xin;
+  double* o;
+  if (x_is_elem) { rc = aos_to_soa(c, x, c->soa_tmp, c->N); if (rc) return rc; xin = c->soa_tmp.p; }
+  else { MFB_CUDA(cudaMemcpyAsync(c->vecF.p, x, nVx * 8, cudaMemcpyHostToDevice, c->stream)); xin = c->vecF.p; }
+  if (out_is_elem) {
+    // second staging buffer for out
+    mfb::DBuf<double> stage;
+    rc = stage.alloc(nEl); if (rc) return rc;
+    MFB_CUDA(cudaMemcpyAsync(stage.p, out, nEl * 8, cudaMemcpyHostToDevice, c->stream));
+    k_aos_to_soa<<<nblk((int64_t)nEl), 256, 0, c->stream>>>(stage.p, c->soa_tmp2.p, c->N, c->nE, c->ld);
+    o = c->soa_tmp2.p;
+    if (c->dim == 3) k_product<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, o);
+    else k_product<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, o);
+    k_soa_to_aos<<<nblk((int64_t)nEl), 256, 0, c->stream>>>(o, stage.p, c->N, c->nE, c->ld);
+    LAUNCHED(c, 3);
+    MFB_CUDA(cudaMemcpyAsync(out, stage.p, nEl * 8, cudaMemcpyDeviceToHost, c->stream));
+    MFB_CUDA(cudaStreamSynchronize(c->stream));
+  } else {
+    mfb::DBuf<double> stage;
+    rc = stage.alloc(nVx + 1); if (rc) return rc;
+    MFB_CUDA(cudaMemcpyAsync(stage.p, out, nVx * 8, cudaMemcpyHostToDevice, c->stream));
+    if (c->dim == 3) k_product<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, stage.p);
+    else k_product<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, stage.p);
+    LAUNCHED(c, 1);
+    MFB_CUDA(cudaMemcpyAsync(out, stage.p, nVx * 8, cudaMemcpyDeviceToHost, c->stream));
+    MFB_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
+
+extern "C" int mfb_last_status(mfb_ctx* c, mfb_status* st) {
+  CHECK_CTX(c);
+  if (!st) return MFB_ERR_INVALID;
+  unsigned long long h[5];
+  MFB_CUDA(cudaMemcpyAsync(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  st->polar_maxiter = (int64_t)h[0]; st->polar_hfail = (int64_t)h[1]; st->nonfinite = (int64_t)h[2];
+  st->polar_iters = (int64_t)h[3]; st->eig_sweeps = (int64_t)h[4];
+  return MFB_OK;
+}

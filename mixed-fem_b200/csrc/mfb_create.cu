@@ -1,0 +1,260 @@
+// mfb_create / mfb_destroy: mesh-derived constants (volumes, dphi/dX), the Assembler's CSR pattern and the
+// element->nonzero scatter map, all built once and kept on the device.
+//
+//   volumes ........ src/mesh/tet_mesh.cpp:31-34 (|igl::volume|), src/mesh/tri2d_mesh.cpp:32-34 (signed igl::doublearea)
+//   dphi/dX ........ deps/Bartels/src/linear_tet_dphi_dX.cpp:5-17, linear_tri2d_dphi_dX.cpp:5-17
+//   pattern + map .. src/utils/sparse_utils.cpp:19-117 (ctor) and :140-163 (value index of each block entry)
+// The reference sorts the (row,col) node pairs on the host; here the same sort runs on the GPU as a radix sort of
+// 64-bit keys row*nF+col (cub via thrust), which yields the identical pattern because the pattern only depends on the
+// SET of pairs and on ascending (row, col) order.
+#include "mfb_ctx.cuh"
+#include <thrust/device_ptr.h>
+#include <thrust/sort.h>
+#include <thrust/scan.h>
+#include <thrust/binary_search.h>
+#include <thrust/iterator/counting_iterator.h>
+#include <thrust/execution_policy.h>
+#include <cmath>
+#include <climits>
+
+namespace mfb {
+thread_local std::string g_last_error;
+
+static const long long KEY_INVALID = LLONG_MAX;
+
+__global__ void k_pair_keys(const int* __restrict__ fidx, int npe, int nE, int64_t ld, long long nF, long long* keys, int* vals) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int nn = npe * npe;
+  if (p >= (int64_t)nE * nn) return;
+  const int e = (int)(p / nn), jk = (int)(p % nn), j = jk / npe, k = jk % npe;
+  const int gi = fidx[j * ld + e], gj = fidx[k * ld + e];
+  keys[p] = (gi < 0 || gj < 0) ? KEY_INVALID : (long long)gi * nF + gj;
+  vals[p] = (int)p;
+}
+__global__ void k_heads(const long long* __restrict__ keys, int64_t n, int* head) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  head[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1 : 0;
+}
+__global__ void k_block_info(const long long* __restrict__ keys, const int* __restrict__ head, const int* __restrict__ bid,
+                             int64_t n, long long nF, int* brow, int* bcol, int* diagblk) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !head[i]) return;
+  const int b = bid[i] - 1;
+  const int gi = (int)(keys[i] / nF), gj = (int)(keys[i] % nF);
+  brow[b] = gi; bcol[b] = gj;
+  if (gi == gj) diagblk[gi] = b;
+}
+__global__ void k_fill_maps(const int* __restrict__ vals, const int* __restrict__ bid, const int* __restrict__ brow,
+                            const int* __restrict__ blockptr, int64_t n, int npe, int dim, int64_t ld, int* smap, int* sstride) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = bid[i] - 1;
+  const int gi = brow[b];
+  const int rank = b - blockptr[gi], nbr = blockptr[gi + 1] - blockptr[gi];
+  const int p = vals[i];
+  const int nn = npe * npe;
+  const int e = p / nn, jk = p % nn, j = jk / npe;
+  smap[(int64_t)jk * ld + e] = dim * dim * blockptr[gi] + dim * rank;
+  sstride[(int64_t)j * ld + e] = dim * nbr;
+}
+__global__ void k_outer(const int* __restrict__ blockptr, int nF, int dim, int* outer) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > dim * nF) return;
+  if (i == dim * nF) { outer[i] = dim * dim * blockptr[nF]; return; }
+  const int gi = i / dim, r = i % dim;
+  const int nbr = blockptr[gi + 1] - blockptr[gi];
+  outer[i] = dim * dim * blockptr[gi] + r * dim * nbr;
+}
+__global__ void k_inner(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol, int nb, int dim, int* inner) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int dd = dim * dim;
+  if (i >= (int64_t)nb * dd) return;
+  const int b = (int)(i / dd), rc = (int)(i % dd), r = rc / dim, c = rc % dim;
+  const int gi = brow[b];
+  const int rank = b - blockptr[gi], nbr = blockptr[gi + 1] - blockptr[gi];
+  inner[(int64_t)dd * blockptr[gi] + (int64_t)r * dim * nbr + dim * rank + c] = dim * bcol[b] + c;
+}
+__global__ void k_fill_int(int* p, int64_t n, int v) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+static inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
+
+static int build_pattern(mfb_ctx* c) {
+  const int npe = c->npe, dim = c->dim, nE = c->nE, nF = c->nF;
+  const int64_t np = (int64_t)nE * npe * npe;
+  cudaStream_t st = c->stream;
+  DBuf<long long> keys; DBuf<int> vals, head, bid, brow;
+  int rc;
+  if ((rc = keys.alloc(np)) || (rc = vals.alloc(np)) || (rc = head.alloc(np)) || (rc = bid.alloc(np))) return rc;
+  k_pair_keys<<<nblk(np), 256, 0, st>>>(c->fidx.p, npe, nE, c->ld, nF, keys.p, vals.p);
+  auto pol = thrust::cuda::par.on(st);
+  thrust::sort_by_key(pol, thrust::device_ptr<long long>(keys.p), thrust::device_ptr<long long>(keys.p + np), thrust::device_ptr<int>(vals.p));
+  const int64_t nvalid = thrust::lower_bound(pol, thrust::device_ptr<long long>(keys.p), thrust::device_ptr<long long>(keys.p + np), KEY_INVALID) -
+                         thrust::device_ptr<long long>(keys.p);
+  int nb = 0;
+  if (nvalid > 0) {
+    k_heads<<<nblk(nvalid), 256, 0, st>>>(keys.p, nvalid, head.p);
+    thrust::inclusive_scan(pol, thrust::device_ptr<int>(head.p), thrust::device_ptr<int>(head.p + nvalid), thrust::device_ptr<int>(bid.p));
+    MFB_CUDA(cudaMemcpyAsync(&nb, bid.p + (nvalid - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+    MFB_CUDA(cudaStreamSynchronize(st));
+  }
+  const int64_t nnz = (int64_t)nb * dim * dim;
+  if (nnz > (int64_t)INT_MAX) { g_last_error = "nnz exceeds int32"; return MFB_ERR_TOO_LARGE; }
+  c->nb = nb; c->nnz = nnz;
+  if ((rc = brow.alloc(nb > 0 ? nb : 1)) || (rc = c->bcol.alloc(nb > 0 ? nb : 1)) || (rc = c->diagblk.alloc(nF > 0 ? nF : 1)) ||
+      (rc = c->blockptr.alloc((size_t)nF + 1)) || (rc = c->outer.alloc((size_t)dim * nF + 1)) || (rc = c->inner.alloc(nnz > 0 ? nnz : 1)) ||
+      (rc = c->smap.alloc((size_t)npe * npe * c->ld)) || (rc = c->sstride.alloc((size_t)npe * c->ld)))
+    return rc;
+  k_fill_int<<<nblk((int64_t)npe * npe * c->ld), 256, 0, st>>>(c->smap.p, (int64_t)npe * npe * c->ld, -1);
+  k_fill_int<<<nblk((int64_t)npe * c->ld), 256, 0, st>>>(c->sstride.p, (int64_t)npe * c->ld, 0);
+  k_fill_int<<<nblk(nF > 0 ? nF : 1), 256, 0, st>>>(c->diagblk.p, nF > 0 ? nF : 1, -1);
+  if (nvalid > 0) {
+    k_block_info<<<nblk(nvalid), 256, 0, st>>>(keys.p, head.p, bid.p, nvalid, nF, brow.p, c->bcol.p, c->diagblk.p);
+    // blockptr[gi] = first block whose row >= gi
+    thrust::lower_bound(pol, thrust::device_ptr<int>(brow.p), thrust::device_ptr<int>(brow.p + nb), thrust::counting_iterator<int>(0),
+                        thrust::counting_iterator<int>(nF + 1), thrust::device_ptr<int>(c->blockptr.p));
+    k_fill_maps<<<nblk(nvalid), 256, 0, st>>>(vals.p, bid.p, brow.p, c->blockptr.p, nvalid, npe, dim, c->ld, c->smap.p, c->sstride.p);
+    k_inner<<<nblk((int64_t)nb * dim * dim), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, nb, dim, c->inner.p);
+  } else {
+    MFB_CUDA(cudaMemsetAsync(c->blockptr.p, 0, ((size_t)nF + 1) * sizeof(int), st));
+  }
+  k_outer<<<nblk((int64_t)dim * nF + 1), 256, 0, st>>>(c->blockptr.p, nF, dim, c->outer.p);
+  MFB_CUDA(cudaStreamSynchronize(st));
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
+
+template <typename T>
+static int upload(DBuf<T>& d, const std::vector<T>& h, cudaStream_t st) {
+  int rc = d.alloc(h.size());
+  if (rc) return rc;
+  MFB_CUDA(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+  return MFB_OK;
+}
+
+}  // namespace mfb
+
+using namespace mfb;
+
+extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
+  if (!out || !d || !d->T || !d->Vref || !d->free_map || d->nV <= 0 || d->nE <= 0 || d->n_mat <= 0 || !d->materials) {
+    g_last_error = "mfb_create: invalid descriptor";
+    return MFB_ERR_INVALID;
+  }
+  if (d->elem_kind != MFB_TET && d->elem_kind != MFB_TRI2D) { g_last_error = "unsupported elem_kind"; return MFB_ERR_UNSUPPORTED; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    g_last_error = "no CUDA device visible: this library has no CPU fallback";
+    return MFB_ERR_NO_DEVICE;
+  }
+  if (d->device < 0 || d->device >= ndev) { g_last_error = "bad device ordinal"; return MFB_ERR_INVALID; }
+  const int dim = d->elem_kind == MFB_TET ? 3 : 2;
+  for (int i = 0; i < d->n_mat; ++i) {
+    const int mdl = d->materials[i].model;
+    if (mdl < 0 || mdl > 5) { g_last_error = "unknown material model"; return MFB_ERR_INVALID; }
+    if (dim == 2 && (mdl == MFB_NH || mdl == MFB_FUNG)) {
+      g_last_error = "Neohookean/Fung have no 3-vector (2D) form in the reference (src/energies/*.cpp)";
+      return MFB_ERR_UNSUPPORTED;
+    }
+  }
+  MFB_CUDA(cudaSetDevice(d->device));
+  mfb_ctx* c = new mfb_ctx();
+  c->device = d->device;
+  c->dim = dim; c->npe = dim + 1; c->N = dim == 3 ? 6 : 3; c->M = dim * dim; c->NP = c->N * (c->N + 1) / 2;
+  c->nV = d->nV; c->nE = d->nE;
+  c->ld = ((int64_t)d->nE + 31) / 32 * 32;
+  const int npe = c->npe, nE = c->nE;
+  const int64_t ld = c->ld;
+  int nF = 0;
+  for (int v = 0; v < d->nV; ++v) nF = d->free_map[v] + 1 > nF ? d->free_map[v] + 1 : nF;
+  c->nF = nF;
+
+  // host precompute, component-major
+  std::vector<int> hT((size_t)npe * ld, 0), hf((size_t)npe * ld, -1), hmat;
+  std::vector<double> hdphi((size_t)dim * dim * ld, 0.0), hvol((size_t)ld, 1.0);
+  for (int e = 0; e < nE; ++e) {
+    const int32_t* t = &d->T[(size_t)e * npe];
+    for (int k = 0; k < npe; ++k) {
+      if (t[k] < 0 || t[k] >= d->nV) { delete c; g_last_error = "element references a vertex out of range"; return MFB_ERR_INVALID; }
+      hT[(size_t)k * ld + e] = t[k];
+      hf[(size_t)k * ld + e] = d->free_map[t[k]];
+    }
+    if (dim == 3) {
+      const double* a = &d->Vref[3 * (size_t)t[0]]; const double* b = &d->Vref[3 * (size_t)t[1]];
+      const double* cc = &d->Vref[3 * (size_t)t[2]]; const double* dd = &d->Vref[3 * (size_t)t[3]];
+      double ad[3], bd[3], cd[3];
+      for (int l = 0; l < 3; ++l) { ad[l] = a[l] - dd[l]; bd[l] = b[l] - dd[l]; cd[l] = cc[l] - dd[l]; }
+      const double cr[3] = {bd[1] * cd[2] - bd[2] * cd[1], bd[2] * cd[0] - bd[0] * cd[2], bd[0] * cd[1] - bd[1] * cd[0]};
+      hvol[e] = std::fabs(-(ad[0] * cr[0] + ad[1] * cr[1] + ad[2] * cr[2]) / 6.0);
+      double A[3][3];   // Dm, columns = edges from vertex 0
+      for (int k = 0; k < 3; ++k) for (int l = 0; l < 3; ++l) A[l][k] = d->Vref[3 * (size_t)t[k + 1] + l] - a[l];
+      const double det = A[0][0] * (A[1][1] * A[2][2] - A[2][1] * A[1][2]) - A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+                         A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+      const double id = 1.0 / det;
+      double inv[3][3];
+      inv[0][0] = (A[1][1] * A[2][2] - A[2][1] * A[1][2]) * id;  inv[0][1] = -(A[0][1] * A[2][2] - A[0][2] * A[2][1]) * id;
+      inv[0][2] = (A[0][1] * A[1][2] - A[0][2] * A[1][1]) * id;  inv[1][0] = -(A[1][0] * A[2][2] - A[1][2] * A[2][0]) * id;
+      inv[1][1] = (A[0][0] * A[2][2] - A[0][2] * A[2][0]) * id;  inv[1][2] = -(A[0][0] * A[1][2] - A[1][0] * A[0][2]) * id;
+      inv[2][0] = (A[1][0] * A[2][1] - A[2][0] * A[1][1]) * id;  inv[2][1] = -(A[0][0] * A[2][1] - A[2][0] * A[0][1]) * id;
+      inv[2][2] = (A[0][0] * A[1][1] - A[1][0] * A[0][1]) * id;
+      for (int k = 0; k < 3; ++k) for (int cix = 0; cix < 3; ++cix) hdphi[(size_t)(3 * k + cix) * ld + e] = inv[k][cix];
+    } else {
+      const double* a = &d->Vref[2 * (size_t)t[0]]; const double* b = &d->Vref[2 * (size_t)t[1]]; const double* cc = &d->Vref[2 * (size_t)t[2]];
+      hvol[e] = (a[0] - cc[0]) * (b[1] - cc[1]) - (a[1] - cc[1]) * (b[0] - cc[0]);
+      double A[2][2];
+      for (int k = 0; k < 2; ++k) for (int l = 0; l < 2; ++l) A[l][k] = d->Vref[2 * (size_t)t[k + 1] + l] - a[l];
+      const double id = 1.0 / (A[0][0] * A[1][1] - A[0][1] * A[1][0]);
+      const double inv[2][2] = {{A[1][1] * id, -A[0][1] * id}, {-A[1][0] * id, A[0][0] * id}};
+      for (int k = 0; k < 2; ++k) for (int cix = 0; cix < 2; ++cix) hdphi[(size_t)(2 * k + cix) * ld + e] = inv[k][cix];
+    }
+  }
+  int rc = MFB_OK;
+  cudaStream_t st = c->stream;
+#define TRY(x) do { rc = (x); if (rc) { delete c; return rc; } } while (0)
+  { std::vector<double> hv(d->Vref, d->Vref + (size_t)dim * d->nV); TRY(upload(c->vref, hv, st)); MFB_CUDA(cudaStreamSynchronize(st)); }
+  TRY(upload(c->T, hT, st)); TRY(upload(c->fidx, hf, st)); TRY(upload(c->dphi, hdphi, st)); TRY(upload(c->vol, hvol, st));
+  if (d->mat_id) {
+    hmat.assign((size_t)ld, 0);
+    for (int e = 0; e < nE; ++e) {
+      if (d->mat_id[e] < 0 || d->mat_id[e] >= d->n_mat) { delete c; g_last_error = "mat_id out of range"; return MFB_ERR_INVALID; }
+      hmat[e] = d->mat_id[e];
+    }
+    TRY(upload(c->matid, hmat, st));
+  }
+  std::vector<MaterialDev> hm(d->n_mat);
+  for (int i = 0; i < d->n_mat; ++i) { hm[i].model = d->materials[i].model; hm[i].mu = d->materials[i].mu; hm[i].la = d->materials[i].la; }
+  TRY(upload(c->mats, hm, st));
+  TRY(build_pattern(c));
+  const size_t N = c->N, M = c->M, NP = c->NP;
+  TRY(c->R.alloc(M * ld)); TRY(c->s.alloc(N * ld)); TRY(c->la.alloc(N * ld)); TRY(c->ds.alloc(N * ld)); TRY(c->S.alloc(N * ld));
+  TRY(c->dSdF.alloc(M * N * ld)); TRY(c->g.alloc(N * ld)); TRY(c->H.alloc(NP * ld)); TRY(c->Hinv.alloc(NP * ld));
+  TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
+  TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
+  TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));
+  TRY(c->partials.alloc((size_t)c->grid() + 64)); TRY(c->scal.alloc(16));
+  TRY(c->soa_tmp.alloc(N * ld)); TRY(c->soa_tmp2.alloc(N * ld));
+#undef TRY
+  cudaError_t e1 = cudaMallocHost((void**)&c->h_scal, 16 * sizeof(double));
+  if (e1 != cudaSuccess) { delete c; g_last_error = "cudaMallocHost failed"; return MFB_ERR_CUDA; }
+  // zero all state so that padding lanes hold finite values
+  cudaMemsetAsync(c->R.p, 0, M * ld * 8, st); cudaMemsetAsync(c->s.p, 0, N * ld * 8, st); cudaMemsetAsync(c->la.p, 0, N * ld * 8, st);
+  cudaMemsetAsync(c->ds.p, 0, N * ld * 8, st); cudaMemsetAsync(c->S.p, 0, N * ld * 8, st); cudaMemsetAsync(c->dSdF.p, 0, M * N * ld * 8, st);
+  cudaMemsetAsync(c->g.p, 0, N * ld * 8, st); cudaMemsetAsync(c->H.p, 0, NP * ld * 8, st); cudaMemsetAsync(c->Hinv.p, 0, NP * ld * 8, st);
+  cudaMemsetAsync(c->evals.p, 0, ld * 8, st); cudaMemsetAsync(c->gl.p, 0, N * ld * 8, st); cudaMemsetAsync(c->grad_la.p, 0, N * ld * 8, st);
+  cudaMemsetAsync(c->iters.p, 0, ld * 4, st); cudaMemsetAsync(c->grad_x.p, 0, ((size_t)dim * nF + 1) * 8, st);
+  cudaMemsetAsync(c->rhs.p, 0, ((size_t)dim * nF + 1) * 8, st); cudaMemsetAsync(c->Avals.p, 0, (c->nnz > 0 ? c->nnz : 1) * 8, st);
+  cudaMemsetAsync(c->counters.p, 0, 64, st);
+  MFB_CUDA(cudaStreamSynchronize(st));
+  *out = c;
+  return MFB_OK;
+}
+
+extern "C" void mfb_destroy(mfb_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->h_scal) cudaFreeHost(c->h_scal);
+  delete c;
+}

@@ -1,0 +1,87 @@
+// Context object behind the C ABI: owns every device allocation of one MixedStretch instance.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/mfem_b200.h"
+#include "mfb_kernels2.cuh"
+
+namespace mfb {
+
+extern thread_local std::string g_last_error;
+
+#define MFB_CUDA(call)                                                                                   \
+  do {                                                                                                   \
+    cudaError_t err__ = (call);                                                                          \
+    if (err__ != cudaSuccess) {                                                                          \
+      mfb::g_last_error = std::string(#call) + ": " + cudaGetErrorString(err__);                         \
+      return MFB_ERR_CUDA;                                                                               \
+    }                                                                                                    \
+  } while (0)
+
+template <typename T>
+struct DBuf {   // plain device buffer
+  T* p = nullptr;
+  size_t n = 0;
+  int alloc(size_t count) {
+    free();
+    n = count;
+    if (count == 0) return MFB_OK;
+    cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+    if (e != cudaSuccess) { g_last_error = std::string("cudaMalloc: ") + cudaGetErrorString(e); p = nullptr; return MFB_ERR_CUDA; }
+    return MFB_OK;
+  }
+  void free() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  ~DBuf() { free(); }
+};
+
+}  // namespace mfb
+
+struct mfb_ctx {
+  int device = 0;
+  cudaStream_t stream = 0;
+  int dim = 3, npe = 4, N = 6, M = 9, NP = 21;
+  int nV = 0, nE = 0, nF = 0, nb = 0;
+  int64_t ld = 0, nnz = 0;
+  // options
+  int fuse_rhs = 1;
+  int assembly = 0;
+  // mesh (device)
+  mfb::DBuf<int> T, fidx, matid, smap, sstride;
+  mfb::DBuf<double> dphi, vol, vref;
+  mfb::DBuf<mfb::MaterialDev> mats;
+  // CSR structure (device)
+  mfb::DBuf<int> blockptr, bcol, diagblk, outer, inner;
+  // state (device)
+  mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals;
+  mfb::DBuf<int> iters;
+  mfb::DBuf<unsigned long long> counters;
+  // scratch
+  mfb::DBuf<double> xdev, vecF, partials, scal, aos, soa_tmp, soa_tmp2;
+  // pcg work vectors
+  mfb::DBuf<double> pcg_r, pcg_p, pcg_z, pcg_t, pcg_dinv;
+  double* h_scal = nullptr;   // pinned
+  // host copies (lazy)
+  std::vector<int32_t> h_outer, h_inner, h_smap, h_sstride;
+  // flags
+  bool rhs_valid = false;     // rhs_/gl_ match the current S_, s_, g_, H_, dSdF_
+  bool updated = false;
+  int64_t launches = 0;
+
+  mfb::DevMesh mesh() const {
+    mfb::DevMesh m;
+    m.dim = dim; m.npe = npe; m.nV = nV; m.nE = nE; m.nF = nF; m.ld = ld;
+    m.T = T.p; m.fidx = fidx.p; m.dphi = dphi.p; m.vol = vol.p; m.matid = matid.p; m.mats = mats.p;
+    m.smap = smap.p; m.sstride = sstride.p;
+    return m;
+  }
+  mfb::DevState state() const {
+    mfb::DevState st;
+    st.R = R.p; st.s = s.p; st.la = la.p; st.ds = ds.p; st.S = S.p; st.dSdF = dSdF.p; st.g = g.p; st.H = H.p;
+    st.Hinv = Hinv.p; st.evals = evals.p; st.gl = gl.p; st.grad_la = grad_la.p; st.iters = iters.p;
+    st.grad_x = grad_x.p; st.rhs = rhs.p; st.Avals = Avals.p; st.counters = counters.p;
+    return st;
+  }
+  int grid() const { return (nE + 127) / 128; }
+};

@@ -1,0 +1,541 @@
+// Remaining kernels of the path: reset, non-fused rhs, solve, energy / constraint reductions, evaluate_constraint,
+// matrix-free products and layout conversions.  Templated on DIM (3: tets, N=6, M=9; 2: triangles, N=3, M=4).
+#pragma once
+#include "mfb_kernels.cuh"
+
+namespace mfb {
+
+template <int DIM> struct Dims { static constexpr int N = DIM == 3 ? 6 : 3, M = DIM * DIM, NPE = DIM + 1, NP = N * (N + 1) / 2; };
+
+template <int DIM>
+__device__ __forceinline__ double symw(int k) { return k < DIM ? 1.0 : 2.0; }
+template <int DIM>
+__device__ __forceinline__ double syminvw(int k) { return k < DIM ? 1.0 : 0.5; }
+
+// F for either element kind; dphi gets the d*d stored rows
+template <int DIM>
+__device__ __forceinline__ void elem_F(const DevMesh& m, int e, const double* __restrict__ x, double* dphi, double* F) {
+  const int64_t ld = m.ld;
+  int v[DIM + 1];
+#pragma unroll
+  for (int k = 0; k <= DIM; ++k) v[k] = m.T[k * ld + e];
+#pragma unroll
+  for (int i = 0; i < DIM * DIM; ++i) dphi[i] = m.dphi[i * ld + e];
+  double x0[DIM], dx[DIM * DIM];
+#pragma unroll
+  for (int l = 0; l < DIM; ++l) x0[l] = __ldg(&x[DIM * (int64_t)v[0] + l]);
+#pragma unroll
+  for (int k = 0; k < DIM; ++k)
+#pragma unroll
+    for (int l = 0; l < DIM; ++l) dx[DIM * k + l] = __ldg(&x[DIM * (int64_t)v[k + 1] + l]) - x0[l];
+#pragma unroll
+  for (int c = 0; c < DIM; ++c)
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) {
+      double a = 0.0;
+#pragma unroll
+      for (int k = 0; k < DIM; ++k) a += dx[DIM * k + r] * dphi[DIM * k + c];
+      F[DIM * c + r] = a;
+    }
+}
+
+// polar without gradients from a given R (3D warm start; 2D closed form ignores R): stretch vector only
+template <int DIM>
+__device__ __forceinline__ void polar_stretch(double* R, const double* F, double* S, int* status, int* iters) {
+  if constexpr (DIM == 3) {
+    double Y[9];
+    *iters = procrustes3(R, F, Y, 1e-6, 100, status);
+    stretch6(R, F, S);
+  } else {
+    double Js[3][4];
+    polar2(F, R, S, Js);
+    *iters = 0;
+  }
+}
+
+// scatter  sign * vol * Jloc^T t  into a free-vertex vector (t is the M-vector of an element)
+template <int DIM>
+__device__ __forceinline__ void scatter_vertex(const DevMesh& m, int e, const double* dphi, const double* t, double scale, double* out) {
+  const int64_t ld = m.ld;
+  double v0[DIM];
+#pragma unroll
+  for (int r = 0; r < DIM; ++r) v0[r] = 0.0;
+#pragma unroll
+  for (int k = 0; k < DIM; ++k) {
+    const int f = m.fidx[(k + 1) * ld + e];
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) {
+      double a = 0.0;
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) a += dphi[DIM * k + c] * t[DIM * c + r];
+      a *= scale;
+      v0[r] -= a;
+      if (f >= 0) red_add(&out[DIM * (int64_t)f + r], a);
+    }
+  }
+  const int f0 = m.fidx[e];
+  if (f0 >= 0) {
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) red_add(&out[DIM * (int64_t)f0 + r], v0[r]);
+  }
+}
+
+// (PJW^T dx)_e : M-vector, = vol * sum_k dphi(k,c) dx[f_k][r] over free vertices
+template <int DIM>
+__device__ __forceinline__ void gather_Jdx(const DevMesh& m, int e, const double* __restrict__ dx, double vol, double* Jdx) {
+  const int64_t ld = m.ld;
+  double d[DIM + 1][DIM], dp[DIM * DIM];
+#pragma unroll
+  for (int i = 0; i < DIM * DIM; ++i) dp[i] = m.dphi[i * ld + e];
+#pragma unroll
+  for (int k = 0; k <= DIM; ++k) {
+    const int f = m.fidx[k * ld + e];
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) d[k][r] = (f >= 0) ? __ldg(&dx[DIM * (int64_t)f + r]) : 0.0;
+  }
+#pragma unroll
+  for (int c = 0; c < DIM; ++c) {
+    double p0 = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) p0 -= dp[DIM * k + c];
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) {
+      double a = p0 * d[0][r];
+#pragma unroll
+      for (int k = 0; k < DIM; ++k) a += dp[DIM * k + c] * d[k + 1][r];
+      Jdx[DIM * c + r] = vol * a;
+    }
+  }
+}
+
+// reset()  mixed_stretch.cpp:294-338 : R = I, polar with gradients, s_ = S_, la_ = 0, H_ = Hinv_ = I, g_ = 0
+template <int DIM>
+__global__ void __launch_bounds__(128) k_reset(DevMesh m, DevState st, const double* __restrict__ x) {
+  using D = Dims<DIM>;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  double dphi[D::M], F[D::M], R[D::M], S[D::N];
+  int status = 0, iters = 0;
+  elem_F<DIM>(m, e, x, dphi, F);
+#pragma unroll
+  for (int i = 0; i < D::M; ++i) R[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < DIM; ++i) R[i * DIM + i] = 1.0;
+  if constexpr (DIM == 3) {
+    double Y[9], Hinv3[6];
+    iters = procrustes3(R, F, Y, 1e-6, 100, &status);
+    stretch6(R, F, S);
+    if (!procrustes_hinv(Y, Hinv3)) status |= ST_POLAR_HFAIL;
+#pragma unroll
+    for (int n = 0; n < 6; ++n) {
+      double col[9];
+      dsdf3_column(n, R, F, Hinv3, col);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) st.dSdF[(n * 9 + k) * ld + e] = symw<3>(n) * col[k];
+    }
+  } else {
+    double Js[3][4];
+    polar2(F, R, S, Js);
+#pragma unroll
+    for (int n = 0; n < 3; ++n)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) st.dSdF[(n * 4 + k) * ld + e] = symw<2>(n) * Js[n][k];
+  }
+#pragma unroll
+  for (int i = 0; i < D::M; ++i) st.R[i * ld + e] = R[i];
+#pragma unroll
+  for (int k = 0; k < D::N; ++k) { st.S[k * ld + e] = S[k]; st.s[k * ld + e] = S[k]; st.la[k * ld + e] = 0.0; st.ds[k * ld + e] = 0.0; st.g[k * ld + e] = 0.0; st.gl[k * ld + e] = 0.0; st.grad_la[k * ld + e] = 0.0; }
+#pragma unroll
+  for (int i = 0; i < D::N; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) { st.H[symidx(i, j) * ld + e] = (i == j) ? 1.0 : 0.0; st.Hinv[symidx(i, j) * ld + e] = (i == j) ? 1.0 : 0.0; }
+  st.evals[e] = 0.0;
+  st.iters[e] = iters;
+  count_status(st.counters, status, iters, 0);
+}
+
+// rhs()  mixed_stretch.cpp:245-275 from stored fields (used when the fused value is stale)
+template <int DIM>
+__global__ void __launch_bounds__(128) k_rhs(DevMesh m, DevState st) {
+  using D = Dims<DIM>;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  const double vol = m.vol[e];
+  double diff[D::N], gl[D::N];
+#pragma unroll
+  for (int k = 0; k < D::N; ++k) diff[k] = symw<DIM>(k) * (st.S[k * ld + e] - st.s[k * ld + e]);
+#pragma unroll
+  for (int r = 0; r < D::N; ++r) {
+    double a = 0.0;
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) a += st.H[symidx(r, k) * ld + e] * diff[k];
+    gl[r] = vol * a + syminvw<DIM>(r) * st.g[r * ld + e];
+    st.gl[r * ld + e] = gl[r];
+  }
+  double t[D::M], dphi[D::M];
+#pragma unroll
+  for (int q = 0; q < D::M; ++q) {
+    double a = 0.0;
+#pragma unroll
+    for (int n = 0; n < D::N; ++n) a += st.dSdF[(n * D::M + q) * ld + e] * gl[n];
+    t[q] = a;
+    dphi[q] = m.dphi[q * ld + e];
+  }
+  scatter_vertex<DIM>(m, e, dphi, t, -vol, st.rhs);
+}
+
+// grad_x_ only (mixed_stretch.cpp:224-232), for callers that changed la_ after update()
+template <int DIM>
+__global__ void __launch_bounds__(128) k_grad_x(DevMesh m, DevState st) {
+  using D = Dims<DIM>;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  double t[D::M], dphi[D::M];
+#pragma unroll
+  for (int q = 0; q < D::M; ++q) {
+    double a = 0.0;
+#pragma unroll
+    for (int n = 0; n < D::N; ++n) a += st.dSdF[(n * D::M + q) * ld + e] * st.la[n * ld + e];
+    t[q] = a;
+    dphi[q] = m.dphi[q * ld + e];
+  }
+  scatter_vertex<DIM>(m, e, dphi, t, m.vol[e], st.grad_x);
+}
+
+// solve(dx)  mixed_stretch.cpp:277-292
+template <int DIM>
+__global__ void __launch_bounds__(128) k_solve(DevMesh m, DevState st, const double* __restrict__ dx) {
+  using D = Dims<DIM>;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  double Jdx[D::M];
+  gather_Jdx<DIM>(m, e, dx, m.vol[e], Jdx);
+  double t[D::N], la[D::N];
+#pragma unroll
+  for (int n = 0; n < D::N; ++n) {
+    double a = 0.0;
+#pragma unroll
+    for (int q = 0; q < D::M; ++q) a += st.dSdF[(n * D::M + q) * ld + e] * Jdx[q];
+    t[n] = a;
+  }
+#pragma unroll
+  for (int r = 0; r < D::N; ++r) {
+    double a = st.gl[r * ld + e];
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) a += st.H[symidx(r, k) * ld + e] * t[k];
+    la[r] = a;
+    st.la[r * ld + e] = a;
+  }
+  double v[D::N];
+#pragma unroll
+  for (int k = 0; k < D::N; ++k) v[k] = st.g[k * ld + e] - symw<DIM>(k) * la[k];
+#pragma unroll
+  for (int r = 0; r < D::N; ++r) {
+    double a = 0.0;
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) a += st.Hinv[symidx(r, k) * ld + e] * v[k];
+    st.ds[r * ld + e] = -a;
+  }
+}
+
+// block-level sum, deterministic: per-block partials, then k_sum_partials adds them in index order
+__device__ __forceinline__ double block_sum_128(double v, double* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) sh[w] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (threadIdx.x == 0) { for (int i = 0; i < (int)(blockDim.x >> 5); ++i) r += sh[i]; }
+  return r;
+}
+static __global__ void k_sum_partials(const double* __restrict__ partials, int n, double* out) {
+  __shared__ double sh[32];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) a += partials[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) { double r = 0.0; for (int i = 0; i < (int)(blockDim.x >> 5); ++i) r += sh[i]; *out = r; }
+}
+
+// energy()  mixed_stretch.cpp:93-107 ; s given component-major with leading dimension ld
+template <int DIM>
+__global__ void __launch_bounds__(128) k_energy(DevMesh m, const double* __restrict__ s_soa, double* partials) {
+  using D = Dims<DIM>;
+  __shared__ double sh[4];
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  double val = 0.0;
+  if (e < m.nE) {
+    double s[D::N];
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) s[k] = s_soa[k * m.ld + e];
+    const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
+    const double psi = (DIM == 3) ? material_energy6(mat.model, mat.mu, mat.la, s) : material_energy3(mat.model, mat.mu, mat.la, s);
+    val = psi * m.vol[e];
+  }
+  const double r = block_sum_128(val, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = r;
+}
+
+// constraint_value()  mixed_stretch.cpp:109-136  (WRITE_C: evaluate_constraint :345-366 writes the vector instead)
+template <int DIM, bool WRITE_C>
+__global__ void __launch_bounds__(128) k_constraint(DevMesh m, DevState st, const double* __restrict__ x,
+                                                    const double* __restrict__ s_soa, double* partials, double* c_out) {
+  using D = Dims<DIM>;
+  __shared__ double sh[4];
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  double val = 0.0;
+  if (e < m.nE) {
+    const int64_t ld = m.ld;
+    double dphi[D::M], F[D::M], R[D::M], S[D::N];
+    int status = 0, iters = 0;
+    elem_F<DIM>(m, e, x, dphi, F);
+#pragma unroll
+    for (int i = 0; i < D::M; ++i) R[i] = st.R[i * ld + e];
+    polar_stretch<DIM>(R, F, S, &status, &iters);
+    const double vol = m.vol[e];
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) {
+      const double d = symw<DIM>(k) * (S[k] - s_soa[k * ld + e]);
+      if (WRITE_C) c_out[k * ld + e] = d * vol;
+      else val += st.la[k * ld + e] * d;
+    }
+    val *= vol;
+  }
+  if (!WRITE_C) {
+    const double r = block_sum_128(val, sh);
+    if (threadIdx.x == 0) partials[blockIdx.x] = r;
+  }
+}
+
+// product_* operators  mixed_stretch.cpp:406-468 ; element vectors are component-major (ld), vertex vectors d*nF
+template <int DIM>
+__global__ void __launch_bounds__(128) k_product(DevMesh m, DevState st, int which, int transposed,
+                                                 const double* __restrict__ xin, double* out) {
+  using D = Dims<DIM>;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  const double vol = m.vol[e];
+  if (which == 0 || which == 1) {
+    double xv[D::N];
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) xv[k] = xin[k * ld + e];
+#pragma unroll
+    for (int r = 0; r < D::N; ++r) {
+      double a = 0.0;
+#pragma unroll
+      for (int k = 0; k < D::N; ++k) {
+        // Hloc_ = vol * Hfix = vol^2 Sym H_ Sym ; product_hessian_inv uses vol * Hinv_
+        const double hv = (which == 0) ? vol * vol * symw<DIM>(r) * symw<DIM>(k) * st.H[symidx(r, k) * ld + e]
+                                       : vol * st.Hinv[symidx(r, k) * ld + e];
+        a += hv * xv[k];
+      }
+      out[r * ld + e] += a;
+    }
+  } else if (which == 2) {
+#pragma unroll
+    for (int k = 0; k < D::N; ++k) out[k * ld + e] += vol * symw<DIM>(k) * xin[k * ld + e];
+  } else if (transposed) {   // out (d*nF) -= PJW * (dSdF x_e)
+    double t[D::M], dphi[D::M];
+#pragma unroll
+    for (int q = 0; q < D::M; ++q) {
+      double a = 0.0;
+#pragma unroll
+      for (int n = 0; n < D::N; ++n) a += st.dSdF[(n * D::M + q) * ld + e] * xin[n * ld + e];
+      t[q] = a; dphi[q] = m.dphi[q * ld + e];
+    }
+    scatter_vertex<DIM>(m, e, dphi, t, -vol, out);
+  } else {                   // out_e -= dSdF^T (PJW^T x)_e
+    double Jdx[D::M];
+    gather_Jdx<DIM>(m, e, xin, vol, Jdx);
+#pragma unroll
+    for (int n = 0; n < D::N; ++n) {
+      double a = 0.0;
+#pragma unroll
+      for (int q = 0; q < D::M; ++q) a += st.dSdF[(n * D::M + q) * ld + e] * Jdx[q];
+      out[n * ld + e] -= a;
+    }
+  }
+}
+
+// -----------------------------------------------------------------------------------------------------------------
+// k_update_tri2d : MixedStretch<2>::update() for Tri2DMesh elements, same fusion as k_update_tet (N=3, M=4, 6x6 blocks).
+// The reference's 2D "volume" is the SIGNED double area (tri2d_mesh.cpp:32-34), so vol multiplies at the end and no
+// square root of it is taken.
+// -----------------------------------------------------------------------------------------------------------------
+template <bool FUSE_RHS, bool ASSEMBLE>
+__global__ void __launch_bounds__(128) k_update_tri2d(DevMesh m, DevState st, const double* __restrict__ x, double h2) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  int status = 0;
+  double s[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) s[k] = st.s[k * ld + e];
+  const double vol = m.vol[e];
+  const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
+  double g[3], Hf[6], Hinv[6];
+  int sweeps;
+  material_grad_hess3(mat.model, mat.mu, mat.la, s, h2, g, Hf);
+  const double lmax = psd_fix_invert<3>(Hf, Hinv, 1e-8, &sweeps);
+  st.evals[e] = h2 * lmax;
+  if (!(lmax == lmax) || lmax > 1e300) status |= ST_NONFINITE;
+  const double iv = 1.0 / vol;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) {
+      const double w = ((i < 2) ? 1.0 : 0.5) * ((j < 2) ? 1.0 : 0.5);
+      st.H[symidx(i, j) * ld + e] = iv * w * Hf[symidx(i, j)];
+      st.Hinv[symidx(i, j) * ld + e] = Hinv[symidx(i, j)];
+    }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) st.g[k * ld + e] = g[k];
+
+  double dphi[4], F[4], R[4], S[3], Js[3][4];
+  elem_F<2>(m, e, x, dphi, F);
+  polar2(F, R, S, Js);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) st.R[i * ld + e] = R[i];
+  st.iters[e] = 0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    st.S[k * ld + e] = S[k];
+    st.grad_la[k * ld + e] = ((k < 2) ? 1.0 : 2.0) * (S[k] - s[k]) * vol;
+  }
+  double u[3];
+  if (FUSE_RHS) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      double a = g[i];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) a += Hf[symidx(i, j)] * (S[j] - s[j]);
+      u[i] = a;
+      st.gl[i * ld + e] = ((i < 2) ? 1.0 : 0.5) * a;
+    }
+  }
+  double B[4][3];   // rows (k-1)*2 + r for vertices k = 1..2
+#pragma unroll
+  for (int n = 0; n < 3; ++n) {
+    const double sy = (n < 2) ? 1.0 : 2.0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) st.dSdF[(n * 4 + k) * ld + e] = sy * Js[n][k];
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+      for (int r = 0; r < 2; ++r) B[2 * k + r][n] = dphi[2 * k] * Js[n][r] + dphi[2 * k + 1] * Js[n][2 + r];
+  }
+  if (!(B[0][0] == B[0][0])) status |= ST_NONFINITE;
+  int f[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) f[k] = m.fidx[k * ld + e];
+  {
+    double tl[3];
+#pragma unroll
+    for (int n = 0; n < 3; ++n) tl[n] = ((n < 2) ? 1.0 : 2.0) * st.la[n * ld + e];
+    double gx0[2] = {0, 0}, rh0[2] = {0, 0};
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        double a = 0.0, b = 0.0;
+#pragma unroll
+        for (int n = 0; n < 3; ++n) { a += B[2 * k + r][n] * tl[n]; if (FUSE_RHS) b += B[2 * k + r][n] * u[n]; }
+        a *= vol; b *= -vol;
+        gx0[r] -= a; rh0[r] -= b;
+        if (f[k + 1] >= 0) {
+          red_add(&st.grad_x[2 * (int64_t)f[k + 1] + r], a);
+          if (FUSE_RHS) red_add(&st.rhs[2 * (int64_t)f[k + 1] + r], b);
+        }
+      }
+    if (f[0] >= 0) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        red_add(&st.grad_x[2 * (int64_t)f[0] + r], gx0[r]);
+        if (FUSE_RHS) red_add(&st.rhs[2 * (int64_t)f[0] + r], rh0[r]);
+      }
+    }
+  }
+  if (ASSEMBLE) {
+    // W = vol * B * Hfix (4x3, plus vertex-0 rows), block(j,k) = W_j B_k^T
+    double Bf[6][3], W[6][3];
+#pragma unroll
+    for (int n = 0; n < 3; ++n) {
+      Bf[0][n] = -(B[0][n] + B[2][n]); Bf[1][n] = -(B[1][n] + B[3][n]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) Bf[2 + q][n] = B[q][n];
+    }
+#pragma unroll
+    for (int q = 0; q < 6; ++q)
+#pragma unroll
+      for (int n = 0; n < 3; ++n) {
+        double a = 0.0;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) a += Bf[q][i] * Hf[symidx(i, n)];
+        W[q][n] = vol * a;
+      }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int stride = m.sstride[j * ld + e];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int idx = m.smap[(j * 3 + k) * ld + e];
+        if (idx < 0) continue;
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            double a = 0.0;
+#pragma unroll
+            for (int n = 0; n < 3; ++n) a += W[2 * j + r][n] * Bf[2 * k + c][n];
+            red_add(&st.Avals[(int64_t)idx + (int64_t)r * stride + c], a);
+          }
+      }
+    }
+  }
+  count_status(st.counters, status, 0, sweeps);
+}
+
+// ---- layout conversions (getters / setters; not on the hot path) ----
+static __global__ void k_soa_to_aos(const double* __restrict__ soa, double* __restrict__ aos, int ncomp, int nE, int64_t ld) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nE * ncomp) return;
+  const int e = (int)(i / ncomp), c = (int)(i % ncomp);
+  aos[i] = soa[c * ld + e];
+}
+static __global__ void k_aos_to_soa(const double* __restrict__ aos, double* __restrict__ soa, int ncomp, int nE, int64_t ld) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nE * ncomp) return;
+  const int e = (int)(i / ncomp), c = (int)(i % ncomp);
+  soa[c * ld + e] = aos[i];
+}
+// packed symmetric N x N (component-major) -> full column-major N x N per element; mode 0 plain, 1 Hloc scaling
+static __global__ void k_sym_to_full(const double* __restrict__ soa, const double* __restrict__ vol, double* __restrict__ aos,
+                              int N, int dim, int nE, int64_t ld, int mode) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nE * N * N) return;
+  const int e = (int)(i / (N * N)), q = (int)(i % (N * N));
+  const int r = q % N, c = q / N;
+  double v = soa[(int64_t)symidx(r, c) * ld + e];
+  if (mode == 1) { const double w = ((r < dim) ? 1.0 : 2.0) * ((c < dim) ? 1.0 : 2.0); v *= vol[e] * vol[e] * w; }
+  aos[i] = v;
+}
+static __global__ void k_grad_mixed(const double* __restrict__ g, const double* __restrict__ vol, double* __restrict__ aos, int N, int nE, int64_t ld) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nE * N) return;
+  const int e = (int)(i / N), c = (int)(i % N);
+  aos[i] = vol[e] * g[c * ld + e];     // grad_ = vol * g_   (mixed_stretch.cpp:237-242)
+}
+static __global__ void k_int_to_double(const int* __restrict__ a, double* __restrict__ o, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) o[i] = (double)a[i];
+}
+
+}  // namespace mfb

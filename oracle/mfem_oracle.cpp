@@ -170,10 +170,10 @@ struct Mesh {
         }
       } else {
         const double* a = &Vref[2 * t[0]]; const double* b = &Vref[2 * t[1]]; const double* c = &Vref[2 * t[2]];
-        // igl::doublearea for 2D triangles (signed r0(0)*r1(1)-r0(1)*r1(0) with r0=a-c, r1=b-c), then |.| ;
-        // tri2d_mesh.cpp:32-34 : the reference's 2D "volume" is the DOUBLE area
+        // igl::doublearea for 2D triangles: SIGNED rx*sy - ry*sx with r=a-c, s=b-c (doublearea.cpp:33-42,60-67);
+        // tri2d_mesh.cpp:32-34 takes it as is: the reference's 2D "volume" is the signed DOUBLE area
         const double r0x = a[0] - c[0], r0y = a[1] - c[1], r1x = b[0] - c[0], r1y = b[1] - c[1];
-        vols[e] = std::fabs(r0x * r1y - r0y * r1x);
+        vols[e] = r0x * r1y - r0y * r1x;
         M2 Dm;
         for (int k = 0; k < 2; ++k) for (int l = 0; l < 2; ++l) Dm(l, k) = Vref[2 * t[k + 1] + l] - a[l];
         const double det = Dm(0, 0) * Dm(1, 1) - Dm(0, 1) * Dm(1, 0);
