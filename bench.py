@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""Benchmark of the mixed-stretch hot path: tet updates+assemblies per second (FP64).
+
+    python bench.py --gpus N --steps K --warmup W            # CUDA path (this repo)
+    python bench.py --impl reference --steps K --warmup W     # CPU arm: the oracle port on the box's host cores
+
+A step = one MixedStretch::update() (F -> polar -> material g,H -> PSD fix -> element blocks -> CSR scatter,
+grad_x_, grad_la_, fused Schur rhs) over every tet of the workload, inputs resident in HBM.  The workload is
+BASELINE.json configs[3]: the synthetic 10M-tet Kuhn box grid (119^3 x 6), Stable-Neohookean; with N > 1 the SAME grid
+is element-partitioned into N slabs (strong scaling) and the interface-vertex sums of grad_x_/rhs_ go through one
+NCCL all-reduce per step.  Consecutive steps alternate between two vertex states so the warm-started polar solve
+does real Newton iterations every step (a repeated x would converge in zero iterations).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "tet_updates_assemblies_per_s"
+UNIT = "tets/s"
+DT = 0.0333
+E_YOUNG, NU = 1e6, 0.45
+_NATIVE_LIB = None
+
+
+def algorithmic_bytes(nE, nV, nF, nb):
+    """1372 nE + 24 nV + 24 nF + 72 nb (each datum once, FP64 / int32, symmetric 6x6 packed)."""
+    return 1372.0 * nE + 24.0 * nV + 24.0 * nF + 72.0 * nb
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            p = [t.strip() for t in r.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_arm(nx, ny, nz, seconds, threads=None, native=True):
+    """Time the oracle (CPU restatement, OpenMP) on a bounded sample of the workload: same generator, same material,
+    same alternating states.  Returns (tets/s, dict)."""
+    from mixed_fem_b200 import meshgen
+    from oracle import orc
+    global _NATIVE_LIB
+    libpath = None
+    if native:   # rebuild for this host's ISA into a scratch file (the shipped liborc.so targets x86-64-v3)
+        if _NATIVE_LIB is None:
+            try:
+                _NATIVE_LIB = orc.build(march="native", out="/tmp/liborc_native_%d.so" % os.getpid(), force=True)
+            except Exception:
+                _NATIVE_LIB = ""
+        libpath = _NATIVE_LIB or None
+    L = orc.lib(libpath)
+    if threads:
+        L.orc_set_num_threads(int(threads))
+    cores = L.orc_num_threads()
+    V, T = meshgen.kuhn_grid(nx, ny, nz, h=1.0 / 119)
+    fm = meshgen.pinned_free_map(V)
+    mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
+    xa = meshgen.deformed_positions(V, 1.0 / 119, scale=1.0)
+    xb = meshgen.deformed_positions(V, 1.0 / 119, scale=0.5)
+    o = orc.OracleMixedStretch(V, T, fm, [("Stable-Neohookean", mu, la)], libpath=libpath)
+    o.reset()
+    o.update_rotations(xb)
+    o.set("s", o.get("S"))
+    rng = np.random.default_rng(meshgen.SEED)
+    o.set("la", rng.uniform(-1, 1, size=6 * T.shape[0]) * mu * 1e-3)
+    o.update(xa, DT); o.rhs()          # warm-up
+    o.timers(reset=True)
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        o.update(xb if reps % 2 == 0 else xa, DT)
+        o.rhs()
+        reps += 1
+        if time.perf_counter() - t0 >= seconds:
+            break
+    el = time.perf_counter() - t0
+    tm = o.timers()
+    info = {"value": T.shape[0] * reps / el, "unit": UNIT, "cores": int(cores), "kind": "port",
+            "sample": "%dx%dx%d x6 = %d tets of the same Kuhn grid, %d update()+rhs() calls in %.1f s, OpenMP, -O3 -march=%s; "
+                      "oracle = Eigen-free restatement (generous: no per-element heap matrices)" %
+                      (nx, ny, nz, T.shape[0], reps, el, "native" if libpath else "x86-64-v3"),
+            "phase_ms_per_call": {k: v / reps for k, v in tm.items()}}
+    return info["value"], info
+
+
+class DevArray:
+    """__cuda_array_interface__ view of a raw device pointer so torch can wrap context-owned vectors without copies."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f8", "data": (int(ptr), False), "version": 2}
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import mixed_fem_b200 as mf
+    from mixed_fem_b200 import meshgen, partition
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the CUDA path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    nx, ny, nz = args.grid
+    h = 1.0 / 119
+    V, T = meshgen.kuhn_grid(nx, ny, nz, h=h)
+    fm = meshgen.pinned_free_map(V)
+    mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
+    nE_total, nV_total = T.shape[0], V.shape[0]
+    xa = meshgen.deformed_positions(V, h, scale=1.0)
+    xb = meshgen.deformed_positions(V, h, scale=0.5)
+    rng = np.random.default_rng(meshgen.SEED)
+    lam = rng.uniform(-1, 1, size=6 * nE_total) * mu * 1e-3
+    if world > 1:
+        loc, parts, shared = partition.make_local(V, T, fm, world, rank)
+        Vl, Tl, fml = loc.V, loc.T, loc.free_map
+        xa, xb = loc.restrict_vertex_vector(xa, 3), loc.restrict_vertex_vector(xb, 3)
+        lam = loc.restrict_element_vector(lam, 6)
+    else:
+        loc, Vl, Tl, fml = None, V, T, fm
+    del V, T
+    ms = mf.MixedStretch(Vl, Tl, fml, [("Stable-Neohookean", mu, la)], device=local_rank)
+    ms.set_stream(torch.cuda.current_stream().cuda_stream)
+    # state: R, s from the 'previous' positions (polar from identity on the device), lambda seeded
+    ms.reset(xb)
+    ms.set("la", lam)
+    del lam
+    nb = ms.nnz // 9
+    # device-resident inputs + pinned host copies for the e2e leg
+    xs_host = [torch.from_numpy(xa).pin_memory(), torch.from_numpy(xb).pin_memory()]
+    xs_dev = [t.to(dev) for t in xs_host]
+    rhs_host = torch.empty(3 * ms.nfree, dtype=torch.float64).pin_memory()
+    iface = None
+    if world > 1:
+        iface = partition.TorchInterface(loc, 3, dev)
+        gx = torch.as_tensor(DevArray(ms.field_dev("grad_x")[0], (ms.nfree, 3)), device=dev)
+        rh = torch.as_tensor(DevArray(ms.rhs_dev(), (ms.nfree, 3)), device=dev)
+
+    def step(i):
+        ms.update_dev(xs_dev[i % 2].data_ptr(), DT)
+        if iface is not None:
+            iface.sum2(gx, rh)
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    sync()
+    st0 = ms.status()
+    ms.set_option("profile", 1)
+    ms.kernel_time_ms()
+    ms.launches(reset=True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    e0.record()
+    for i in range(args.steps):
+        step(args.warmup + i)
+    e1.record()
+    sync()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ms.launches()
+    kt, kn = ms.kernel_time_ms()
+    ms.set_option("profile", 0)
+    # ---- e2e leg: host buffers through the C ABI, H2D of x and D2H of rhs inside the timed region
+    import ctypes as C
+    def e2e_step(i):
+        xh = xs_host[i % 2]
+        ms._check(ms.L.mfb_update(ms.h, C.cast(xh.data_ptr(), C.POINTER(C.c_double)), DT))
+        if iface is not None:
+            iface.sum2(gx, rh)
+        ms._check(ms.L.mfb_rhs(ms.h, C.cast(rhs_host.data_ptr(), C.POINTER(C.c_double))))
+    for i in range(2):
+        e2e_step(i)
+    sync()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        e2e_step(i)
+    e1.record()
+    sync()
+    e2e_ms = max(e0.elapsed_time(e1), 0.0)
+    e2e_wall = (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([ms_total, e2e_ms, kt / max(kn, 1)], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([launches, 3 * Vl.shape[0] * 8, 3 * ms.nfree * 8, nb], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms_total, e2e_ms, k_ms = t.tolist()
+    launches_all, h2d, d2h, nb_all = cnt.tolist()
+    if rank == 0:
+        per_step = ms_total / args.steps
+        value = nE_total / (per_step * 1e-3)
+        nF_total = int((fm >= 0).sum())
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        # roofline of the dominant kernel (k_update_tet) on rank 0's share, per launch
+        nE_l, nV_l, nF_l = Tl.shape[0], Vl.shape[0], ms.nfree
+        abytes = algorithmic_bytes(nE_l, nV_l, nF_l, nb)
+        achieved = abytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else None
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_update_tet_bytes_per_launch")
+        except Exception:
+            pass
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "C4: synthetic %dx%dx%d Kuhn box grid = %d tets / %d vertices, Stable-Neohookean E=1e6 nu=0.45, dt=0.0333, "
+                                   "MixedStretch::update() + fused Schur rhs" % (nx, ny, nz, nE_total, nV_total),
+                       "partition": "1 GPU" if world == 1 else "%d element slabs, NCCL all-reduce of interface grad_x_/rhs_" % world,
+                       "l2": "inputs larger than L2 (%.1f GB of per-element state per step), no flush needed" % (1372.0 * nE_total / world / 1e9),
+                       "states": "x alternates between two seeded states each step so the warm-started polar iterates"},
+            "e2e": {"value": nE_total / (e2e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "api": "mfb_update(x_host) + mfb_rhs(out_host), pinned host buffers", "ms_per_step": e2e_ms / args.steps,
+                    "wall_ms_per_step": e2e_wall / args.steps},
+            "gpu_launches": int(launches_all),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                         "traffic": traffic, "kernel": "k_update_tet<fuse_rhs,assemble>", "kernel_ms": k_ms,
+                         "algorithmic_bytes_per_launch": abytes, "bytes_per_tet": abytes / nE_l,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                         "kernel_share_of_step": k_ms / per_step if per_step > 0 else None},
+            "polar_iters_per_tet": st0["polar_iters"] / max(nE_l, 1), "eig_sweeps_per_tet": st0["eig_sweeps"] / max(nE_l, 1),
+        }
+        if world == 1 and not args.no_cpu:
+            cx, cy, cz = args.cpu_grid
+            _, info = cpu_arm(cx, cy, cz, args.cpu_seconds)
+            out["cpu_baseline"] = info
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cx, cy, cz = args.cpu_grid
+    per = max(2.0, min(20.0, 60.0 / max(1, args.steps + args.warmup)))
+    vals = []
+    info = None
+    for i in range(args.warmup + args.steps):
+        v, info = cpu_arm(cx, cy, cz, per)
+        if i >= args.warmup:
+            vals.append(v)
+    value = float(np.mean(vals))
+    info["value"] = value
+    nE = cx * cy * cz * 6
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": nE / value * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic",
+           "config": {"workload": "bounded sample of C4: %dx%dx%d Kuhn grid = %d tets, Stable-Neohookean, update()+rhs() on the host cores "
+                                  "(reference cannot be compiled here: no Eigen; oracle port timed instead)" % (cx, cy, cz, nE)},
+           "cpu_baseline": info,
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--grid", type=int, nargs=3, default=[119, 119, 119])
+    ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -140,7 +140,9 @@ int mfb_pcg_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* b_dev, dou
 
 /* ---- instrumentation ---- */
 int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
-int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "assembly" 0 atomic / 1 gather */
+int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0) */
+/* device time of the update kernel alone, CUDA events on the ctx stream, accumulated while option "profile" is 1 */
+int mfb_kernel_time_ms(mfb_ctx* ctx, double* total_ms, int* count);
 
 #ifdef __cplusplus
 }

@@ -27,7 +27,7 @@ EXPORTS = [
     "mfb_solve", "mfb_solve_dev", "mfb_post_solve", "mfb_energy", "mfb_constraint_value", "mfb_energy_dev",
     "mfb_constraint_value_dev", "mfb_evaluate_constraint", "mfb_lhs_values", "mfb_lhs_values_dev", "mfb_product",
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
-    "mfb_num_kernel_launches", "mfb_set_option",
+    "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
 ]
 
 
@@ -113,6 +113,7 @@ def lib():
     L.mfb_pcg_dev.argtypes = [vp, vp, vp, vp, C.c_int, C.c_double, C.c_int, ip, dp]
     L.mfb_num_kernel_launches.argtypes = [vp, C.POINTER(C.c_int64), C.c_int]
     L.mfb_set_option.argtypes = [vp, C.c_char_p, C.c_int]
+    L.mfb_kernel_time_ms.argtypes = [vp, dp, ip]
     _lib = L
     return L
 
@@ -331,6 +332,11 @@ class MixedStretch:
 
     def set_option(self, name, value):
         self._check(self.L.mfb_set_option(self.h, name.encode(), int(value)))
+
+    def kernel_time_ms(self):
+        t, n = C.c_double(), C.c_int32()
+        self._check(self.L.mfb_kernel_time_ms(self.h, C.byref(t), C.byref(n)))
+        return t.value, n.value
 
     def launches(self, reset=False):
         n = C.c_int64()

@@ -19,6 +19,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!name) return MFB_ERR_INVALID;
   if (!strcmp(name, "fuse_rhs")) { c->fuse_rhs = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "assembly")) { c->assembly = value; return MFB_OK; }
+  if (!strcmp(name, "profile")) { c->profile = value ? 1 : 0; return MFB_OK; }
   g_last_error = "unknown option";
   return MFB_ERR_INVALID;
 }
@@ -105,13 +106,30 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   if (c->nnz) MFB_CUDA(cudaMemsetAsync(c->Avals.p, 0, (size_t)c->nnz * 8, st));
   const DevMesh m = c->mesh();
   const DevState s = c->state();
+  int slot = -1;
+  if (c->profile && c->ev_count < 4096) {
+    slot = c->ev_count++;
+    if ((int)c->ev0.size() <= slot) {
+      cudaEvent_t a, b;
+      MFB_CUDA(cudaEventCreate(&a)); MFB_CUDA(cudaEventCreate(&b));
+      c->ev0.push_back(a); c->ev1.push_back(b);
+    }
+    MFB_CUDA(cudaEventRecord(c->ev0[slot], st));
+  }
   if (c->dim == 3) {
+    k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
+    LAUNCHED(c, 1);
     if (c->fuse_rhs) k_update_tet<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tet<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   } else {
     if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   }
+  if (c->dim == 3 && c->nb > 0) {   // tets accumulate the upper triangle only
+    k_mirror_lower<<<nblk((int64_t)c->nb * 9), 256, 0, st>>>(c->blockptr.p, c->brow.p, c->bcol.p, c->bT.p, c->nb, 3, c->Avals.p);
+    LAUNCHED(c, 1);
+  }
+  if (slot >= 0) MFB_CUDA(cudaEventRecord(c->ev1[slot], st));
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
   c->rhs_valid = c->fuse_rhs != 0;
@@ -311,5 +329,17 @@ extern "C" int mfb_last_status(mfb_ctx* c, mfb_status* st) {
   MFB_CUDA(cudaStreamSynchronize(c->stream));
   st->polar_maxiter = (int64_t)h[0]; st->polar_hfail = (int64_t)h[1]; st->nonfinite = (int64_t)h[2];
   st->polar_iters = (int64_t)h[3]; st->eig_sweeps = (int64_t)h[4];
+  return MFB_OK;
+}
+
+// sum / count of the update-kernel durations recorded since the last call (option "profile" = 1); resets the ring
+extern "C" int mfb_kernel_time_ms(mfb_ctx* c, double* total_ms, int* count) {
+  CHECK_CTX(c);
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  double tot = 0.0;
+  for (int i = 0; i < c->ev_count; ++i) { float ms = 0.f; MFB_CUDA(cudaEventElapsedTime(&ms, c->ev0[i], c->ev1[i])); tot += ms; }
+  if (total_ms) *total_ms = tot;
+  if (count) *count = c->ev_count;
+  c->ev_count = 0;
   return MFB_OK;
 }

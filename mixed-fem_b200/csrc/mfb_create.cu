@@ -75,6 +75,15 @@ __global__ void k_inner(const int* __restrict__ blockptr, const int* __restrict_
   const int rank = b - blockptr[gi], nbr = blockptr[gi + 1] - blockptr[gi];
   inner[(int64_t)dd * blockptr[gi] + (int64_t)r * dim * nbr + dim * rank + c] = dim * bcol[b] + c;
 }
+// bT[b] = index of the transposed block (gj,gi) of block b = (gi,gj): binary search in block-row gj (columns ascending)
+__global__ void k_block_transpose(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol, int nb, int* bT) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  const int gi = brow[b], gj = bcol[b];
+  int lo = blockptr[gj], hi = blockptr[gj + 1] - 1;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (bcol[mid] < gi) lo = mid + 1; else hi = mid; }
+  bT[b] = lo;
+}
 __global__ void k_fill_int(int* p, int64_t n, int v) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -86,7 +95,8 @@ static int build_pattern(mfb_ctx* c) {
   const int npe = c->npe, dim = c->dim, nE = c->nE, nF = c->nF;
   const int64_t np = (int64_t)nE * npe * npe;
   cudaStream_t st = c->stream;
-  DBuf<long long> keys; DBuf<int> vals, head, bid, brow;
+  DBuf<long long> keys; DBuf<int> vals, head, bid;
+  DBuf<int>& brow = c->brow;
   int rc;
   if ((rc = keys.alloc(np)) || (rc = vals.alloc(np)) || (rc = head.alloc(np)) || (rc = bid.alloc(np))) return rc;
   k_pair_keys<<<nblk(np), 256, 0, st>>>(c->fidx.p, npe, nE, c->ld, nF, keys.p, vals.p);
@@ -104,7 +114,7 @@ static int build_pattern(mfb_ctx* c) {
   const int64_t nnz = (int64_t)nb * dim * dim;
   if (nnz > (int64_t)INT_MAX) { g_last_error = "nnz exceeds int32"; return MFB_ERR_TOO_LARGE; }
   c->nb = nb; c->nnz = nnz;
-  if ((rc = brow.alloc(nb > 0 ? nb : 1)) || (rc = c->bcol.alloc(nb > 0 ? nb : 1)) || (rc = c->diagblk.alloc(nF > 0 ? nF : 1)) ||
+  if ((rc = brow.alloc(nb > 0 ? nb : 1)) || (rc = c->bT.alloc(nb > 0 ? nb : 1)) || (rc = c->bcol.alloc(nb > 0 ? nb : 1)) || (rc = c->diagblk.alloc(nF > 0 ? nF : 1)) ||
       (rc = c->blockptr.alloc((size_t)nF + 1)) || (rc = c->outer.alloc((size_t)dim * nF + 1)) || (rc = c->inner.alloc(nnz > 0 ? nnz : 1)) ||
       (rc = c->smap.alloc((size_t)npe * npe * c->ld)) || (rc = c->sstride.alloc((size_t)npe * c->ld)))
     return rc;
@@ -118,6 +128,7 @@ static int build_pattern(mfb_ctx* c) {
                         thrust::counting_iterator<int>(nF + 1), thrust::device_ptr<int>(c->blockptr.p));
     k_fill_maps<<<nblk(nvalid), 256, 0, st>>>(vals.p, bid.p, brow.p, c->blockptr.p, nvalid, npe, dim, c->ld, c->smap.p, c->sstride.p);
     k_inner<<<nblk((int64_t)nb * dim * dim), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, nb, dim, c->inner.p);
+    k_block_transpose<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, nb, c->bT.p);
   } else {
     MFB_CUDA(cudaMemsetAsync(c->blockptr.p, 0, ((size_t)nF + 1) * sizeof(int), st));
   }
@@ -231,6 +242,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   const size_t N = c->N, M = c->M, NP = c->NP;
   TRY(c->R.alloc(M * ld)); TRY(c->s.alloc(N * ld)); TRY(c->la.alloc(N * ld)); TRY(c->ds.alloc(N * ld)); TRY(c->S.alloc(N * ld));
   TRY(c->dSdF.alloc(M * N * ld)); TRY(c->g.alloc(N * ld)); TRY(c->H.alloc(NP * ld)); TRY(c->Hinv.alloc(NP * ld));
+  if (dim == 3) TRY(c->Lfac.alloc(NP * ld));
   TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
   TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));

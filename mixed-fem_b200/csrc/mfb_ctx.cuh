@@ -52,9 +52,9 @@ struct mfb_ctx {
   mfb::DBuf<double> dphi, vol, vref;
   mfb::DBuf<mfb::MaterialDev> mats;
   // CSR structure (device)
-  mfb::DBuf<int> blockptr, bcol, diagblk, outer, inner;
+  mfb::DBuf<int> blockptr, brow, bcol, bT, diagblk, outer, inner;
   // state (device)
-  mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals;
+  mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals, Lfac;
   mfb::DBuf<int> iters;
   mfb::DBuf<unsigned long long> counters;
   // scratch
@@ -68,6 +68,10 @@ struct mfb_ctx {
   bool rhs_valid = false;     // rhs_/gl_ match the current S_, s_, g_, H_, dSdF_
   bool updated = false;
   int64_t launches = 0;
+  // optional CUDA-event timing of the update kernel alone (bench.py roofline): ring of event pairs on the stream
+  int profile = 0;
+  std::vector<cudaEvent_t> ev0, ev1;
+  int ev_count = 0;
 
   mfb::DevMesh mesh() const {
     mfb::DevMesh m;
@@ -80,7 +84,7 @@ struct mfb_ctx {
     mfb::DevState st;
     st.R = R.p; st.s = s.p; st.la = la.p; st.ds = ds.p; st.S = S.p; st.dSdF = dSdF.p; st.g = g.p; st.H = H.p;
     st.Hinv = Hinv.p; st.evals = evals.p; st.gl = gl.p; st.grad_la = grad_la.p; st.iters = iters.p;
-    st.grad_x = grad_x.p; st.rhs = rhs.p; st.Avals = Avals.p; st.counters = counters.p;
+    st.grad_x = grad_x.p; st.rhs = rhs.p; st.Avals = Avals.p; st.counters = counters.p; st.Lfac = Lfac.p;
     return st;
   }
   int grid() const { return (nE + 127) / 128; }

@@ -28,6 +28,7 @@ struct DevMesh {
 
 struct DevState {
   double *R, *s, *la, *ds, *S, *dSdF, *g, *H, *Hinv, *evals, *gl, *grad_la;
+  double* Lfac;          // [21][ld] scratch: Cholesky factor of the PSD-fixed Hessian (k_material_psd6 -> k_update_tet)
   int* iters;
   double *grad_x, *rhs, *Avals;
   unsigned long long* counters;   // [5]: maxiter, hfail, nonfinite, polar iters, eig sweeps
@@ -115,6 +116,60 @@ __device__ __forceinline__ void cholesky6(double* H) {
 // Aloc_ is never materialised: with Hfix = L L^T the 12x12 block is vol (B L)(B L)^T, formed 3x3 block by block and
 // sent to the CSR values with FP64 reductions (RED.ADD.F64).
 // -----------------------------------------------------------------------------------------------------------------
+// Phase A as its own kernel (k_material_psd6): g_ = h^2 dpsi, H = h^2 d2psi, psd_fix_invert, evals_, H_, Hinv_ and the
+// Cholesky factor of the fixed Hessian (scratch, read back by k_update_tet).  Splitting it off keeps each kernel's
+// SASS inside the SM instruction cache and lets this latency-bound Jacobi run at 3 blocks/SM instead of 2.
+static __global__ void __launch_bounds__(128, 3) k_material_psd6(DevMesh m, DevState st, double h2) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  double s[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) s[k] = st.s[k * ld + e];
+  const double vol = m.vol[e];
+  const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
+  double g[6], L[21], Hinv[21];
+  int sweeps;
+  material_grad_hess6(mat.model, mat.mu, mat.la, s, h2, g, L);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) st.g[k * ld + e] = g[k];
+  const double lmax = psd_fix_invert<6>(L, Hinv, 1e-8, &sweeps);
+  st.evals[e] = h2 * lmax;
+  const double iv = 1.0 / vol;
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) {
+      const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
+      st.H[symidx(i, j) * ld + e] = iv * w * L[symidx(i, j)];
+      st.Hinv[symidx(i, j) * ld + e] = Hinv[symidx(i, j)];
+    }
+  cholesky6(L);
+#pragma unroll
+  for (int i = 0; i < 21; ++i) st.Lfac[i * ld + e] = L[i];
+  const int bad = (!(lmax == lmax) || lmax > 1e300) ? ST_NONFINITE : 0;
+  count_status(st.counters, bad, 0, sweeps);
+}
+
+// Fill the strict lower triangle of the assembled matrix from the accumulated upper triangle: block (gi,gj), gi > gj,
+// is the transpose of block (gj,gi) (index bT[b]); inside diagonal blocks entry (r,c), r > c, copies (c,r).
+// One thread per scalar entry; A is symmetric by construction (Aloc = vol^2 Jloc^T K Jloc, mixed_stretch.cpp:212).
+static __global__ void k_mirror_lower(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol,
+                                      const int* __restrict__ bT, int nb, int dim, double* __restrict__ A) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int dd = dim * dim;
+  if (i >= (int64_t)nb * dd) return;
+  const int b = (int)(i / dd), rc = (int)(i % dd), r = rc / dim, c = rc % dim;
+  const int gi = brow[b], gj = bcol[b];
+  if (gi < gj || (gi == gj && r <= c)) return;
+  const int p0 = blockptr[gi], n0 = blockptr[gi + 1] - p0;
+  const int64_t dst = (int64_t)dd * p0 + (int64_t)r * dim * n0 + dim * (b - p0) + c;
+  const int bt = (gi == gj) ? b : bT[b];
+  const int p1 = blockptr[gj], n1 = blockptr[gj + 1] - p1;
+  const int64_t src = (int64_t)dd * p1 + (int64_t)c * dim * n1 + dim * (bt - p1) + r;
+  A[dst] = A[src];
+}
+
 template <bool FUSE_RHS, bool ASSEMBLE>
 __global__ void __launch_bounds__(128) k_update_tet(DevMesh m, DevState st, const double* __restrict__ x, double h2) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -122,33 +177,23 @@ __global__ void __launch_bounds__(128) k_update_tet(DevMesh m, DevState st, cons
   const int64_t ld = m.ld;
   int status = 0;
 
-  // ---- A
-  double s[6];
+  // ---- A (done by k_material_psd6): pick up s, g and the Cholesky factor of the fixed Hessian
+  double s[6], g[6], L[21];
 #pragma unroll
-  for (int k = 0; k < 6; ++k) s[k] = st.s[k * ld + e];
+  for (int k = 0; k < 6; ++k) { s[k] = st.s[k * ld + e]; g[k] = st.g[k * ld + e]; }
+#pragma unroll
+  for (int i = 0; i < 21; ++i) L[i] = st.Lfac[i * ld + e];
   const double vol = m.vol[e];
-  const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
-  double g[6], L[21];
-  int sweeps;
-  {
-    double Hinv[21];
-    material_grad_hess6(mat.model, mat.mu, mat.la, s, h2, g, L);
-    const double lmax = psd_fix_invert<6>(L, Hinv, 1e-8, &sweeps);
-    st.evals[e] = h2 * lmax;
-    const double iv = 1.0 / vol;
+  const int sweeps = 0;
+  // scatter indices are fetched up front so their latency hides behind the polar / dSdF work
+  int f[4], stride[4], sidx[16];
 #pragma unroll
-    for (int i = 0; i < 6; ++i)
+  for (int k = 0; k < 4; ++k) { f[k] = m.fidx[k * ld + e]; stride[k] = m.sstride[k * ld + e]; }
 #pragma unroll
-      for (int j = 0; j <= i; ++j) {
-        const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
-        st.H[symidx(i, j) * ld + e] = iv * w * L[symidx(i, j)];
-        st.Hinv[symidx(i, j) * ld + e] = Hinv[symidx(i, j)];
-      }
+  for (int q = 0; q < 16; ++q) sidx[q] = m.smap[q * ld + e];
+  double la6[6];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) st.g[k * ld + e] = g[k];
-    if (!(lmax == lmax) || lmax > 1e300) status |= ST_NONFINITE;
-  }
-  cholesky6(L);   // Hfix = L L^T from here on
+  for (int n = 0; n < 6; ++n) la6[n] = st.la[n * ld + e];
 
   // ---- B
   double dphi[9], F[9], R[9], Y[9];
@@ -222,13 +267,10 @@ __global__ void __launch_bounds__(128) k_update_tet(DevMesh m, DevState st, cons
   if (!(B[0][0] == B[0][0])) status |= ST_NONFINITE;
 
   // ---- D : vector contributions
-  int f[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) f[k] = m.fidx[k * ld + e];
   {
     double tl[6];
 #pragma unroll
-    for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * st.la[n * ld + e];
+    for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * la6[n];
     double gx0[3] = {0, 0, 0}, rh0[3] = {0, 0, 0};
 #pragma unroll
     for (int k = 0; k < 3; ++k)
@@ -272,21 +314,22 @@ __global__ void __launch_bounds__(128) k_update_tet(DevMesh m, DevState st, cons
     for (int r = 0; r < 3; ++r)
 #pragma unroll
       for (int n = 0; n < 6; ++n) B0[r][n] = -(B[r][n] + B[3 + r][n] + B[6 + r][n]);
-    int stride[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) stride[j] = m.sstride[j * ld + e];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
 #pragma unroll
       for (int k = j; k < 4; ++k) {
-        const int idx_jk = m.smap[(j * 4 + k) * ld + e];
+        const int idx_jk = sidx[j * 4 + k];
         if (idx_jk < 0) continue;             // either vertex pinned (then (k,j) is pinned too)
-        const int idx_kj = m.smap[(k * 4 + j) * ld + e];
+        // Only the upper triangle of the GLOBAL matrix is accumulated (block (gi,gj) with gi < gj, and c >= r inside
+        // diagonal blocks); k_mirror_lower fills the rest afterwards.  78 reductions per tet instead of 144.
+        const bool up = (j == k) || (f[j] < f[k]);
+        const int64_t base = up ? (int64_t)idx_jk : (int64_t)sidx[k * 4 + j];
+        const int64_t rs = up ? stride[j] : stride[k];
 #pragma unroll
         for (int r = 0; r < 3; ++r)
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
-            if (j == k && c < r) continue;    // diagonal block: lower half mirrored below
+            if (j == k && c < r) continue;
             double a = 0.0;
 #pragma unroll
             for (int n = 0; n < 6; ++n) {
@@ -294,8 +337,7 @@ __global__ void __launch_bounds__(128) k_update_tet(DevMesh m, DevState st, cons
               const double bk = (k == 0) ? B0[c][n] : B[3 * (k - 1) + c][n];
               a += bj * bk;
             }
-            red_add(&st.Avals[(int64_t)idx_jk + (int64_t)r * stride[j] + c], a);
-            if (j != k || r != c) red_add(&st.Avals[(int64_t)idx_kj + (int64_t)c * stride[k] + r], a);
+            red_add(&st.Avals[up ? base + r * rs + c : base + c * rs + r], a);
           }
       }
     }

@@ -219,12 +219,124 @@ MFB_HD int jacobi_eig(double* A, double* V) {
   return sweep;
 }
 
+// -----------------------------------------------------------------------------------------------------------------
+// Parallel-order Jacobi for N = 6: the 15 pivots of a sweep are visited as 5 rounds of 3 DISJOINT pairs (round-robin
+// tournament).  The three rotation parameter sets of a round depend only on their own 2x2 diagonal blocks, which the
+// other two rotations of the round never touch, so they are computed up front: three independent div/sqrt chains in
+// flight instead of one (the kernel is latency-bound, not FP64-throughput-bound).  Same arithmetic as a sequential
+// cyclic Jacobi with this pivot order.  Branch-free: a negligible pivot gets the identity rotation.
+// -----------------------------------------------------------------------------------------------------------------
+struct JRot { double t, s, c; };
+
+// Reciprocal and reciprocal square root without the IEEE slow paths: hardware seed (MUFU.RCP64H / MUFU.RSQ64H, ~20
+// bits) + two Newton steps, relative error a few ulp, for positive normal arguments only (what Jacobi feeds them).
+MFB_HD double fast_rcp(double x) {
+#if defined(__CUDA_ARCH__)
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  return fma(y, e, y);
+#else
+  return 1.0 / x;
+#endif
+}
+MFB_HD double fast_rsqrt(double x) {
+#if defined(__CUDA_ARCH__)
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double h = 0.5 * x;
+  double e = fma(-h * y, y, 0.5);
+  y = fma(y, e, y);
+  e = fma(-h * y, y, 0.5);
+  return fma(y, e, y);
+#else
+  return 1.0 / sqrt(x);
+#endif
+}
+
+// tan / sin / cos of the Jacobi angle for the pivot (p,q):  t = 2 apq sgn(d) / (|d| + sqrt(d^2 + 4 apq^2)), d = aqq - app
+MFB_HD JRot jacobi_params(double app, double aqq, double apq) {
+  const bool tiny = !(fabs(apq) > 1e-300) || fabs(apq) <= 1e-19 * (fabs(app) + fabs(aqq));
+  const double d = aqq - app;
+  const double q = d * d + 4.0 * apq * apq;
+  const double qs = tiny ? 1.0 : q;
+  const double root = qs * fast_rsqrt(qs);              // sqrt(q)
+  const double num = (d >= 0.0) ? 2.0 * apq : -2.0 * apq;
+  double t = num * fast_rcp(fabs(d) + root);
+  t = tiny ? 0.0 : t;
+  const double c = fast_rsqrt(fma(t, t, 1.0));
+  JRot r; r.t = t; r.c = c; r.s = t * c;
+  return r;
+}
+
+template <int N, int P, int Q>
+MFB_HD void jacobi_apply(double* A, double* V, const JRot r) {
+  const double apq = A[symidx(Q, P)];
+  A[symidx(P, P)] -= r.t * apq;
+  A[symidx(Q, Q)] += r.t * apq;
+  A[symidx(Q, P)] = 0.0;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    if (k != P && k != Q) {
+      const double akp = A[symidx(k, P)], akq = A[symidx(k, Q)];
+      A[symidx(k, P)] = fma(r.c, akp, -r.s * akq);
+      A[symidx(k, Q)] = fma(r.s, akp, r.c * akq);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    const double vkp = V[P * N + k], vkq = V[Q * N + k];
+    V[P * N + k] = fma(r.c, vkp, -r.s * vkq);
+    V[Q * N + k] = fma(r.s, vkp, r.c * vkq);
+  }
+}
+
+template <int P0, int Q0, int P1, int Q1, int P2, int Q2>
+MFB_HD void jacobi_round6(double* A, double* V) {
+  const JRot r0 = jacobi_params(A[symidx(P0, P0)], A[symidx(Q0, Q0)], A[symidx(Q0, P0)]);
+  const JRot r1 = jacobi_params(A[symidx(P1, P1)], A[symidx(Q1, Q1)], A[symidx(Q1, P1)]);
+  const JRot r2 = jacobi_params(A[symidx(P2, P2)], A[symidx(Q2, Q2)], A[symidx(Q2, P2)]);
+  jacobi_apply<6, P0, Q0>(A, V, r0);
+  jacobi_apply<6, P1, Q1>(A, V, r1);
+  jacobi_apply<6, P2, Q2>(A, V, r2);
+}
+
+MFB_HD int jacobi_eig6_parallel(double* A, double* V) {
+#pragma unroll
+  for (int i = 0; i < 36; ++i) V[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) V[i * 6 + i] = 1.0;
+  int sweep = 0;
+#pragma unroll 1
+  for (; sweep < 30; ++sweep) {
+    double off = 0.0, tot = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j <= i; ++j) {
+        const double a = A[symidx(i, j)];
+        if (i == j) tot += a * a; else off += a * a;
+      }
+    tot += 2.0 * off;
+    if (!(off > 1e-28 * tot)) break;
+    jacobi_round6<0, 5, 1, 4, 2, 3>(A, V);
+    jacobi_round6<0, 4, 3, 5, 1, 2>(A, V);
+    jacobi_round6<0, 3, 2, 4, 1, 5>(A, V);
+    jacobi_round6<0, 2, 1, 3, 4, 5>(A, V);
+    jacobi_round6<0, 1, 2, 5, 3, 4>(A, V);
+  }
+  return sweep;
+}
+
 // psd_fix_invert (src/utils/psd_fix.h:10-34): H <- V max(L,tol) V^T, Hinv <- V max(L,tol)^-1 V^T, returns lambda_max
 // (after clamping).  H, Hinv packed lower.  *sweeps gets the Jacobi sweep count.
 template <int N>
 MFB_HD double psd_fix_invert(double* H, double* Hinv, double tol, int* sweeps) {
   double V[N * N];
-  *sweeps = jacobi_eig<N>(H, V);
+  if constexpr (N == 6) *sweeps = jacobi_eig6_parallel(H, V);
+  else *sweeps = jacobi_eig<N>(H, V);
   double ev[N], iv[N];
   double lmax = -1e300;
 #pragma unroll

@@ -1,0 +1,140 @@
+// Host-side C++ mirror of mfem::MixedStretch<DIM> (src/variables/mixed_stretch.h:12-164) over the C ABI of
+// include/mfem_b200.h.  Same method names, argument meaning and ownership as the reference class so that it can be
+// registered with MixedVariableFactory under "mixed-stretch" (src/factories/variable_factory.cpp:13-19); see
+// INTEGRATION.md for the Eigen-typed adapter a maintainer would add inside the reference tree.
+//
+// Eigen is not required: vectors are std::vector<double> with the reference layouts (x[d*v+l], N*e+k).  The members
+// the reference's callers mutate in place (value(), delta(), lambda(): src/linesearch.h:120-125,
+// src/linear_solvers/linear_system.h:97,189) are host mirrors; they are pushed to the device before every call that
+// reads them and pulled back after every call that writes them, exactly the host<->device traffic a drop-in costs.
+// No CPU fallback: every method forwards to the CUDA library and throws std::runtime_error on failure.
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "../../include/mfem_b200.h"
+
+namespace mfb {
+
+struct MeshView {               // what MixedStretch pulls from mfem::Mesh (src/mesh/mesh.h:82-105,151-171)
+  int dim = 3;
+  int nV = 0, nE = 0;
+  const int32_t* T = nullptr;        // nE x (dim+1) row-major
+  const double* Vref = nullptr;      // nV x dim row-major
+  const int32_t* free_map = nullptr; // nV
+  const int32_t* mat_id = nullptr;   // nE or null
+  std::vector<mfb_material> materials;
+  int device = 0;
+};
+
+template <int DIM>
+class MixedStretch {
+ public:
+  static std::string name() { return "mixed-stretch"; }
+  static constexpr int N() { return DIM == 3 ? 6 : 3; }
+  static constexpr int M() { return DIM * DIM; }
+
+  explicit MixedStretch(const MeshView& mesh) {
+    if (mesh.dim != DIM) throw std::runtime_error("MixedStretch: mesh dimension mismatch");
+    mfb_mesh_desc d{};
+    d.elem_kind = DIM == 3 ? MFB_TET : MFB_TRI2D;
+    d.nV = mesh.nV; d.nE = mesh.nE; d.T = mesh.T; d.Vref = mesh.Vref; d.free_map = mesh.free_map; d.mat_id = mesh.mat_id;
+    d.n_mat = (int32_t)mesh.materials.size(); d.materials = mesh.materials.data(); d.device = mesh.device;
+    check(mfb_create(&ctx_, &d));
+    int32_t nF = 0; int64_t nnz = 0;
+    mfb_dims(ctx_, nullptr, nullptr, &nelem_, &nF, nullptr, &nnz);
+    nfree_ = nF; nnz_ = nnz;
+  }
+  ~MixedStretch() { mfb_destroy(ctx_); }
+  MixedStretch(const MixedStretch&) = delete;
+  MixedStretch& operator=(const MixedStretch&) = delete;
+
+  // --- Variable / MixedVariable virtuals -------------------------------------------------------------------
+  double energy(const std::vector<double>& x, const std::vector<double>& s) {
+    double e = 0; check(mfb_energy(ctx_, x.data(), s.data(), &e)); return e;
+  }
+  double constraint_value(const std::vector<double>& x, const std::vector<double>& s) {
+    push_state(); double e = 0; check(mfb_constraint_value(ctx_, x.data(), s.data(), &e)); return e;
+  }
+  void update(const std::vector<double>& x, double dt) {
+    push_state();
+    check(mfb_update(ctx_, x.data(), dt));
+    lhs_valid_ = false;
+  }
+  void reset() {
+    check(mfb_reset(ctx_, nullptr));
+    s_.resize((size_t)N() * nelem_); ds_.assign((size_t)N() * nelem_, 0.0); la_.assign((size_t)N() * nelem_, 0.0);
+    check(mfb_get(ctx_, MFB_F_S, s_.data()));
+    s_dev_ = s_; la_dev_ = la_;
+  }
+  void pre_solve() {}
+  void post_solve() { la_.assign(la_.size(), 0.0); }                       // mixed_stretch.cpp:340-343
+  std::vector<double> rhs() {
+    push_state();
+    std::vector<double> r((size_t)DIM * nfree_); check(mfb_rhs(ctx_, r.data())); return r;
+  }
+  std::vector<double> gradient() { return get(MFB_F_GRAD_X); }
+  std::vector<double> gradient_mixed() { return get(MFB_F_GRAD); }
+  std::vector<double> gradient_dual() { return get(MFB_F_GRAD_LA); }
+  void solve(const std::vector<double>& dx) {
+    push_state();
+    check(mfb_solve(ctx_, dx.data()));
+    check(mfb_get(ctx_, MFB_F_DS, ds_.data()));
+    check(mfb_get(ctx_, MFB_F_LA, la_.data()));
+    la_dev_ = la_;
+  }
+  std::vector<double>& delta() { return ds_; }
+  std::vector<double>& value() { return s_; }
+  std::vector<double>& lambda() { return la_; }
+  int size() const { return N() * nelem_; }
+  int size_dual() const { return N() * nelem_; }
+  std::vector<double> max_stresses() { return get(MFB_F_EVALS); }
+  void evaluate_constraint(const std::vector<double>& x, std::vector<double>& c) {
+    push_state(); c.resize((size_t)N() * nelem_); check(mfb_evaluate_constraint(ctx_, x.data(), c.data()));
+  }
+  // lhs(): RowMajor CSR (outer, inner, values) of A_ ; pattern pointers stay valid for the object's lifetime
+  struct Csr { const int32_t* outer; const int32_t* inner; const double* values; int64_t nnz; int32_t rows; };
+  Csr lhs() {
+    Csr m{};
+    check(mfb_csr_pattern(ctx_, &m.outer, &m.inner, &m.nnz, &m.rows));
+    if (!lhs_valid_) { lhs_vals_.resize((size_t)nnz_); check(mfb_lhs_values(ctx_, lhs_vals_.data())); lhs_valid_ = true; }
+    m.values = lhs_vals_.data();
+    return m;
+  }
+  void product_hessian(const std::vector<double>& x, std::vector<double>& out) { check(mfb_product(ctx_, 0, x.data(), out.data(), 0)); }
+  void product_hessian_inv(const std::vector<double>& x, std::vector<double>& out) { check(mfb_product(ctx_, 1, x.data(), out.data(), 0)); }
+  void product_jacobian_mixed(const std::vector<double>& x, std::vector<double>& out) { check(mfb_product(ctx_, 2, x.data(), out.data(), 0)); }
+  void product_jacobian_x(const std::vector<double>& x, std::vector<double>& out, bool transposed) {
+    check(mfb_product(ctx_, 3, x.data(), out.data(), transposed ? 1 : 0));
+  }
+  // hessian()/hessian_inv()/jacobian_mixed() block diagonals (mixed_stretch.cpp:368-404) as per-element N x N blocks
+  std::vector<double> hessian_blocks() { return get(MFB_F_HLOC); }
+  std::vector<double> hessian_inv_blocks() {
+    std::vector<double> h = get(MFB_F_HINV), v = get(MFB_F_VOLS);
+    for (int e = 0; e < nelem_; ++e) for (int k = 0; k < N() * N(); ++k) h[(size_t)e * N() * N() + k] *= v[e];
+    return h;
+  }
+  std::vector<double> dSdF_blocks() { return get(MFB_F_DSDF); }
+
+  mfb_ctx* ctx() { return ctx_; }
+  mfb_status status() { mfb_status st{}; check(mfb_last_status(ctx_, &st)); return st; }
+
+ private:
+  void check(int rc) const { if (rc != MFB_OK) throw std::runtime_error(std::string("mfem_b200: ") + mfb_last_error_string()); }
+  std::vector<double> get(int f) {
+    std::vector<double> v((size_t)mfb_field_size(ctx_, f)); check(mfb_get(ctx_, f, v.data())); return v;
+  }
+  // value()/lambda() are handed out by reference: upload them when they differ from what the device holds
+  void push_state() {
+    if (s_ != s_dev_) { check(mfb_set(ctx_, MFB_F_S, s_.data())); s_dev_ = s_; }
+    if (la_ != la_dev_) { check(mfb_set(ctx_, MFB_F_LA, la_.data())); la_dev_ = la_; }
+  }
+  mfb_ctx* ctx_ = nullptr;
+  int32_t nelem_ = 0, nfree_ = 0;
+  int64_t nnz_ = 0;
+  std::vector<double> s_, ds_, la_, s_dev_, la_dev_, lhs_vals_;
+  bool lhs_valid_ = false;
+};
+
+}  // namespace mfb

@@ -1,0 +1,134 @@
+"""CPU-side checks of the product: the C-ABI library builds for sm_100a, loads and exports every symbol declared in
+include/mfem_b200.h (no compute calls without a GPU), fails loudly without a device, and the per-element device math
+(mixed-fem_b200/csrc/mfb_math.cuh, compiled here as plain C++ by a TEST-ONLY harness) agrees with the oracle."""
+import ctypes as C
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+import scipy.linalg as sl
+
+import mixed_fem_b200 as mf
+from oracle import orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+dp = C.POINTER(C.c_double)
+
+
+def P(a):
+    return a.ctypes.data_as(dp)
+
+
+def test_header_symbols_are_exported(built):
+    hdr = open(os.path.join(ROOT, "include", "mfem_b200.h")).read()
+    declared = sorted(set(re.findall(r"\b(mfb_[a-z_0-9]+)\s*\(", hdr)))
+    assert len(declared) >= 30
+    L = C.CDLL(mf.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert sorted(mf.EXPORTS) == declared
+
+
+def test_library_is_sm100a_only(built):
+    out = subprocess.run(["cuobjdump", "-lelf", mf.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+def test_no_cpu_fallback_without_device(built):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from mixed_fem_b200 import meshgen
+    V, T = meshgen.kuhn_grid(2, 2, 2)
+    fm = meshgen.pinned_free_map(V)
+    with pytest.raises(mf.MfbError) as ei:
+        mf.MixedStretch(V, T, fm, [("ARAP", 1.0, 1.0)])
+    assert "no CUDA device" in str(ei.value) or "error -" in str(ei.value)
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "mixed-fem_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "liborc" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
+
+
+@pytest.fixture(scope="module")
+def harness():
+    bdir = os.path.join(ROOT, "tests", "harness", "_build")
+    os.makedirs(bdir, exist_ok=True)
+    so = os.path.join(bdir, "libmfbhost.so")
+    src = os.path.join(ROOT, "tests", "harness", "mfb_math_host.cpp")
+    hdr = os.path.join(ROOT, "mixed-fem_b200", "csrc", "mfb_math.cuh")
+    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        subprocess.run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src], check=True)
+    return C.CDLL(so)
+
+
+def test_device_materials_match_reference_generated_code(harness):
+    G = json.load(open(os.path.join(ROOT, "tests", "golden", "materials_golden.json")))
+    for c in G["cases"]:
+        n = c["n"]
+        s = np.array(c["s"]); g = np.zeros(n); H = np.zeros(n * n); e = np.zeros(1)
+        fn = harness.hh_material6 if n == 6 else harness.hh_material3
+        fn(orc.MODELS[c["model"]], C.c_double(c["mu"]), C.c_double(c["la"]), P(s), C.c_double(1.0), P(g), P(H), P(e))
+        He = np.array(c["hessian"])
+        Hl = np.tril(He) + np.tril(He, -1).T
+        assert abs(e[0] - c["energy"]) <= 1e-12 * max(1.0, abs(c["energy"]))
+        assert np.linalg.norm(g - c["gradient"]) <= 1e-12 * max(1e-300, np.linalg.norm(c["gradient"])) or np.linalg.norm(g) < 1e-9
+        assert np.linalg.norm(H.reshape(n, n).T - Hl) <= 1e-12 * np.linalg.norm(Hl)
+
+
+def test_device_psd_fix_matches_oracle(harness):
+    rng = np.random.default_rng(1)
+    for n, fn in ((6, harness.hh_psd6), (3, harness.hh_psd3)):
+        for _ in range(300):
+            A = rng.standard_normal((n, n)); A = A + A.T + rng.uniform(0, n) * np.eye(n)
+            Af, Ai, ev = orc.psd_fix_invert(A, 1e-8)
+            H = np.ascontiguousarray(A.T).reshape(-1).copy(); Hi = np.zeros(n * n); lm = np.zeros(1)
+            sw = fn(P(H), P(Hi), C.c_double(1e-8), P(lm))
+            assert 0 < sw < 12
+            assert np.linalg.norm(H.reshape(n, n).T - Af) <= 1e-11 * np.linalg.norm(Af)
+            assert np.linalg.norm(Hi.reshape(n, n).T - Ai) <= 1e-10 * np.linalg.norm(Ai)
+            assert abs(lm[0] - ev[-1]) <= 1e-12 * ev[-1]
+
+
+def test_device_polar3_contracted_dsdf_matches_explicit_9x9(harness):
+    rng = np.random.default_rng(2)
+    ip = C.POINTER(C.c_int)
+    for _ in range(300):
+        Q = sl.expm(np.cross(np.eye(3), rng.standard_normal(3) * 0.5))
+        F = Q @ (np.diag([1.2, .9, 1.05]) + 0.2 * rng.standard_normal((3, 3)))
+        R0 = sl.expm(np.cross(np.eye(3), rng.standard_normal(3) * 0.1)) @ sl.polar(F)[0]
+        Ro, so, Jo, ito, sto = orc.polar_svd3(R0, F)
+        R = np.ascontiguousarray(R0.T).reshape(-1).copy(); Fc = np.ascontiguousarray(F.T).reshape(-1)
+        s6 = np.zeros(6); Js = np.zeros(54); st = np.zeros(1, dtype=np.int32)
+        it = harness.hh_polar3(P(R), P(Fc), P(s6), P(Js), st.ctypes.data_as(ip))
+        assert it == ito and st[0] == sto
+        assert np.abs(R.reshape(3, 3).T - Ro).max() <= 1e-13
+        assert np.linalg.norm(s6 - so) <= 1e-13 * np.linalg.norm(so)
+        assert np.linalg.norm(Js.reshape(9, 6).T - Jo) <= 1e-12 * np.linalg.norm(Jo)
+
+
+def test_device_polar2_matches_dsvd_route(harness):
+    rng = np.random.default_rng(3)
+    for _ in range(300):
+        F = np.eye(2) + 0.4 * rng.standard_normal((2, 2))
+        Ro, so, Jo = orc.polar_svd2(F)
+        Fc = np.ascontiguousarray(F.T).reshape(-1); R = np.zeros(4); s3 = np.zeros(3); Js = np.zeros(12)
+        harness.hh_polar2(P(Fc), P(R), P(s3), P(Js))
+        assert np.abs(R.reshape(2, 2).T - Ro).max() <= 1e-13
+        assert np.linalg.norm(s3 - so) <= 1e-13 * np.linalg.norm(so)
+        assert np.linalg.norm(Js.reshape(4, 3).T - Jo) <= 1e-11 * max(np.linalg.norm(Jo), 1e-3)
+    # inside the |s1^2 - s0^2| < 1e-4 band the reference freezes dR (dsvd.cpp:163-167)
+    F = np.array([[1.00001, 0.0], [0.0, 1.0]])
+    Ro, so, Jo = orc.polar_svd2(F)
+    Fc = np.ascontiguousarray(F.T).reshape(-1); R = np.zeros(4); s3 = np.zeros(3); Js = np.zeros(12)
+    harness.hh_polar2(P(Fc), P(R), P(s3), P(Js))
+    assert np.linalg.norm(Js.reshape(4, 3).T - Jo) <= 1e-12

@@ -1,0 +1,197 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bars (BASELINE.json north_star): per-element fields and assembled CSR values <= 1e-10 relative, CSR pattern and
+element->nonzero map bit-exact, procrustes iteration counts identical."""
+import numpy as np
+import pytest
+
+from tests.common import DT, LA, MU, TOL, block_rel, mesh, pair, vec_rel
+
+pytestmark = pytest.mark.gpu
+
+MODELS3 = ["Stable-Neohookean", "Neohookean", "Corot", "FixedCorot", "ARAP", "Fung"]
+MODELS2 = ["Stable-Neohookean", "Corot", "FixedCorot", "ARAP"]
+
+
+def check_update(gpu, cpu, dim):
+    N, M = (6, 9) if dim == 3 else (3, 4)
+    errs = {
+        "R": block_rel(gpu.get("R"), cpu.get("R"), M),
+        "S": block_rel(gpu.get("S"), cpu.get("S"), N),
+        "dSdF": block_rel(gpu.get("dSdF"), cpu.get("dSdF"), M * N),
+        "g": block_rel(gpu.get("g"), cpu.get("g"), N),
+        "H": block_rel(gpu.get("H"), cpu.get("H"), N * N),
+        "Hinv": block_rel(gpu.get("Hinv"), cpu.get("Hinv"), N * N),
+        "Hloc": block_rel(gpu.get("Hloc"), cpu.get("Hloc"), N * N),
+        "evals": vec_rel(gpu.get("evals"), cpu.get("evals")),
+        "grad": vec_rel(gpu.get("grad"), cpu.get("grad")),
+        "grad_la": vec_rel(gpu.get("grad_la"), cpu.get("grad_la")),
+        "grad_x": vec_rel(gpu.get("grad_x"), cpu.get("grad_x")),
+        "A": vec_rel(gpu.lhs()[2], cpu.csr()[2]),
+        "rhs": vec_rel(gpu.rhs(), cpu.rhs()),
+        "gl": vec_rel(gpu.get("gl"), cpu.get("gl")),
+    }
+    bad = {k: v for k, v in errs.items() if not v <= TOL}
+    assert not bad, (bad, errs)
+    if dim == 3:
+        assert int((gpu.get("iters").astype(int) != cpu.iters()).sum()) == 0
+    st = gpu.status()
+    assert st["polar_maxiter"] == 0 and st["polar_hfail"] == 0 and st["nonfinite"] == 0
+    return errs
+
+
+@pytest.mark.parametrize("dim,n,shuffle,pin", [(3, (6, 4, 3), False, 0.01), (3, (5, 3, 3), True, 0.2), (3, (3, 3, 3), True, None),
+                                               (2, (9, 7, 0), False, 0.01), (2, (8, 8, 0), True, None)])
+def test_pattern_and_scatter_map_bit_exact(built, dim, n, shuffle, pin):
+    V, T, fm, h = mesh(dim, n, shuffle=shuffle, jitter=0.1 if shuffle else 0.0, pin=pin)
+    gpu, cpu, _ = pair(V, T, fm, [("ARAP", MU, LA)], h=h, state=False)
+    go, gi = gpu.csr_pattern()
+    co, ci, _ = cpu.csr(values=False)
+    assert go.dtype == np.int32 and gi.dtype == np.int32
+    assert np.array_equal(go, co) and np.array_equal(gi, ci)
+    gm, gs = gpu.scatter_map()
+    cm, cs = cpu.scatter_map()
+    assert np.array_equal(gm, cm)
+    assert np.array_equal(gs, cs)
+    gpu.close()
+
+
+@pytest.mark.parametrize("model", MODELS3)
+def test_update_parity_tets(built, model):
+    V, T, fm, h = mesh(3, (7, 4, 4))
+    gpu, cpu, st = pair(V, T, fm, [(model, MU, LA)], h=h)
+    for o in (gpu, cpu):
+        o.update(st["x"], DT)
+    check_update(gpu, cpu, 3)
+    gpu.close()
+
+
+@pytest.mark.parametrize("model", MODELS2)
+def test_update_parity_tri2d(built, model):
+    V, T, fm, h = mesh(2, (12, 9, 0))
+    gpu, cpu, st = pair(V, T, fm, [(model, MU, LA)], h=h)
+    for o in (gpu, cpu):
+        o.update(st["x"], DT)
+    check_update(gpu, cpu, 2)
+    gpu.close()
+
+
+def test_update_parity_irregular_mesh_heterogeneous_materials(built):
+    V, T, fm, h = mesh(3, (6, 5, 4), shuffle=True, jitter=0.15, pin=0.15)
+    mats = [("Stable-Neohookean", MU, LA), ("ARAP", 2 * MU, LA), ("FixedCorot", 0.5 * MU, 0.3 * LA)]
+    mat_id = (np.arange(T.shape[0]) % 3).astype(np.int32)
+    gpu, cpu, st = pair(V, T, fm, mats, mat_id=mat_id, h=h)
+    for o in (gpu, cpu):
+        o.update(st["x"], DT)
+    check_update(gpu, cpu, 3)
+    gpu.close()
+
+
+def test_indefinite_hessians_are_clamped_identically(built):
+    """compressed state: Stable-Neohookean Hessians with negative eigenvalues exercise the 1e-8 clamp (psd_fix.h:20-25)"""
+    V, T, fm, h = mesh(3, (5, 4, 3))
+    gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
+    rng = np.random.default_rng(5)
+    s = st["s"].reshape(-1, 6).copy()
+    s[:, :3] *= rng.uniform(0.45, 0.8, size=(s.shape[0], 1))
+    s[:, 3:] += rng.uniform(-0.3, 0.3, size=(s.shape[0], 3))
+    for o in (gpu, cpu):
+        o.set("s", s.reshape(-1))
+        o.update(st["x"], DT)
+    Hinv = cpu.get("Hinv").reshape(-1, 36)
+    assert (np.abs(Hinv).max(axis=1) > 1e6).any(), "test state does not reach the clamp"
+    check_update(gpu, cpu, 3)
+    gpu.close()
+
+
+def test_newton_like_sequence_rhs_solve_linesearch(built):
+    """update -> rhs -> solve -> (s += a ds) -> update ... : the call order of NewtonOptimizer::step
+    (newton_optimizer.cpp:36-101) with a random dx standing in for the linear solve."""
+    V, T, fm, h = mesh(3, (6, 4, 3))
+    gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
+    rng = np.random.default_rng(11)
+    x = st["x"].copy()
+    for it in range(3):
+        for o in (gpu, cpu):
+            o.update(x, DT)
+        assert vec_rel(gpu.rhs(), cpu.rhs()) <= TOL
+        dx = rng.standard_normal(3 * gpu.nfree) * 1e-3 * h
+        for o in (gpu, cpu):
+            o.solve(dx)
+        assert block_rel(gpu.get("la"), cpu.get("la"), 6) <= TOL
+        # ds = -Hinv (g - Sym la): where the PSD fix clamps an eigenvalue to 1e-8, |Hinv| ~ 1e8 amplifies the rounding of
+        # (g - Sym la) in BOTH implementations, so the bar per element is TOL relative plus eps-level input noise
+        # pushed through |Hinv|: |dds| <= TOL |ds| + 64 eps |Hinv|_F (|g| + |Sym la|)
+        dg, dc = gpu.get("ds").reshape(-1, 6), cpu.get("ds").reshape(-1, 6)
+        Hi = np.linalg.norm(cpu.get("Hinv").reshape(-1, 36), axis=1)
+        gn = np.linalg.norm(cpu.get("g").reshape(-1, 6), axis=1) + 2 * np.linalg.norm(cpu.get("la").reshape(-1, 6), axis=1)
+        bound = TOL * np.linalg.norm(dc, axis=1) + 64 * 2.2e-16 * Hi * gn
+        assert (np.linalg.norm(dg - dc, axis=1) <= bound).all()
+        s_trial = cpu.get("s") + 0.5 * cpu.get("ds")     # same trial point for both: this checks energy(), not ds
+        eg = gpu.energy(x, s_trial)
+        ec = cpu.energy(x, s_trial)
+        assert abs(eg - ec) <= TOL * abs(ec)
+        cg = gpu.constraint_value(x, gpu.get("s"))
+        cc = cpu.constraint_value(x, cpu.get("s"))
+        assert abs(cg - cc) <= 1e-9 * max(abs(cc), 1e-12)
+        s_new = cpu.get("s") + 0.5 * cpu.get("ds")
+        for o in (gpu, cpu):
+            o.set("s", s_new)
+        # move the free vertices a little
+        xf = x.reshape(-1, 3)
+        xf[fm >= 0] += dx.reshape(-1, 3)
+    check_update(gpu, cpu, 3)
+    gpu.close()
+
+
+@pytest.mark.parametrize("dim", [3, 2])
+def test_unfused_rhs_equals_fused(built, dim):
+    V, T, fm, h = mesh(dim, (6, 4, 3))
+    gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
+    gpu.update(st["x"], DT)
+    r1 = gpu.rhs()
+    gpu.set_option("fuse_rhs", 0)
+    gpu.update(st["x"], DT)
+    r2 = gpu.rhs()
+    cpu.update(st["x"], DT)
+    assert vec_rel(r2, r1) <= 1e-13 and vec_rel(r2, cpu.rhs()) <= TOL
+    gpu.close()
+
+
+@pytest.mark.parametrize("dim", [3, 2])
+def test_reset_evaluate_constraint_and_products(built, dim):
+    V, T, fm, h = mesh(dim, (5, 4, 3), shuffle=True, jitter=0.1, pin=0.2)
+    gpu, cpu, st = pair(V, T, fm, [("FixedCorot", MU, LA)], h=h, state=False)
+    N, M = (6, 9) if dim == 3 else (3, 4)
+    for f, w in (("R", M), ("S", N), ("s", N), ("dSdF", M * N)):
+        assert block_rel(gpu.get(f), cpu.get(f), w) <= TOL, f
+    for o in (gpu, cpu):
+        o.set("la", st["la"])
+        o.update(st["x"], DT)
+    assert vec_rel(gpu.evaluate_constraint(st["x"]), cpu.evaluate_constraint(st["x"])) <= TOL
+    rng = np.random.default_rng(2)
+    xe = rng.standard_normal(N * gpu.nE)
+    xv = rng.standard_normal(dim * gpu.nfree)
+    for which, xin, out0, tr in (("hessian", xe, xe * 0.5, False), ("hessian_inv", xe, xe * 0.1, False),
+                                 ("jacobian_mixed", xe, xe * 2, False), ("jacobian_x", xe, xv, True), ("jacobian_x", xv, xe, False)):
+        a = gpu.product(which, xin, out0, tr)
+        b = cpu.product(which, xin, out0, tr)
+        assert vec_rel(a, b) <= TOL, which
+    gpu.close()
+
+
+def test_post_solve_and_setters(built):
+    V, T, fm, h = mesh(3, (4, 3, 3))
+    gpu, cpu, st = pair(V, T, fm, [("ARAP", MU, LA)], h=h)
+    assert np.array_equal(gpu.get("la"), st["la"]) and np.array_equal(gpu.get("s"), st["s"]) and np.array_equal(gpu.get("R"), st["R"])
+    gpu.post_solve()
+    assert not gpu.get("la").any()
+    with pytest.raises(Exception):
+        gpu.set("H", np.zeros(36 * gpu.nE))
+    gpu.close()
+
+
+def test_unsupported_2d_material_is_an_error(built):
+    import mixed_fem_b200 as mf
+    V, T, fm, h = mesh(2, (4, 4, 0))
+    with pytest.raises(mf.MfbError):
+        mf.MixedStretch(V, T, fm, [("Neohookean", MU, LA)])

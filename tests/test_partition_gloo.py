@@ -1,0 +1,123 @@
+"""N>1 path on CPU: element partition + interface all-reduce over gloo (world_size 2 and 3), with the oracle standing in
+for each rank's local update.  Checks that the slab decomposition + interface sum reproduces the single-domain grad_x_,
+rhs_ and matvec, i.e. A = sum_r P_r^T A_r P_r."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import mixed_fem_b200  # noqa: F401
+    from mixed_fem_b200 import meshgen, partition
+    from oracle import orc
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    orc.lib().orc_set_num_threads(1)
+    V, T = meshgen.kuhn_grid(6, 3, 3)
+    fm = meshgen.pinned_free_map(V, ratio=0.01)
+    mu, la = meshgen.enu_to_lame(1e6, 0.45)
+    st = meshgen.synthetic_state(V, T, 1.0 / 6, mu)
+    loc, parts, shared = partition.make_local(V, T, fm, world, rank)
+    o = orc.OracleMixedStretch(loc.V, loc.T, loc.free_map, [("Stable-Neohookean", mu, la)])
+    o.reset()
+    R = st["R"].reshape(-1, 9)[loc.elems].reshape(-1)
+    o.set("R", R); o.set("s", loc.restrict_element_vector(st["s"], 6)); o.set("la", loc.restrict_element_vector(st["la"], 6))
+    o.update(loc.restrict_vertex_vector(st["x"], 3), 0.0333)
+
+    def allreduce(buf):
+        t = torch.from_numpy(buf)
+        dist.all_reduce(t)
+
+    gx = partition.interface_sum_numpy(loc, o.get("grad_x").copy(), 3, allreduce)
+    rhs = partition.interface_sum_numpy(loc, o.rhs().copy(), 3, allreduce)
+    # distributed matvec y = A p with the sub-assembled local matrices
+    nFg = int(fm.max()) + 1
+    p_glob = np.random.default_rng(1).standard_normal(3 * nFg)
+    p_loc = p_glob.reshape(-1, 3)[loc.free_l2g].reshape(-1)
+    outer, inner, vals = o.csr()
+    A = sp.csr_matrix((vals, inner, outer), shape=(outer.size - 1, outer.size - 1))
+    y = partition.interface_sum_numpy(loc, A @ p_loc, 3, allreduce)
+    q.put((rank, loc.free_l2g, gx, rhs, y, loc.elems.size, loc.if_local.size))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_slab_partition_interface_sum_matches_single_domain(world):
+    import torch.multiprocessing as mp
+    from mixed_fem_b200 import meshgen
+    from oracle import orc
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    V, T = meshgen.kuhn_grid(6, 3, 3)
+    fm = meshgen.pinned_free_map(V, ratio=0.01)
+    mu, la = meshgen.enu_to_lame(1e6, 0.45)
+    st = meshgen.synthetic_state(V, T, 1.0 / 6, mu)
+    o = orc.OracleMixedStretch(V, T, fm, [("Stable-Neohookean", mu, la)])
+    o.reset()
+    o.set("R", st["R"]); o.set("s", st["s"]); o.set("la", st["la"])
+    o.update(st["x"], 0.0333)
+    gx_g, rhs_g = o.get("grad_x").reshape(-1, 3), o.rhs().reshape(-1, 3)
+    outer, inner, vals = o.csr()
+    A = sp.csr_matrix((vals, inner, outer), shape=(outer.size - 1, outer.size - 1))
+    y_g = (A @ np.random.default_rng(1).standard_normal(A.shape[0])).reshape(-1, 3)
+    assert sum(r[5] for r in res) == T.shape[0]
+    assert all(r[6] > 0 for r in res)
+    covered = np.zeros(gx_g.shape[0], dtype=bool)
+    for rank, l2g, gx, rhs, y, _, _ in res:
+        covered[l2g] = True
+        for a, b in ((gx, gx_g), (rhs, rhs_g), (y, y_g)):
+            a = a.reshape(-1, 3)
+            # interior vertices of a slab hold the full value; interface vertices hold it after the sum
+            full = np.ones(l2g.size, dtype=bool)
+            assert np.linalg.norm(a[full] - b[l2g][full]) <= 1e-12 * np.linalg.norm(b)
+    assert covered.all()
+
+
+def test_partition_is_a_partition():
+    from mixed_fem_b200 import meshgen, partition
+    V, T = meshgen.kuhn_grid(8, 3, 2)
+    fm = meshgen.pinned_free_map(V)
+    for n in (1, 2, 4, 8):
+        parts = partition.partition_elements(V, T, n)
+        allel = np.concatenate(parts)
+        assert np.array_equal(np.sort(allel), np.arange(T.shape[0]))
+        assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+        shared = partition.shared_free_vertices(T, fm, parts)
+        assert (n == 1) == (shared.size == 0)
+        for r in range(n):
+            loc = partition.LocalProblem(V, T, fm, parts[r], shared)
+            assert np.array_equal(loc.vmap[loc.T], T[parts[r]])
+            free = loc.free_map[loc.free_map >= 0]
+            assert np.array_equal(free, np.arange(free.size))
+            assert np.all(np.diff(loc.free_l2g) > 0)
+            assert np.array_equal(shared[loc.if_pos], loc.free_l2g[loc.if_local])
