@@ -177,6 +177,8 @@ def gpu_arm(args):
     del V, T
     ms = mf.MixedStretch(Vl, Tl, fml, [("Stable-Neohookean", mu, la)], device=local_rank)
     ms.set_stream(torch.cuda.current_stream().cuda_stream)
+    if args.variant is not None:
+        ms.set_option("smem_b", args.variant)
     # state: R, s from the 'previous' positions (polar from identity on the device), lambda seeded
     ms.reset(xb)
     ms.set("la", lam)
@@ -335,6 +337,7 @@ def main():
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): 0 register B, 1 shared-memory B, 2 single fused launch")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":

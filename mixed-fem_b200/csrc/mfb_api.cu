@@ -1,5 +1,6 @@
 // C ABI entry points of the mixed-stretch path (see include/mfem_b200.h for the reference interface each replaces).
 #include "mfb_ctx.cuh"
+#include "mfb_kernels3.cuh"
 #include <cstring>
 
 using namespace mfb;
@@ -20,6 +21,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "fuse_rhs")) { c->fuse_rhs = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "assembly")) { c->assembly = value; return MFB_OK; }
   if (!strcmp(name, "profile")) { c->profile = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch
   g_last_error = "unknown option";
   return MFB_ERR_INVALID;
 }
@@ -117,16 +119,38 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     MFB_CUDA(cudaEventRecord(c->ev0[slot], st));
   }
   if (c->dim == 3) {
-    k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
-    LAUNCHED(c, 1);
-    if (c->fuse_rhs) k_update_tet<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
-    else k_update_tet<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+    if (c->smem_b == 2) {
+      static bool attr2_done = false;
+      if (!attr2_done) {
+        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
+        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
+        attr2_done = true;
+      }
+      if (c->fuse_rhs) k_update_tet_fused<true><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
+      else k_update_tet_fused<false><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
+    } else if (c->smem_b) {
+      k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
+      LAUNCHED(c, 1);
+      static bool attr_done = false;
+      if (!attr_done) {
+        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_sm<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
+        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_sm<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
+        attr_done = true;
+      }
+      if (c->fuse_rhs) k_update_tet_sm<true><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
+      else k_update_tet_sm<false><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
+    } else {
+      k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
+      LAUNCHED(c, 1);
+      if (c->fuse_rhs) k_update_tet<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+      else k_update_tet<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+    }
   } else {
     if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   }
   if (c->dim == 3 && c->nb > 0) {   // tets accumulate the upper triangle only
-    k_mirror_lower<<<nblk((int64_t)c->nb * 9), 256, 0, st>>>(c->blockptr.p, c->brow.p, c->bcol.p, c->bT.p, c->nb, 3, c->Avals.p);
+    k_mirror_lower<<<nblk((int64_t)c->n_mirror * 9), 256, 0, st>>>(c->mirror.p, c->n_mirror, 3, c->Avals.p);
     LAUNCHED(c, 1);
   }
   if (slot >= 0) MFB_CUDA(cudaEventRecord(c->ev1[slot], st));

@@ -84,6 +84,25 @@ __global__ void k_block_transpose(const int* __restrict__ blockptr, const int* _
   while (lo < hi) { const int mid = (lo + hi) >> 1; if (bcol[mid] < gi) lo = mid + 1; else hi = mid; }
   bT[b] = lo;
 }
+// mirror list: one int4 (dst0, dst row stride, src0, src row stride) per block of the lower triangle incl. diagonal
+// blocks, so that k_mirror_lower needs a single index load per copied entry
+__global__ void k_mirror_flags(const int* __restrict__ brow, const int* __restrict__ bcol, int nb, int* flag) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < nb) flag[b] = (brow[b] >= bcol[b]) ? 1 : 0;
+}
+__global__ void k_mirror_fill(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol,
+                              const int* __restrict__ bT, const int* __restrict__ flag, const int* __restrict__ pos, int nb, int dim, int4* list) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb || !flag[b]) return;
+  const int gi = brow[b], gj = bcol[b], dd = dim * dim;
+  const int p0 = blockptr[gi], n0 = blockptr[gi + 1] - p0;
+  const int p1 = blockptr[gj], n1 = blockptr[gj + 1] - p1;
+  const int bt = (gi == gj) ? b : bT[b];
+  int4 v;
+  v.x = dd * p0 + dim * (b - p0); v.y = dim * n0;
+  v.z = dd * p1 + dim * (bt - p1); v.w = dim * n1;
+  list[pos[b]] = v;
+}
 __global__ void k_fill_int(int* p, int64_t n, int v) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -129,6 +148,18 @@ static int build_pattern(mfb_ctx* c) {
     k_fill_maps<<<nblk(nvalid), 256, 0, st>>>(vals.p, bid.p, brow.p, c->blockptr.p, nvalid, npe, dim, c->ld, c->smap.p, c->sstride.p);
     k_inner<<<nblk((int64_t)nb * dim * dim), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, nb, dim, c->inner.p);
     k_block_transpose<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, nb, c->bT.p);
+    {
+      // head / bid are free again: reuse them as flag / position of the mirror list
+      k_mirror_flags<<<nblk(nb), 256, 0, st>>>(brow.p, c->bcol.p, nb, head.p);
+      thrust::exclusive_scan(pol, thrust::device_ptr<int>(head.p), thrust::device_ptr<int>(head.p + nb), thrust::device_ptr<int>(bid.p));
+      int last_pos = 0, last_flag = 0;
+      MFB_CUDA(cudaMemcpyAsync(&last_pos, bid.p + (nb - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+      MFB_CUDA(cudaMemcpyAsync(&last_flag, head.p + (nb - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+      MFB_CUDA(cudaStreamSynchronize(st));
+      c->n_mirror = last_pos + last_flag;
+      if ((rc = c->mirror.alloc(c->n_mirror > 0 ? c->n_mirror : 1))) return rc;
+      k_mirror_fill<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, c->bT.p, head.p, bid.p, nb, dim, c->mirror.p);
+    }
   } else {
     MFB_CUDA(cudaMemsetAsync(c->blockptr.p, 0, ((size_t)nF + 1) * sizeof(int), st));
   }

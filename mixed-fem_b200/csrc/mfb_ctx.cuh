@@ -47,12 +47,15 @@ struct mfb_ctx {
   // options
   int fuse_rhs = 1;
   int assembly = 0;
+  int smem_b = 1;       // k_update_tet_sm (B staged in shared memory) instead of the register-resident k_update_tet
   // mesh (device)
   mfb::DBuf<int> T, fidx, matid, smap, sstride;
   mfb::DBuf<double> dphi, vol, vref;
   mfb::DBuf<mfb::MaterialDev> mats;
   // CSR structure (device)
   mfb::DBuf<int> blockptr, brow, bcol, bT, diagblk, outer, inner;
+  mfb::DBuf<int4> mirror;     // (dst0, dst stride, src0, src stride) per lower-triangle block, see k_mirror_lower
+  int n_mirror = 0;
   // state (device)
   mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals, Lfac;
   mfb::DBuf<int> iters;

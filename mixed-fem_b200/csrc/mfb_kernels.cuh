@@ -119,9 +119,7 @@ __device__ __forceinline__ void cholesky6(double* H) {
 // Phase A as its own kernel (k_material_psd6): g_ = h^2 dpsi, H = h^2 d2psi, psd_fix_invert, evals_, H_, Hinv_ and the
 // Cholesky factor of the fixed Hessian (scratch, read back by k_update_tet).  Splitting it off keeps each kernel's
 // SASS inside the SM instruction cache and lets this latency-bound Jacobi run at 3 blocks/SM instead of 2.
-static __global__ void __launch_bounds__(128, 3) k_material_psd6(DevMesh m, DevState st, double h2) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= m.nE) return;
+__device__ __forceinline__ void material_psd6_body(const DevMesh& m, const DevState& st, int e, double h2) {
   const int64_t ld = m.ld;
   double s[6];
 #pragma unroll
@@ -150,28 +148,30 @@ static __global__ void __launch_bounds__(128, 3) k_material_psd6(DevMesh m, DevS
   const int bad = (!(lmax == lmax) || lmax > 1e300) ? ST_NONFINITE : 0;
   count_status(st.counters, bad, 0, sweeps);
 }
+static __global__ void __launch_bounds__(128, 3) k_material_psd6(DevMesh m, DevState st, double h2) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  material_psd6_body(m, st, e, h2);
+}
 
 // Fill the strict lower triangle of the assembled matrix from the accumulated upper triangle: block (gi,gj), gi > gj,
 // is the transpose of block (gj,gi) (index bT[b]); inside diagonal blocks entry (r,c), r > c, copies (c,r).
 // One thread per scalar entry; A is symmetric by construction (Aloc = vol^2 Jloc^T K Jloc, mixed_stretch.cpp:212).
-static __global__ void k_mirror_lower(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol,
-                                      const int* __restrict__ bT, int nb, int dim, double* __restrict__ A) {
+static __global__ void __launch_bounds__(256) k_mirror_lower(const int4* __restrict__ list, int n, int dim, double* __restrict__ A) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int dd = dim * dim;
-  if (i >= (int64_t)nb * dd) return;
-  const int b = (int)(i / dd), rc = (int)(i % dd), r = rc / dim, c = rc % dim;
-  const int gi = brow[b], gj = bcol[b];
-  if (gi < gj || (gi == gj && r <= c)) return;
-  const int p0 = blockptr[gi], n0 = blockptr[gi + 1] - p0;
-  const int64_t dst = (int64_t)dd * p0 + (int64_t)r * dim * n0 + dim * (b - p0) + c;
-  const int bt = (gi == gj) ? b : bT[b];
-  const int p1 = blockptr[gj], n1 = blockptr[gj + 1] - p1;
-  const int64_t src = (int64_t)dd * p1 + (int64_t)c * dim * n1 + dim * (bt - p1) + r;
-  A[dst] = A[src];
+  if (i >= (int64_t)n * dd) return;
+  const int q = (int)(i / dd), rc = (int)(i % dd), r = rc / dim, c = rc % dim;
+  const int4 v = __ldg(&list[q]);        // (dst0, dst row stride, src0, src row stride)
+  if (v.x == v.z && r <= c) return;      // diagonal block: only its strict lower half is copied
+  A[(int64_t)v.x + (int64_t)r * v.y + c] = A[(int64_t)v.z + (int64_t)c * v.w + r];
 }
 
+#ifndef MFB_K2_MINBLOCKS
+#define MFB_K2_MINBLOCKS 2
+#endif
 template <bool FUSE_RHS, bool ASSEMBLE>
-__global__ void __launch_bounds__(128) k_update_tet(DevMesh m, DevState st, const double* __restrict__ x, double h2) {
+__global__ void __launch_bounds__(128, MFB_K2_MINBLOCKS) k_update_tet(DevMesh m, DevState st, const double* __restrict__ x, double h2) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
