@@ -132,3 +132,20 @@ def test_device_polar2_matches_dsvd_route(harness):
     Fc = np.ascontiguousarray(F.T).reshape(-1); R = np.zeros(4); s3 = np.zeros(3); Js = np.zeros(12)
     harness.hh_polar2(P(Fc), P(R), P(s3), P(Js))
     assert np.linalg.norm(Js.reshape(4, 3).T - Jo) <= 1e-12
+
+
+def test_host_cpp_shim_compiles_and_links(built, tmp_path):
+    """mixed-fem_b200/host/mixed_stretch.hpp (the C++ mirror of mfem::MixedStretch<DIM>) instantiates for DIM = 2, 3
+    and links against the C-ABI library (not run here: no GPU)."""
+    src = tmp_path / "shim.cpp"
+    src.write_text('#include "mixed-fem_b200/host/mixed_stretch.hpp"\n'
+                   'template class mfb::MixedStretch<3>;\ntemplate class mfb::MixedStretch<2>;\n'
+                   'int main(int argc, char**) { if (argc > 99) { mfb::MeshView m; mfb::MixedStretch<3> v(m); v.reset(); '
+                   'std::vector<double> x; v.update(x, 0.1); auto r = v.rhs(); v.solve(r); return (int)v.lhs().nnz; } return 0; }\n')
+    exe = tmp_path / "shim"
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    libdir = os.path.join(ROOT, "mixed-fem_b200")
+    r = subprocess.run([cxx, "-std=c++17", "-I", ROOT, str(src), "-o", str(exe), "-L", libdir, "-lmfem_b200",
+                        "-Wl,-rpath," + libdir, "-L/usr/local/cuda/lib64", "-Wl,-rpath-link,/usr/local/cuda/lib64"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]

@@ -1,0 +1,121 @@
+"""GPU: y = (M + A) x and the PCG loop against scipy / the Eigen-CG restatement (oracle/pcg.py); full-size
+property checks of the assembled matrix at BASELINE sizes where the oracle would take too long."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from oracle import pcg as opcg
+from tests.common import DT, LA, MU, TOL, mesh, pair, vec_rel
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(dim, n, model="Stable-Neohookean"):
+    import torch
+    V, T, fm, h = mesh(dim, n)
+    gpu, cpu, st = pair(V, T, fm, [(model, MU, LA)], h=h)
+    for o in (gpu, cpu):
+        o.update(st["x"], DT)
+    outer, inner, vals = cpu.csr()
+    nrow = outer.size - 1
+    A = sp.csr_matrix((vals, inner, outer), shape=(nrow, nrow))
+    # mass-like term on the same pattern: PMP^T has the pattern of A; here rho*vol lumped on the diagonal
+    Mv = np.zeros_like(vals)
+    diagpos = np.array([outer[r] + np.searchsorted(inner[outer[r]:outer[r + 1]], r) for r in range(nrow)])
+    Mv[diagpos] = 1e-3 * (1.0 + 0.1 * np.arange(nrow) % 7)
+    M = sp.csr_matrix((Mv, inner, outer), shape=(nrow, nrow))
+    dev = torch.device("cuda")
+    return gpu, cpu, st, A, M, torch.as_tensor(Mv, device=dev), dev
+
+
+@pytest.mark.parametrize("dim,n", [(3, (7, 5, 4)), (2, (15, 11, 0))])
+def test_spmv_matches_scipy(built, dim, n):
+    import torch
+    gpu, cpu, st, A, M, Mv_d, dev = _setup(dim, n)
+    x = np.random.default_rng(0).standard_normal(A.shape[0])
+    xd = torch.as_tensor(x, device=dev)
+    yd = torch.zeros_like(xd)
+    gpu.spmv_dev(xd.data_ptr(), yd.data_ptr())
+    torch.cuda.synchronize()
+    assert vec_rel(yd.cpu().numpy(), A @ x) <= 1e-13
+    gpu.spmv_dev(xd.data_ptr(), yd.data_ptr(), M_ptr=Mv_d.data_ptr())
+    torch.cuda.synchronize()
+    assert vec_rel(yd.cpu().numpy(), (A + M) @ x) <= 1e-13
+    gpu.close()
+
+
+@pytest.mark.parametrize("dim,n,precond", [(3, (7, 5, 4), 1), (3, (7, 5, 4), 2), (3, (6, 4, 3), 0), (2, (15, 11, 0), 1), (2, (15, 11, 0), 2)])
+def test_pcg_matches_eigen_cg_recurrence(built, dim, n, precond):
+    import torch
+    gpu, cpu, st, A, M, Mv_d, dev = _setup(dim, n)
+    K = (A + M).tocsr()
+    b = cpu.rhs()
+    x0 = 1e-3 * np.random.default_rng(1).standard_normal(b.size)
+    tol, maxit = 1e-8, 500
+    xr, itr, err = opcg.conjugate_gradient(K, b, x0, opcg.make_precond(K, precond, dim), tol, maxit)
+    bd = torch.as_tensor(b, device=dev)
+    xd = torch.as_tensor(x0, device=dev).clone()
+    it, rr = gpu.pcg_dev(bd.data_ptr(), xd.data_ptr(), M_ptr=Mv_d.data_ptr(), precond=precond, tol=tol, max_iters=maxit)
+    torch.cuda.synchronize()
+    assert abs(it - itr) <= 1, (it, itr)             # rounding can move the stopping test by one iteration
+    assert rr <= tol and err <= tol
+    xg = xd.cpu().numpy()
+    assert np.linalg.norm(K @ xg - b) <= 2 * tol * np.linalg.norm(b)
+    assert vec_rel(xg, xr) <= 1e-6
+    # zero right-hand side: Eigen returns x = 0 with 0 iterations
+    zd = torch.zeros_like(bd)
+    it0, rr0 = gpu.pcg_dev(zd.data_ptr(), xd.data_ptr(), M_ptr=Mv_d.data_ptr(), precond=precond, tol=tol, max_iters=maxit)
+    torch.cuda.synchronize()
+    assert it0 == 0 and not xd.cpu().numpy().any()
+    gpu.close()
+
+
+def test_full_size_properties_C2(built):
+    """BASELINE config C2 (64x16x16x6 = 98 304 tets): full parity against the oracle, which finishes in seconds."""
+    from tests.test_gpu_parity import check_update
+    V, T, fm, h = mesh(3, (64, 16, 16))
+    gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
+    for o in (gpu, cpu):
+        o.update(st["x"], DT)
+    check_update(gpu, cpu, 3)
+    go, gi = gpu.csr_pattern()
+    co, ci, _ = cpu.csr(values=False)
+    assert np.array_equal(go, co) and np.array_equal(gi, ci)
+    gpu.close()
+
+
+def test_full_size_properties_C3_1M(built):
+    """BASELINE config C3 size (55^3 x 6 = 998 250 tets, ARAP): size-independent properties, no oracle.
+    symmetry x.(Ay) = y.(Ax); idempotence (a second update at the same x takes zero polar iterations and
+    reproduces every field); product_jacobian_x(gl) reproduces rhs; counters clean."""
+    import torch
+    from mixed_fem_b200 import meshgen
+    import mixed_fem_b200 as mf
+    V, T = meshgen.kuhn_grid(55, 55, 55)
+    fm = meshgen.pinned_free_map(V)
+    gpu = mf.MixedStretch(V, T, fm, [("ARAP", MU, LA)])
+    xa = meshgen.deformed_positions(V, 1.0 / 55, scale=1.0)
+    xb = meshgen.deformed_positions(V, 1.0 / 55, scale=0.5)
+    gpu.reset(xb)
+    rng = np.random.default_rng(3)
+    gpu.set("la", rng.uniform(-1, 1, size=6 * T.shape[0]) * MU * 1e-3)
+    gpu.update(xa, DT)
+    st1 = gpu.status()
+    assert st1["polar_maxiter"] == 0 and st1["polar_hfail"] == 0 and st1["nonfinite"] == 0 and st1["polar_iters"] > 0
+    rhs1, S1, A1 = gpu.rhs(), gpu.get("S"), gpu.lhs()[2]
+    dev = torch.device("cuda")
+    n = rhs1.size
+    x = torch.as_tensor(rng.standard_normal(n), device=dev); y = torch.as_tensor(rng.standard_normal(n), device=dev)
+    Ax = torch.empty_like(x); Ay = torch.empty_like(x)
+    gpu.spmv_dev(x.data_ptr(), Ax.data_ptr()); gpu.spmv_dev(y.data_ptr(), Ay.data_ptr())
+    torch.cuda.synchronize()
+    a, b = float(x @ Ay), float(y @ Ax)
+    assert abs(a - b) <= 1e-11 * max(abs(a), abs(b))
+    assert float(x @ Ax) > 0                                  # PSD-fixed blocks => positive on a generic vector
+    out = gpu.product("jacobian_x", gpu.get("gl"), np.zeros(n), transposed=True)   # out -= PJW dSdF gl  == rhs
+    assert vec_rel(out, rhs1) <= 1e-12
+    gpu.update(xa, DT)                                         # idempotence
+    st2 = gpu.status()
+    assert st2["polar_iters"] == 0
+    assert vec_rel(gpu.get("S"), S1) <= 1e-14 and vec_rel(gpu.rhs(), rhs1) <= 1e-12 and vec_rel(gpu.lhs()[2], A1) <= 1e-12
+    gpu.close()
