@@ -179,6 +179,8 @@ def gpu_arm(args):
     ms.set_stream(torch.cuda.current_stream().cuda_stream)
     if args.variant is not None:
         ms.set_option("smem_b", args.variant)
+    if args.asm is not None:
+        ms.set_option("asm_mode", args.asm)
     # state: R, s from the 'previous' positions (polar from identity on the device), lambda seeded
     ms.reset(xb)
     ms.set("la", lam)
@@ -292,6 +294,7 @@ def gpu_arm(args):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                          "kernel_share_of_step": k_ms / per_step if per_step > 0 else None},
             "polar_iters_per_tet": st0["polar_iters"] / max(nE_l, 1), "eig_sweeps_per_tet": st0["eig_sweeps"] / max(nE_l, 1),
+            "psd_slow_fraction": st0.get("psd_slow", 0) / max(nE_l, 1),
         }
         if world == 1 and not args.no_cpu:
             cx, cy, cz = args.cpu_grid
@@ -337,7 +340,8 @@ def main():
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): 0 register B, 1 shared-memory B, 2 single fused launch")
+    ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): 3 v4 (default), 0 register B, 1 shared-memory B, 2 single fused launch")
+    ap.add_argument("--asm", type=int, default=None, help="v4 assembly mode (library option asm_mode): 1 bulk reductions into block-CSR (default), 0 FP64 RED into scalar CSR")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":

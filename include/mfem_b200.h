@@ -56,6 +56,7 @@ typedef struct {          /* SURVEY.md §5 failure detection: counts since the l
   int64_t nonfinite;      /* elements that produced a non-finite value */
   int64_t polar_iters;    /* total procrustes iterations */
   int64_t eig_sweeps;     /* total Jacobi sweeps */
+  int64_t psd_slow;       /* elements whose Hessian needed the eigen-decomposition (fast Cholesky path refused) */
 } mfb_status;
 
 /* per-element / per-dof fields for mfb_get / mfb_set / mfb_field_dev (names = members of MixedStretch, mixed_stretch.h:141-162) */

@@ -48,7 +48,7 @@ class _MeshDesc(C.Structure):
 
 class _Status(C.Structure):
     _fields_ = [("polar_maxiter", C.c_int64), ("polar_hfail", C.c_int64), ("nonfinite", C.c_int64),
-                ("polar_iters", C.c_int64), ("eig_sweeps", C.c_int64)]
+                ("polar_iters", C.c_int64), ("eig_sweeps", C.c_int64), ("psd_slow", C.c_int64)]
 
 
 def build(force=False, verbose=False):

@@ -21,7 +21,8 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "fuse_rhs")) { c->fuse_rhs = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "assembly")) { c->assembly = value; return MFB_OK; }
   if (!strcmp(name, "profile")) { c->profile = value ? 1 : 0; return MFB_OK; }
-  if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch
+  if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch, 3 v4 (default)
+  if (!strcmp(name, "asm_mode")) { c->asm_mode = value ? 1 : 0; return MFB_OK; }   // v4: 1 bulk reductions into block-CSR, 0 RED into scalar CSR
   g_last_error = "unknown option";
   return MFB_ERR_INVALID;
 }
@@ -102,10 +103,17 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   if (!x_dev) return MFB_ERR_INVALID;
   cudaStream_t st = c->stream;
   const double h2 = dt * dt;
+  const bool v4 = c->dim == 3 && c->smem_b == 3;
+  const bool bulk = v4 && c->asm_mode == 1;
   MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
-  MFB_CUDA(cudaMemsetAsync(c->grad_x.p, 0, (size_t)c->dim * c->nF * 8, st));
-  if (c->fuse_rhs) MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, (size_t)c->dim * c->nF * 8, st));
-  if (c->nnz) MFB_CUDA(cudaMemsetAsync(c->Avals.p, 0, (size_t)c->nnz * 8, st));
+  if (bulk) {
+    MFB_CUDA(cudaMemsetAsync(c->gxrh.p, 0, (size_t)6 * c->nF * 8, st));
+    if (c->nbu) MFB_CUDA(cudaMemsetAsync(c->Ablk.p, 0, (size_t)c->nbu * 9 * 8, st));
+  } else {
+    MFB_CUDA(cudaMemsetAsync(c->grad_x.p, 0, (size_t)c->dim * c->nF * 8, st));
+    if (c->fuse_rhs) MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, (size_t)c->dim * c->nF * 8, st));
+    if (c->nnz) MFB_CUDA(cudaMemsetAsync(c->Avals.p, 0, (size_t)c->nnz * 8, st));
+  }
   const DevMesh m = c->mesh();
   const DevState s = c->state();
   int slot = -1;
@@ -118,7 +126,34 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     }
     MFB_CUDA(cudaEventRecord(c->ev0[slot], st));
   }
-  if (c->dim == 3) {
+  if (v4) {
+    const DevAsm a = c->asmdesc();
+    const int smem = kV4SmemB + kV4SmemStage;
+    static bool attr4_done = false;
+    if (!attr4_done) {
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      attr4_done = true;
+    }
+    const int tail_grid = c->grid() < 148 * 3 ? c->grid() : 148 * 3;
+    if (bulk) {
+      if (c->fuse_rhs) { k_update_tet_v4<true, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      else { k_update_tet_v4<false, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      if (c->nb > 0) k_finalize_csr<<<nblk((int64_t)c->nb * 9), 256, 0, st>>>(c->finlist.p, c->nb, c->Ablk.p, c->Avals.p);
+      if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
+      LAUNCHED(c, 3);
+    } else {
+      if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      else { k_update_tet_v4<false, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      LAUNCHED(c, 1);
+    }
+  } else if (c->dim == 3) {
     if (c->smem_b == 2) {
       static bool attr2_done = false;
       if (!attr2_done) {
@@ -149,7 +184,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   }
-  if (c->dim == 3 && c->nb > 0) {   // tets accumulate the upper triangle only
+  if (c->dim == 3 && c->nb > 0 && !bulk) {   // RED variants accumulate the upper triangle only
     k_mirror_lower<<<nblk((int64_t)c->n_mirror * 9), 256, 0, st>>>(c->mirror.p, c->n_mirror, 3, c->Avals.p);
     LAUNCHED(c, 1);
   }
@@ -348,11 +383,11 @@ extern "C" int mfb_product(mfb_ctx* c, int which, const double* x, double* out, 
 extern "C" int mfb_last_status(mfb_ctx* c, mfb_status* st) {
   CHECK_CTX(c);
   if (!st) return MFB_ERR_INVALID;
-  unsigned long long h[5];
+  unsigned long long h[6];
   MFB_CUDA(cudaMemcpyAsync(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
   MFB_CUDA(cudaStreamSynchronize(c->stream));
   st->polar_maxiter = (int64_t)h[0]; st->polar_hfail = (int64_t)h[1]; st->nonfinite = (int64_t)h[2];
-  st->polar_iters = (int64_t)h[3]; st->eig_sweeps = (int64_t)h[4];
+  st->polar_iters = (int64_t)h[3]; st->eig_sweeps = (int64_t)h[4]; st->psd_slow = (int64_t)h[5];
   return MFB_OK;
 }
 

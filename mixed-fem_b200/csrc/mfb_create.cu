@@ -103,6 +103,36 @@ __global__ void k_mirror_fill(const int* __restrict__ blockptr, const int* __res
   v.z = dd * p1 + dim * (bt - p1); v.w = dim * n1;
   list[pos[b]] = v;
 }
+// ---- v4 assembly structures (tets): block-CSR copy of the upper triangle
+__global__ void k_upper_flags(const int* __restrict__ brow, const int* __restrict__ bcol, int nb, int* flag) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < nb) flag[b] = (brow[b] <= bcol[b]) ? 1 : 0;
+}
+// finalize list: (dst0, dst row length, src0 in Ablk, transposed) per block; ub = exclusive scan of the upper flags
+__global__ void k_finlist_fill(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol,
+                               const int* __restrict__ bT, const int* __restrict__ ub, int nb, int dim, int4* list) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  const int gi = brow[b], gj = bcol[b], dd = dim * dim;
+  const int p0 = blockptr[gi], n0 = blockptr[gi + 1] - p0;
+  int4 v;
+  v.x = dd * p0 + dim * (b - p0); v.y = dim * n0;
+  v.z = 9 * ((gi <= gj) ? ub[b] : ub[bT[b]]); v.w = (gi <= gj) ? 0 : 1;
+  list[b] = v;
+}
+// bmap[pair10(j,k)][e] = 2 * upper block + transposed for the local pairs j <= k (sorted pair list: vals = e*16+j*4+k)
+__global__ void k_fill_bmap(const int* __restrict__ vals, const int* __restrict__ bid, const int* __restrict__ brow, const int* __restrict__ bcol,
+                            const int* __restrict__ bT, const int* __restrict__ ub, int64_t n, int64_t ld, int* bmap) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int p = vals[i];
+  const int e = p / 16, j = (p % 16) / 4, k = p % 4;
+  if (j > k) return;
+  const int b = bid[i] - 1;
+  const int gi = brow[b], gj = bcol[b];
+  const int code = (gi <= gj) ? 2 * ub[b] : 2 * ub[bT[b]] + 1;
+  bmap[(int64_t)(j * 4 - j * (j - 1) / 2 + (k - j)) * ld + e] = code;
+}
 __global__ void k_fill_int(int* p, int64_t n, int v) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -159,6 +189,26 @@ static int build_pattern(mfb_ctx* c) {
       c->n_mirror = last_pos + last_flag;
       if ((rc = c->mirror.alloc(c->n_mirror > 0 ? c->n_mirror : 1))) return rc;
       k_mirror_fill<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, c->bT.p, head.p, bid.p, nb, dim, c->mirror.p);
+    }
+    if (dim == 3) {
+      // v4 assembly: number the upper-triangle blocks, element->block map, finalize list
+      DBuf<int> uflag, ub;
+      if ((rc = uflag.alloc(nb)) || (rc = ub.alloc(nb)) || (rc = c->bmap.alloc((size_t)10 * c->ld)) || (rc = c->finlist.alloc(nb))) return rc;
+      k_upper_flags<<<nblk(nb), 256, 0, st>>>(brow.p, c->bcol.p, nb, uflag.p);
+      thrust::exclusive_scan(pol, thrust::device_ptr<int>(uflag.p), thrust::device_ptr<int>(uflag.p + nb), thrust::device_ptr<int>(ub.p));
+      int last_pos = 0, last_flag = 0;
+      MFB_CUDA(cudaMemcpyAsync(&last_pos, ub.p + (nb - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+      MFB_CUDA(cudaMemcpyAsync(&last_flag, uflag.p + (nb - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+      MFB_CUDA(cudaStreamSynchronize(st));
+      c->nbu = last_pos + last_flag;
+      k_fill_int<<<nblk((int64_t)10 * c->ld), 256, 0, st>>>(c->bmap.p, (int64_t)10 * c->ld, -1);
+      // vals / bid still hold the sorted pair list (head was reused above, bid was overwritten by the mirror scan: redo it)
+      k_heads<<<nblk(nvalid), 256, 0, st>>>(keys.p, nvalid, head.p);
+      thrust::inclusive_scan(pol, thrust::device_ptr<int>(head.p), thrust::device_ptr<int>(head.p + nvalid), thrust::device_ptr<int>(bid.p));
+      k_fill_bmap<<<nblk(nvalid), 256, 0, st>>>(vals.p, bid.p, brow.p, c->bcol.p, c->bT.p, ub.p, nvalid, c->ld, c->bmap.p);
+      k_finlist_fill<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, c->bT.p, ub.p, nb, dim, c->finlist.p);
+      MFB_CUDA(cudaStreamSynchronize(st));
+      if ((int64_t)c->nbu * 9 > (int64_t)INT_MAX) { g_last_error = "block-CSR exceeds int32"; return MFB_ERR_TOO_LARGE; }
     }
   } else {
     MFB_CUDA(cudaMemsetAsync(c->blockptr.p, 0, ((size_t)nF + 1) * sizeof(int), st));
@@ -276,6 +326,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   if (dim == 3) TRY(c->Lfac.alloc(NP * ld));
   TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
+  if (dim == 3) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 16)); TRY(c->gxrh.alloc((size_t)6 * nF + 8)); TRY(c->slow_list.alloc((size_t)nE + 1)); }
   TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));
   TRY(c->partials.alloc((size_t)c->grid() + 64)); TRY(c->scal.alloc(16));
   TRY(c->soa_tmp.alloc(N * ld)); TRY(c->soa_tmp2.alloc(N * ld));

@@ -6,6 +6,7 @@
 #include <vector>
 #include "../../include/mfem_b200.h"
 #include "mfb_kernels2.cuh"
+#include "mfb_kernels4.cuh"
 
 namespace mfb {
 
@@ -47,7 +48,8 @@ struct mfb_ctx {
   // options
   int fuse_rhs = 1;
   int assembly = 0;
-  int smem_b = 1;       // k_update_tet_sm (B staged in shared memory) instead of the register-resident k_update_tet
+  int smem_b = 3;       // update kernel variant: 3 = k_update_tet_v4 (default), 0/1/2 = the earlier register / shared-memory / fused variants
+  int asm_mode = 1;     // v4 assembly: 1 = warp-cooperative coalesced RED into the block-CSR upper triangle, 0 = FP64 RED into the scalar CSR
   // mesh (device)
   mfb::DBuf<int> T, fidx, matid, smap, sstride;
   mfb::DBuf<double> dphi, vol, vref;
@@ -56,6 +58,11 @@ struct mfb_ctx {
   mfb::DBuf<int> blockptr, brow, bcol, bT, diagblk, outer, inner;
   mfb::DBuf<int4> mirror;     // (dst0, dst stride, src0, src stride) per lower-triangle block, see k_mirror_lower
   int n_mirror = 0;
+  // v4 assembly: block-CSR upper triangle (9 doubles per block), element->block map, finalize list, interleaved vectors
+  mfb::DBuf<double> Ablk, gxrh;
+  mfb::DBuf<int> bmap, slow_list;
+  mfb::DBuf<int4> finlist;
+  int nbu = 0;
   // state (device)
   mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals, Lfac;
   mfb::DBuf<int> iters;
@@ -89,6 +96,11 @@ struct mfb_ctx {
     st.Hinv = Hinv.p; st.evals = evals.p; st.gl = gl.p; st.grad_la = grad_la.p; st.iters = iters.p;
     st.grad_x = grad_x.p; st.rhs = rhs.p; st.Avals = Avals.p; st.counters = counters.p; st.Lfac = Lfac.p;
     return st;
+  }
+  mfb::DevAsm asmdesc() const {
+    mfb::DevAsm a;
+    a.Ablk = Ablk.p; a.gxrh = gxrh.p; a.bmap = bmap.p; a.slow_list = slow_list.p;
+    return a;
   }
   int grid() const { return (nE + 127) / 128; }
 };

@@ -1,0 +1,412 @@
+// k_update_tet_v4 : MixedStretch<3>::update() (mixed_stretch.cpp:158-243, 345-366) in ONE launch per step, plus a
+// tail launch over the (normally empty or short) list of elements whose Hessian needs the eigen-decomposition.
+//
+// Per element (one thread):
+//   1. F = Ds Dm^-1, warm-started Newton polar, R_, S_, grad_la_, dSdF_; B = (Js Jloc)^T goes to SHARED memory
+//      (54 doubles per thread, thread-private column of a [54][128] tile: conflict-free, no barriers);
+//   2. g = h^2 dpsi, H = h^2 d2psi, psd_fix_invert (psd_fix.h:10-34):
+//        fast path  (psd_fast6): H has no eigenvalue below tol => fixed H is H, H^-1 by Cholesky, lambda_max by
+//                   tridiagonal Newton.  ~1/6 of the FP64 work of the eigen-decomposition;
+//        otherwise  the element index is appended to a list and the thread goes idle; k_update_tet_v4_tail redoes
+//                   step 1 from the already converged R_ (no iteration), runs the Jacobi eigen-solver and continues;
+//   3. u = Hfix (S - s) + g, gl_; vertex vectors grad_x_ / rhs_; B <- sqrt(vol) B L in place (Hfix = L L^T);
+//      3x3 blocks B_j B_k^T of the element matrix for the 10 local vertex pairs j <= k.
+//
+// Assembly modes (template ASM):
+//   0  one scattered FP64 RED per value into the reference-layout CSR values, upper triangle only, then k_mirror_lower;
+//   1  WARP-COOPERATIVE reductions into an internal block-CSR copy of the upper triangle (9 contiguous doubles per
+//      block): each lane parks its 3x3 block in a per-warp shared-memory buffer, then the 32 lanes re-read the 288
+//      values so that 9 ADJACENT lanes cover the 9 CONTIGUOUS doubles of one block and issue 9 RED instructions for the
+//      32 blocks.  Same number of RED instructions, but the LSU coalesces each into a few 72-byte runs.  Vertex
+//      vectors the same way (6 contiguous doubles per vertex: grad_x | rhs interleaved).  k_finalize_csr then writes
+//      every value of the reference-layout scalar CSR (both triangles), k_deinterleave_vec the two vertex vectors.
+//      Measured on B200 (tools/ubench_red.cu, L2-resident targets): scattered RED.F64 179 G values/s; lane groups of
+//      8 contiguous doubles 500 G values/s; 80-byte cp.reduce.async.bulk 57 G ops/s, but each bulk operation is a
+//      warp-uniform instruction that ptxas serialises over the lanes (ELECT/R2UR/UBLKRED loop, ~9 issue slots per
+//      operation) - tried, 6.3 ms per 10M tets against 7.3 ms for mode 0, replaced by this mode.
+#pragma once
+#include "mfb_kernels.cuh"
+
+namespace mfb {
+
+constexpr int kV4Threads = 128;
+constexpr int kV4Warps = kV4Threads / 32;
+constexpr int kV4StageDoubles = 32 * 9;                 // per warp: one 3x3 block per lane
+constexpr int kV4SmemB = 54 * kV4Threads * (int)sizeof(double);
+constexpr int kV4SmemStage = kV4Warps * (kV4StageDoubles * (int)sizeof(double) + 32 * (int)sizeof(int));
+
+struct DevAsm {
+  double* Ablk;          // [nbu][9]  block-CSR copy of the upper triangle (row-major 3x3)
+  double* gxrh;          // [nF][6]   grad_x | rhs interleaved
+  const int* bmap;       // [10][ld]  2*upper_block + transposed, -1 if a vertex of the pair is pinned
+  int* slow_list;        // [nE]
+};
+
+// Every lane holds NV values for NV contiguous doubles at base[target .. target+NV) (target < 0: nothing to add).
+// The warp re-distributes them through its shared-memory buffer so that each RED instruction covers runs of NV
+// contiguous doubles with NV adjacent lanes.  All 32 lanes must call this.
+template <int NV>
+__device__ __forceinline__ void coop_red(double* __restrict__ base, const double* v, int target, double* sW, int* sC, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < NV; ++i) sW[lane * NV + i] = v[i];
+  sC[lane] = target;
+  __syncwarp();
+#pragma unroll
+  for (int it = 0; it < NV; ++it) {
+    const int q = it * 32 + lane;
+    const int b = q / NV, i = q - b * NV;
+    const int t = sC[b];
+    const double val = sW[q];
+    if (t >= 0) red_add(base + (int64_t)t + i, val);
+  }
+}
+
+// local pair (j,k), j <= k  ->  0..9
+__device__ __forceinline__ constexpr int pair10(int j, int k) { return j * 4 - j * (j - 1) / 2 + (k - j); }
+
+// `inrange` false: the lane has no element (grid padding); it runs on a clamped element index so that the warp stays
+// convergent for the cooperative reductions, and stores nothing.
+template <bool FUSE_RHS, bool TAIL, int ASM>
+__device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevState& st, const DevAsm& as, const double* __restrict__ x,
+                                                   int e, bool inrange, double h2, double* sB, double* sW, int* sC) {
+  double* myB = sB + threadIdx.x;                       // element (row, n) at myB[(6*row + n) * kV4Threads]
+  const int lane = threadIdx.x & 31;
+  const int64_t ld = m.ld;
+  int status = 0, iters = 0, sweeps = 0;
+
+  // ---- 1 : deformation gradient, polar, stretch, dS/dF
+  double dphi[9], F[9], R[9], Y[9];
+  tet_F(m, e, x, dphi, F);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R[i] = st.R[i * ld + e];
+  double s[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) s[k] = st.s[k * ld + e];
+  const double vol = m.vol[e];
+  if (!TAIL) {
+    iters = procrustes3(R, F, Y, 1e-6, 100, &status);
+    if (inrange) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) st.R[i * ld + e] = R[i];
+      st.iters[e] = iters;
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) Y[3 * c + r] = R[r] * F[c] + R[3 + r] * F[3 + c] + R[6 + r] * F[6 + c];
+  }
+  double u[6];    // S - s first, then Hfix (S - s) + g
+  {
+    double S[6];
+    stretch6(R, F, S);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) u[k] = S[k] - s[k];
+    if (!TAIL) {
+      if (inrange) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) st.S[k * ld + e] = S[k];
+      }
+      // evaluate_constraint's own polar from a copy of R_ (mixed_stretch.cpp:358-360): zero iterations when the
+      // iterated Y = R F^T already passes the tolerance test, which it does unless the iteration cap was hit
+      const double q0 = Y[5] - Y[7], q1 = Y[6] - Y[2], q2 = Y[1] - Y[3];
+      if (!(sqrt(q0 * q0 + q1 * q1 + q2 * q2) < 1e-6)) {
+        M33 Rc, Fc;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { Rc.a[i] = R[i]; Fc.a[i] = F[i]; }
+        const V6 r = polar_from_copy_slow(Rc, Fc);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) S[k] = r.a[k];
+      }
+      if (inrange) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) st.grad_la[k * ld + e] = ((k < 3) ? 1.0 : 2.0) * (S[k] - s[k]) * vol;
+      }
+    }
+  }
+  {
+    double Hinv3[6];
+    if (!procrustes_hinv(Y, Hinv3)) status |= ST_POLAR_HFAIL;
+#pragma unroll
+    for (int n = 0; n < 6; ++n) {
+      double col[9];
+      dsdf3_column(n, R, F, Hinv3, col);
+      if (!TAIL && inrange) {
+        const double sy = (n < 3) ? 1.0 : 2.0;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) st.dSdF[(n * 9 + k) * ld + e] = sy * col[k];
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+          myB[(6 * (3 * k + r) + n) * kV4Threads] = dphi[3 * k] * col[r] + dphi[3 * k + 1] * col[3 + r] + dphi[3 * k + 2] * col[6 + r];
+      if (n == 0 && !(col[0] == col[0])) status |= ST_NONFINITE;
+    }
+  }
+
+  // ---- 2 : material gradient / Hessian, PSD fix, inverse, lambda_max
+  bool live = inrange;       // false: this lane stores / adds nothing from here on
+  double L[21];
+  {
+    const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
+    double g[6], Hinv[21], lmax;
+    material_grad_hess6(mat.model, mat.mu, mat.la, s, h2, g, L);     // L holds H for now
+    if (!TAIL) {
+      double Hm[21];
+#pragma unroll
+      for (int i = 0; i < 21; ++i) Hm[i] = L[i];
+      int nit;
+      const bool ok = psd_fast6(Hm, L, Hinv, 1e-8, 1e-5, &lmax, &nit);
+      // elements that need the eigen-decomposition: append to the list (one atomic per warp); the lane goes idle
+      const bool fail = inrange && !ok;
+      const unsigned failm = __ballot_sync(0xffffffffu, fail);
+      if (failm) {
+        const int leader = __ffs(failm) - 1;
+        unsigned long long base = 0;
+        if (lane == leader) base = atomicAdd(&st.counters[5], (unsigned long long)__popc(failm));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (fail) as.slow_list[base + __popc(failm & ((1u << lane) - 1u))] = e;
+        live = live && ok;
+        if (__ballot_sync(0xffffffffu, live) == 0u) {     // nothing left to do for this warp
+          count_status(st.counters, inrange ? status : 0, inrange ? iters : 0, 0);
+          return;
+        }
+      }
+      if (live) {
+        const double iv = 1.0 / vol;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) {
+            const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
+            st.H[symidx(i, j) * ld + e] = iv * w * Hm[symidx(i, j)];
+          }
+      }
+    } else {
+      lmax = psd_fix_invert<6>(L, Hinv, 1e-8, &sweeps);
+      if (live) {
+        const double iv = 1.0 / vol;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) {
+            const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
+            st.H[symidx(i, j) * ld + e] = iv * w * L[symidx(i, j)];
+          }
+      }
+      cholesky6(L);
+    }
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < 21; ++i) st.Hinv[i * ld + e] = Hinv[i];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) st.g[k * ld + e] = g[k];
+      st.evals[e] = h2 * lmax;
+      if (!(lmax == lmax) || lmax > 1e300) status |= ST_NONFINITE;
+    }
+    // u = Hfix (S - s) + g = L (L^T (S - s)) + g ; gl = Syminv u   (rhs(): gl = vol H_ Sym (S-s) + Syminv g)
+    if (FUSE_RHS) {
+      double t[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) { double a = 0.0;
+#pragma unroll
+        for (int i = j; i < 6; ++i) a += L[symidx(i, j)] * u[i];
+        t[j] = a; }
+#pragma unroll
+      for (int i = 0; i < 6; ++i) { double a = g[i];
+#pragma unroll
+        for (int j = 0; j <= i; ++j) a += L[symidx(i, j)] * t[j];
+        u[i] = a; if (live) st.gl[i * ld + e] = ((i < 3) ? 1.0 : 0.5) * a; }
+    }
+  }
+
+  // ---- 3 : vertex vectors, and B <- sqrt(vol) B L in place (one row at a time through registers)
+  int f[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) f[k] = live ? m.fidx[k * ld + e] : -1;
+  double tl[6];
+#pragma unroll
+  for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * st.la[n * ld + e];
+  const double sv = sqrt(vol);
+  double B0[3][6];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int n = 0; n < 6; ++n) B0[r][n] = 0.0;
+  {
+    double v0[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      double vv[6];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        double row[6];
+#pragma unroll
+        for (int n = 0; n < 6; ++n) row[n] = myB[(6 * (3 * k + r) + n) * kV4Threads];
+        double a = 0.0, b = 0.0;
+#pragma unroll
+        for (int n = 0; n < 6; ++n) { a += row[n] * tl[n]; if (FUSE_RHS) b += row[n] * u[n]; }
+        a *= vol; b *= -vol;
+        v0[r] -= a; v0[3 + r] -= b;
+        vv[r] = a; vv[3 + r] = b;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          double t = 0.0;
+#pragma unroll
+          for (int i = j; i < 6; ++i) t += row[i] * L[symidx(i, j)];
+          t *= sv;
+          myB[(6 * (3 * k + r) + j) * kV4Threads] = t;
+          B0[r][j] -= t;
+        }
+      }
+      if (ASM == 0) {
+        if (f[k + 1] >= 0) {
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            red_add(&st.grad_x[3 * (int64_t)f[k + 1] + r], vv[r]);
+            if (FUSE_RHS) red_add(&st.rhs[3 * (int64_t)f[k + 1] + r], vv[3 + r]);
+          }
+        }
+      } else {
+        coop_red<6>(as.gxrh, vv, f[k + 1] >= 0 ? 6 * f[k + 1] : -1, sW, sC, lane);
+      }
+    }
+    if (ASM == 0) {
+      if (f[0] >= 0) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          red_add(&st.grad_x[3 * (int64_t)f[0] + r], v0[r]);
+          if (FUSE_RHS) red_add(&st.rhs[3 * (int64_t)f[0] + r], v0[3 + r]);
+        }
+      }
+    } else {
+      coop_red<6>(as.gxrh, v0, f[0] >= 0 ? 6 * f[0] : -1, sW, sC, lane);
+    }
+  }
+
+  // ---- 3 : matrix blocks for the local pairs j <= k
+  if (ASM == 0) {
+    int stride[4], sidx[16];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) stride[k] = m.sstride[k * ld + e];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) sidx[q] = live ? m.smap[q * ld + e] : -1;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      double bj[3][6];
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int n = 0; n < 6; ++n) bj[r][n] = (j == 0) ? B0[r][n] : myB[(6 * (3 * (j - 1) + r) + n) * kV4Threads];
+#pragma unroll
+      for (int k = j; k < 4; ++k) {
+        const int idx_jk = sidx[j * 4 + k];
+        if (idx_jk < 0) continue;
+        const bool up = (j == k) || (f[j] < f[k]);
+        const int64_t base = up ? (int64_t)idx_jk : (int64_t)sidx[k * 4 + j];
+        const int64_t rs = up ? stride[j] : stride[k];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          double bk[6];
+#pragma unroll
+          for (int n = 0; n < 6; ++n) bk[n] = (k == j) ? bj[c][n] : myB[(6 * (3 * (k - 1) + c) + n) * kV4Threads];
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            if (j == k && c < r) continue;
+            double a = 0.0;
+#pragma unroll
+            for (int n = 0; n < 6; ++n) a += bj[r][n] * bk[n];
+            red_add(&st.Avals[up ? base + r * rs + c : base + c * rs + r], a);
+          }
+        }
+      }
+    }
+  } else {
+    int code[10];
+#pragma unroll
+    for (int q = 0; q < 10; ++q) code[q] = live ? as.bmap[q * ld + e] : -1;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      double bj[3][6];
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int n = 0; n < 6; ++n) bj[r][n] = (j == 0) ? B0[r][n] : myB[(6 * (3 * (j - 1) + r) + n) * kV4Threads];
+#pragma unroll
+      for (int k = j; k < 4; ++k) {
+        const int cd = code[pair10(j, k)];
+        double a[3][3];      // a[r][c] = (B_j B_k^T)(r,c)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          double bk[6];
+#pragma unroll
+          for (int n = 0; n < 6; ++n) bk[n] = (k == j) ? bj[c][n] : myB[(6 * (3 * (k - 1) + c) + n) * kV4Threads];
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            if (j == k && r < c) { a[r][c] = a[c][r]; continue; }
+            double t = 0.0;
+#pragma unroll
+            for (int n = 0; n < 6; ++n) t += bj[r][n] * bk[n];
+            a[r][c] = t;
+          }
+        }
+        const bool tr = (cd & 1) != 0;     // the stored block is (g_k, g_j): park the transpose
+        double v[9];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int c = 0; c < 3; ++c) v[3 * r + c] = tr ? a[c][r] : a[r][c];
+        coop_red<9>(as.Ablk, v, cd >= 0 ? 9 * (cd >> 1) : -1, sW, sC, lane);
+      }
+    }
+  }
+  count_status(st.counters, inrange ? status : 0, inrange ? iters : 0, inrange ? sweeps : 0);
+}
+
+template <bool FUSE_RHS, int ASM>
+__global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
+  extern __shared__ __align__(128) double smem4[];
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int w = threadIdx.x >> 5;
+  double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;
+  int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;
+  if ((e & ~31) >= m.nE) return;                       // whole warp out of range
+  update_tet_v4_body<FUSE_RHS, false, ASM>(m, st, as, x, e < m.nE ? e : m.nE - 1, e < m.nE, h2, smem4, sW, sC);
+}
+
+// elements the fast PSD path refused: grid-stride over the list the main kernel built (count in counters[5])
+template <bool FUSE_RHS, int ASM>
+__global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4_tail(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
+  extern __shared__ __align__(128) double smem4[];
+  const int w = threadIdx.x >> 5;
+  double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;
+  int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;
+  const long long n = (long long)st.counters[5];
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += (long long)gridDim.x * blockDim.x) {
+    const long long i = i0 + (threadIdx.x & 31);
+    const bool in = i < n;
+    update_tet_v4_body<FUSE_RHS, true, ASM>(m, st, as, x, as.slow_list[in ? i : n - 1], in, h2, smem4, sW, sC);
+  }
+}
+
+// Block-CSR upper triangle -> reference-layout scalar CSR values, every entry written once.
+// list[b] = (dst0, dst row length, src0, transposed) for each of the nb blocks; one thread per scalar entry.
+static __global__ void __launch_bounds__(256) k_finalize_csr(const int4* __restrict__ list, int nb, const double* __restrict__ Ablk, double* __restrict__ A) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nb * 9) return;
+  const int b = (int)(i / 9), rc = (int)(i % 9), r = rc / 3, c = rc % 3;
+  const int4 v = __ldg(&list[b]);
+  A[(int64_t)v.x + (int64_t)r * v.y + c] = Ablk[(int64_t)v.z + (v.w ? c * 3 + r : r * 3 + c)];   // v.z = 9 * upper block
+}
+
+static __global__ void __launch_bounds__(256) k_deinterleave_vec(const double* __restrict__ gxrh, int nF, double* __restrict__ gx, double* __restrict__ rh, int with_rhs) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nF * 3) return;
+  const int64_t v = i / 3; const int r = (int)(i % 3);
+  gx[i] = gxrh[6 * v + r];
+  if (with_rhs) rh[i] = gxrh[6 * v + 3 + r];
+}
+
+}  // namespace mfb

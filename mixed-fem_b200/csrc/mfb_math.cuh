@@ -362,6 +362,152 @@ MFB_HD double psd_fix_invert(double* H, double* Hinv, double tol, int* sweeps) {
 }
 
 // -----------------------------------------------------------------------------------------------------------------
+// psd_fix_invert FAST PATH for N = 6 (src/utils/psd_fix.h:10-34 when no eigenvalue is clamped).
+// If every eigenvalue of H exceeds tol, the reference's  V max(L,tol) V^T  is H itself and  V max(L,tol)^-1 V^T  is
+// H^-1: no eigenvectors are needed.  What is still needed from the spectrum is lambda_max (evals_).
+//   1. Cholesky H = L L^T with relative pivot check (pivot > relpiv * H_jj, i.e. kappa(H) <~ 1/relpiv);
+//   2. H^-1 = L^-T L^-1; certificate lambda_min(H) >= 1/trace(H^-1) > tol;
+//   3. lambda_max: Householder tridiagonalisation (no Q), then Newton on the characteristic polynomial from the
+//      upper bound |H|_F: monotone from above for a real-rooted polynomial, quadratic for a separated top eigenvalue.
+// Returns false (caller must take the Jacobi path) when a pivot fails, the certificate fails, Newton has not
+// converged in 24 iterations (a cluster of eigenvalues at the top: the root is then ill-conditioned as a
+// polynomial root although not as an eigenvalue) or anything is non-finite.
+// Outputs: L (packed lower Cholesky factor), Hinv (packed lower), *lmax.
+// -----------------------------------------------------------------------------------------------------------------
+template <int K>
+MFB_HD void tridiag6_step(double* A) {
+  // Householder step K of the reduction of the packed-lower symmetric 6x6 A to tridiagonal form
+  constexpr int m = 5 - K;             // length of the column below the diagonal
+  double v[m];
+#pragma unroll
+  for (int i = 0; i < m; ++i) v[i] = A[symidx(K + 1 + i, K)];
+  double sig = 0.0;
+#pragma unroll
+  for (int i = 1; i < m; ++i) sig = fma(v[i], v[i], sig);
+  const bool act = sig > 0.0;
+  const double q = act ? fma(v[0], v[0], sig) : 1.0;
+  const double nrm = q * fast_rsqrt(q);
+  const double alpha = act ? (v[0] >= 0.0 ? -nrm : nrm) : v[0];
+  v[0] -= alpha;                        // 0 when inactive
+  const double vv = act ? fma(v[0], v[0], sig) : 1.0;
+  const double beta = act ? 2.0 * fast_rcp(vv) : 0.0;
+  double p[m];
+#pragma unroll
+  for (int i = 0; i < m; ++i) {
+    double a = 0.0;
+#pragma unroll
+    for (int j = 0; j < m; ++j) a = fma(A[symidx(K + 1 + i, K + 1 + j)], v[j], a);
+    p[i] = beta * a;
+  }
+  double kk = 0.0;
+#pragma unroll
+  for (int i = 0; i < m; ++i) kk = fma(v[i], p[i], kk);
+  kk *= 0.5 * beta;
+#pragma unroll
+  for (int i = 0; i < m; ++i) p[i] = fma(-kk, v[i], p[i]);       // w
+#pragma unroll
+  for (int i = 0; i < m; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) A[symidx(K + 1 + i, K + 1 + j)] -= fma(v[i], p[j], p[i] * v[j]);
+  A[symidx(K + 1, K)] = alpha;
+}
+
+MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, double relpiv, double* lmax, int* newton_iters) {
+  bool ok = true;
+  // ---- 1. Cholesky with pivot check; id[j] = 1 / L_jj
+  double id[6];
+#pragma unroll
+  for (int i = 0; i < 21; ++i) L[i] = H[i];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    double d = L[symidx(j, j)];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d = fma(-L[symidx(j, k)], L[symidx(j, k)], d);
+    const bool good = d > relpiv * H[symidx(j, j)] && d > 0.0;    // false on NaN as well
+    ok = ok && good;
+    d = good ? d : 1.0;
+    const double r = fast_rsqrt(d);
+    id[j] = r;
+    L[symidx(j, j)] = d * r;
+#pragma unroll
+    for (int i = j + 1; i < 6; ++i) {
+      double a = L[symidx(i, j)];
+#pragma unroll
+      for (int k = 0; k < j; ++k) a = fma(-L[symidx(i, k)], L[symidx(j, k)], a);
+      L[symidx(i, j)] = a * r;
+    }
+  }
+  // ---- 2. inverse: W = L^-1 (lower), Hinv = W^T W
+  double W[21];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    W[symidx(j, j)] = id[j];
+#pragma unroll
+    for (int i = j + 1; i < 6; ++i) {
+      double a = 0.0;
+#pragma unroll
+      for (int k = j; k < i; ++k) a = fma(L[symidx(i, k)], W[symidx(k, j)], a);
+      W[symidx(i, j)] = -a * id[i];
+    }
+  }
+  double tr = 0.0;
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) {
+      double a = 0.0;
+#pragma unroll
+      for (int k = i; k < 6; ++k) a = fma(W[symidx(k, i)], W[symidx(k, j)], a);
+      Hinv[symidx(i, j)] = a;
+      if (i == j) tr += a;
+    }
+  ok = ok && (tr * tol < 1.0);          // lambda_min >= 1 / trace(H^-1) > tol ; false on NaN
+  // ---- 3. lambda_max
+  double A[21];
+  double fro = 0.0;
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) { const double a = H[symidx(i, j)]; fro = fma((i == j) ? a : 2.0 * a, a, fro); }
+  const bool fok = fro > 0.0 && fro < 1e300;
+  ok = ok && fok;
+  fro = fok ? fro : 1.0;
+  const double inrm = fast_rsqrt(fro), nrm = fro * inrm;
+#pragma unroll
+  for (int i = 0; i < 21; ++i) A[i] = H[i] * inrm;
+  tridiag6_step<0>(A); tridiag6_step<1>(A); tridiag6_step<2>(A); tridiag6_step<3>(A);
+  double d[6], e2[5];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) d[i] = A[symidx(i, i)];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) e2[i] = A[symidx(i + 1, i)] * A[symidx(i + 1, i)];
+  double sg = 1.0;                      // |A|_F = 1 >= lambda_max(A)
+  bool conv = false;
+  int it = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  for (; it < 24; ++it) {
+    double p0 = 1.0, p1 = sg - d[0], q0 = 0.0, q1 = 1.0;
+#pragma unroll
+    for (int i = 1; i < 6; ++i) {
+      const double t = sg - d[i];
+      const double p2 = fma(t, p1, -e2[i - 1] * p0);
+      const double q2 = fma(t, q1, fma(-e2[i - 1], q0, p1));
+      p0 = p1; p1 = p2; q0 = q1; q1 = q2;
+    }
+    if (!(q1 > 0.0)) break;             // cannot happen above the largest root; guards NaN
+    const double dl = p1 * fast_rcp(q1);
+    sg -= dl;
+    if (!(dl > 1e-15)) { conv = dl > -1e-12; ++it; break; }   // a large negative step = noise near a clustered root
+  }
+  ok = ok && conv;
+  *lmax = sg * nrm;
+  *newton_iters = it;
+  return ok;
+}
+
+// -----------------------------------------------------------------------------------------------------------------
 // 3x3 helpers.  Matrices are column-major double[9]: m[3*c + r].
 // -----------------------------------------------------------------------------------------------------------------
 MFB_HD void cross3(const double* a, const double* b, double* o) {

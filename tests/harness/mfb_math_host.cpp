@@ -23,6 +23,14 @@ int hh_psd6(double* Hfull, double* Hinvfull, double tol, double* lmax) {
   for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) { Hfull[j * 6 + i] = H[symidx(i, j)]; Hinvfull[j * 6 + i] = Hi[symidx(i, j)]; }
   return sw;
 }
+// fast path: returns 1 when accepted; Hfull in (col-major), outputs Lfull (lower, col-major), Hinvfull, lmax, iters
+int hh_psd_fast6(const double* Hfull, double* Lfull, double* Hinvfull, double tol, double relpiv, double* lmax, int* iters) {
+  double H[21], L[21], Hi[21];
+  for (int i = 0; i < 6; ++i) for (int j = 0; j <= i; ++j) H[symidx(i, j)] = Hfull[j * 6 + i];
+  const bool ok = psd_fast6(H, L, Hi, tol, relpiv, lmax, iters);
+  for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) { Lfull[j * 6 + i] = (i >= j) ? L[symidx(i, j)] : 0.0; Hinvfull[j * 6 + i] = Hi[symidx(i, j)]; }
+  return ok ? 1 : 0;
+}
 int hh_psd3(double* Hfull, double* Hinvfull, double tol, double* lmax) {
   double H[6], Hi[6]; int sw;
   for (int i = 0; i < 3; ++i) for (int j = 0; j <= i; ++j) H[symidx(i, j)] = Hfull[j * 3 + i];

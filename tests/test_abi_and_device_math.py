@@ -99,6 +99,60 @@ def test_device_psd_fix_matches_oracle(harness):
             assert abs(lm[0] - ev[-1]) <= 1e-12 * ev[-1]
 
 
+def _snh_hessian(s, mu, la, h2, harness):
+    g = np.zeros(6); H = np.zeros(36); e = np.zeros(1)
+    harness.hh_material6(orc.MODELS["Stable-Neohookean"], C.c_double(mu), C.c_double(la), P(np.ascontiguousarray(s)), C.c_double(h2), P(g), P(H), P(e))
+    return H.reshape(6, 6).T.copy()
+
+
+def test_device_psd_fast_path_matches_oracle_and_rejects_what_it_must(harness):
+    """psd_fast6 (Cholesky + tridiagonal Newton for lambda_max) either reproduces psd_fix_invert (psd_fix.h:10-34) to
+    rounding or refuses: indefinite, near-singular, clustered-top and non-finite inputs must go to the Jacobi path."""
+    rng = np.random.default_rng(11)
+    ip = C.POINTER(C.c_int)
+
+    def run(A, relpiv=1e-5):
+        Hc = np.ascontiguousarray(A.T).reshape(-1).copy(); L = np.zeros(36); Hi = np.zeros(36); lm = np.zeros(1); it = np.zeros(1, dtype=np.int32)
+        ok = harness.hh_psd_fast6(P(Hc), P(L), P(Hi), C.c_double(1e-8), C.c_double(relpiv), P(lm), it.ctypes.data_as(ip))
+        return ok, L.reshape(6, 6).T, Hi.reshape(6, 6).T, lm[0], int(it[0])
+
+    mu, la = 344827.5862068966, 3103448.2758620693
+    n_ok = 0
+    for k in range(600):
+        if k % 2 == 0:   # material Hessians around realistic stretches
+            S = np.diag([1.2, .9, 1.05]) + 0.08 * rng.standard_normal((3, 3)); S = 0.5 * (S + S.T)
+            s = np.array([S[0, 0], S[1, 1], S[2, 2], S[0, 1], S[0, 2], S[1, 2]])
+            A = _snh_hessian(s, mu, la, 0.0333 ** 2, harness)
+        else:            # random SPD with a spread spectrum
+            Q, _ = np.linalg.qr(rng.standard_normal((6, 6)))
+            A = (Q * np.exp(rng.uniform(-3, 3, size=6))) @ Q.T; A = 0.5 * (A + A.T)
+        ev = np.linalg.eigvalsh(A)
+        ok, L, Hi, lm, it = run(A)
+        if ev[0] < 1e-8:
+            assert not ok
+            continue
+        if not ok:
+            continue
+        n_ok += 1
+        Af, Ai, evo = orc.psd_fix_invert(A, 1e-8)
+        assert np.linalg.norm(L @ L.T - Af) <= 1e-13 * np.linalg.norm(Af)
+        assert np.linalg.norm(Hi - Ai) <= 1e-11 * np.linalg.norm(Ai) * max(1.0, ev[-1] / ev[0] * 1e-4)
+        assert abs(lm - evo[-1]) <= 1e-12 * evo[-1], (lm, evo[-1], it)
+        assert it <= 24
+    assert n_ok > 400
+    # must refuse: indefinite, singular, negative definite, NaN, clustered top eigenvalue (polynomial root ill-conditioned)
+    Q, _ = np.linalg.qr(rng.standard_normal((6, 6)))
+    for lam in ([-1, 1, 2, 3, 4, 5], [0, 1, 2, 3, 4, 5], [1e-9, 1, 2, 3, 4, 5], [-5, -4, -3, -2, -1, -.5], [1, 2, 3, 4, 5, np.nan],
+                [1, 2, 3, 5, 5, 5], [1, 2, 3, 4, 5, 5 * (1 + 1e-9)]):
+        A = (Q * np.array(lam, dtype=float)) @ Q.T; A = 0.5 * (A + A.T)
+        assert not run(A)[0], lam
+    # accepted: diagonal / already tridiagonal inputs (Householder steps with nothing to annihilate), separated top
+    for A in (np.diag([1., 2, 3, 4, 5, 7]), np.diag([3., 1, 4, 1.5, 9, 2.6]) + np.diag([.1] * 5, 1) + np.diag([.1] * 5, -1)):
+        ok, L, Hi, lm, it = run(A)
+        assert ok and abs(lm - np.linalg.eigvalsh(A)[-1]) <= 1e-13 * lm
+        assert np.linalg.norm(Hi - np.linalg.inv(A)) <= 1e-13 * np.linalg.norm(Hi)
+
+
 def test_device_polar3_contracted_dsdf_matches_explicit_9x9(harness):
     rng = np.random.default_rng(2)
     ip = C.POINTER(C.c_int)

@@ -86,6 +86,33 @@ def test_update_parity_irregular_mesh_heterogeneous_materials(built):
     gpu.close()
 
 
+@pytest.mark.parametrize("variant,asm", [(3, 1), (3, 0), (1, 0), (0, 0), (2, 0)])
+def test_update_kernel_variants_agree_with_oracle(built, variant, asm):
+    """every update-kernel variant the library can select (option smem_b / asm_mode): default = v4 with bulk-reduction
+    assembly; the mesh is irregular with pinned vertices; about a third of the elements get an indefinite Hessian so
+    both the Cholesky fast path and the Jacobi tail are exercised (status psd_slow counts the latter)."""
+    V, T, fm, h = mesh(3, (9, 6, 5), shuffle=True, jitter=0.12, pin=0.12)
+    gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
+    gpu.set_option("smem_b", variant)
+    gpu.set_option("asm_mode", asm)
+    rng = np.random.default_rng(7)
+    s = st["s"].reshape(-1, 6).copy()
+    sel = rng.uniform(size=s.shape[0]) < 0.33
+    s[sel, :3] *= rng.uniform(0.45, 0.8, size=(int(sel.sum()), 1))
+    for it in range(2):      # second pass: warm R, values accumulate into freshly zeroed targets again
+        for o in (gpu, cpu):
+            o.set("s", s.reshape(-1))
+            o.update(st["x"] if it == 0 else st["xprev"], DT)
+        check_update(gpu, cpu, 3)
+    stt = gpu.status()
+    if variant == 3:
+        nslow = stt["psd_slow"]
+        assert 0 < nslow < gpu.nE, stt
+        ev = np.linalg.eigvalsh(cpu.get("H").reshape(-1, 6, 6))
+        assert nslow >= int(sel.sum()) // 4
+    gpu.close()
+
+
 def test_indefinite_hessians_are_clamped_identically(built):
     """compressed state: Stable-Neohookean Hessians with negative eigenvalues exercise the 1e-8 clamp (psd_fix.h:20-25)"""
     V, T, fm, h = mesh(3, (5, 4, 3))
