@@ -145,7 +145,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     if (bulk) {
       if (c->fuse_rhs) { k_update_tet_v4<true, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
       else { k_update_tet_v4<false, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
-      if (c->nb > 0) k_finalize_csr<<<nblk((int64_t)c->nb * 9), 256, 0, st>>>(c->finlist.p, c->nb, c->Ablk.p, c->Avals.p);
+      if (c->nb > 0) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, c->nF, c->Ablk.p, c->Avals.p);
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
       LAUNCHED(c, 3);
     } else {

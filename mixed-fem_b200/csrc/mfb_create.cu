@@ -108,30 +108,36 @@ __global__ void k_upper_flags(const int* __restrict__ brow, const int* __restric
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < nb) flag[b] = (brow[b] <= bcol[b]) ? 1 : 0;
 }
-// finalize list: (dst0, dst row length, src0 in Ablk, transposed) per block; ub = exclusive scan of the upper flags
-__global__ void k_finlist_fill(const int* __restrict__ blockptr, const int* __restrict__ brow, const int* __restrict__ bcol,
-                               const int* __restrict__ bT, const int* __restrict__ ub, int nb, int dim, int4* list) {
+// fcode[b] = 2 * (upper block holding the values of block b) + transposed ; ub = exclusive scan of the upper flags
+__global__ void k_fcode_fill(const int* __restrict__ brow, const int* __restrict__ bcol, const int* __restrict__ bT, const int* __restrict__ ub, int nb, int* fcode) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= nb) return;
-  const int gi = brow[b], gj = bcol[b], dd = dim * dim;
-  const int p0 = blockptr[gi], n0 = blockptr[gi + 1] - p0;
-  int4 v;
-  v.x = dd * p0 + dim * (b - p0); v.y = dim * n0;
-  v.z = 9 * ((gi <= gj) ? ub[b] : ub[bT[b]]); v.w = (gi <= gj) ? 0 : 1;
-  list[b] = v;
+  fcode[b] = (brow[b] <= bcol[b]) ? 2 * ub[b] : 2 * ub[bT[b]] + 1;
 }
-// bmap[pair10(j,k)][e] = 2 * upper block + transposed for the local pairs j <= k (sorted pair list: vals = e*16+j*4+k)
-__global__ void k_fill_bmap(const int* __restrict__ vals, const int* __restrict__ bid, const int* __restrict__ brow, const int* __restrict__ bcol,
-                            const int* __restrict__ bT, const int* __restrict__ ub, int64_t n, int64_t ld, int* bmap) {
+// local pair (j,k), j < k -> 0..5
+__host__ __device__ inline int pair6_index(int j, int k) { return j * 3 - j * (j - 1) / 2 + (k - j - 1); }
+// bmap[pair6(j,k)][e] for pairs with BOTH vertices free (sorted pair list: vals = e*16+j*4+k): 2 * upper block + transposed
+__global__ void k_fill_bmap(const int* __restrict__ vals, const int* __restrict__ bid, const int* __restrict__ fcode, int64_t n, int64_t ld, int* bmap) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int p = vals[i];
   const int e = p / 16, j = (p % 16) / 4, k = p % 4;
-  if (j > k) return;
-  const int b = bid[i] - 1;
-  const int gi = brow[b], gj = bcol[b];
-  const int code = (gi <= gj) ? 2 * ub[b] : 2 * ub[bT[b]] + 1;
-  bmap[(int64_t)(j * 4 - j * (j - 1) / 2 + (k - j)) * ld + e] = code;
+  if (j >= k) return;
+  bmap[(int64_t)pair6_index(j, k) * ld + e] = fcode[bid[i] - 1];
+}
+// pairs with exactly ONE pinned vertex: the block K_e(free, pinned) is accumulated into the DIAGONAL slot of the free
+// vertex; k_finalize_rows turns (row sum of the off-diagonal blocks + that slot) into the diagonal block, using
+// sum_k K_e(j,k) = 0 (Jloc = dphi^T (x) I and the four dphi rows sum to zero).
+__global__ void k_fill_bmap_pinned(const int* __restrict__ fidx, const int* __restrict__ diagblk, const int* __restrict__ ub, int nE, int64_t ld, int* bmap) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nE) return;
+  int f[4];
+  for (int k = 0; k < 4; ++k) f[k] = fidx[k * ld + e];
+  for (int j = 0; j < 4; ++j)
+    for (int k = j + 1; k < 4; ++k) {
+      if (f[j] >= 0 && f[k] < 0) bmap[(int64_t)pair6_index(j, k) * ld + e] = 2 * ub[diagblk[f[j]]];
+      else if (f[j] < 0 && f[k] >= 0) bmap[(int64_t)pair6_index(j, k) * ld + e] = 2 * ub[diagblk[f[k]]] + 1;
+    }
 }
 __global__ void k_fill_int(int* p, int64_t n, int v) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -193,7 +199,7 @@ static int build_pattern(mfb_ctx* c) {
     if (dim == 3) {
       // v4 assembly: number the upper-triangle blocks, element->block map, finalize list
       DBuf<int> uflag, ub;
-      if ((rc = uflag.alloc(nb)) || (rc = ub.alloc(nb)) || (rc = c->bmap.alloc((size_t)10 * c->ld)) || (rc = c->finlist.alloc(nb))) return rc;
+      if ((rc = uflag.alloc(nb)) || (rc = ub.alloc(nb)) || (rc = c->bmap.alloc((size_t)6 * c->ld)) || (rc = c->fcode.alloc(nb))) return rc;
       k_upper_flags<<<nblk(nb), 256, 0, st>>>(brow.p, c->bcol.p, nb, uflag.p);
       thrust::exclusive_scan(pol, thrust::device_ptr<int>(uflag.p), thrust::device_ptr<int>(uflag.p + nb), thrust::device_ptr<int>(ub.p));
       int last_pos = 0, last_flag = 0;
@@ -201,12 +207,13 @@ static int build_pattern(mfb_ctx* c) {
       MFB_CUDA(cudaMemcpyAsync(&last_flag, uflag.p + (nb - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
       MFB_CUDA(cudaStreamSynchronize(st));
       c->nbu = last_pos + last_flag;
-      k_fill_int<<<nblk((int64_t)10 * c->ld), 256, 0, st>>>(c->bmap.p, (int64_t)10 * c->ld, -1);
+      k_fill_int<<<nblk((int64_t)6 * c->ld), 256, 0, st>>>(c->bmap.p, (int64_t)6 * c->ld, -1);
       // vals / bid still hold the sorted pair list (head was reused above, bid was overwritten by the mirror scan: redo it)
       k_heads<<<nblk(nvalid), 256, 0, st>>>(keys.p, nvalid, head.p);
       thrust::inclusive_scan(pol, thrust::device_ptr<int>(head.p), thrust::device_ptr<int>(head.p + nvalid), thrust::device_ptr<int>(bid.p));
-      k_fill_bmap<<<nblk(nvalid), 256, 0, st>>>(vals.p, bid.p, brow.p, c->bcol.p, c->bT.p, ub.p, nvalid, c->ld, c->bmap.p);
-      k_finlist_fill<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, c->bT.p, ub.p, nb, dim, c->finlist.p);
+      k_fcode_fill<<<nblk(nb), 256, 0, st>>>(brow.p, c->bcol.p, c->bT.p, ub.p, nb, c->fcode.p);
+      k_fill_bmap<<<nblk(nvalid), 256, 0, st>>>(vals.p, bid.p, c->fcode.p, nvalid, c->ld, c->bmap.p);
+      k_fill_bmap_pinned<<<nblk(nE), 256, 0, st>>>(c->fidx.p, c->diagblk.p, ub.p, nE, c->ld, c->bmap.p);
       MFB_CUDA(cudaStreamSynchronize(st));
       if ((int64_t)c->nbu * 9 > (int64_t)INT_MAX) { g_last_error = "block-CSR exceeds int32"; return MFB_ERR_TOO_LARGE; }
     }

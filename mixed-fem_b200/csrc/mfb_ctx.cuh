@@ -58,10 +58,10 @@ struct mfb_ctx {
   mfb::DBuf<int> blockptr, brow, bcol, bT, diagblk, outer, inner;
   mfb::DBuf<int4> mirror;     // (dst0, dst stride, src0, src stride) per lower-triangle block, see k_mirror_lower
   int n_mirror = 0;
-  // v4 assembly: block-CSR upper triangle (9 doubles per block), element->block map, finalize list, interleaved vectors
+  // v4 assembly: block-CSR upper triangle (9 doubles per block), element->block map (6 pairs j<k), per-block source code, interleaved vectors
   mfb::DBuf<double> Ablk, gxrh;
   mfb::DBuf<int> bmap, slow_list;
-  mfb::DBuf<int4> finlist;
+  mfb::DBuf<int> fcode;       // per block: 2 * upper block + transposed
   int nbu = 0;
   // state (device)
   mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals, Lfac;

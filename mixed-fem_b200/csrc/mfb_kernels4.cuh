@@ -38,7 +38,7 @@ constexpr int kV4SmemStage = kV4Warps * (kV4StageDoubles * (int)sizeof(double) +
 struct DevAsm {
   double* Ablk;          // [nbu][9]  block-CSR copy of the upper triangle (row-major 3x3)
   double* gxrh;          // [nF][6]   grad_x | rhs interleaved
-  const int* bmap;       // [10][ld]  2*upper_block + transposed, -1 if a vertex of the pair is pinned
+  const int* bmap;       // [6][ld]   pairs j < k: 2*upper_block + transposed; one vertex pinned: the free vertex's diagonal slot; both: -1
   int* slow_list;        // [nE]
 };
 
@@ -62,8 +62,8 @@ __device__ __forceinline__ void coop_red(double* __restrict__ base, const double
   }
 }
 
-// local pair (j,k), j <= k  ->  0..9
-__device__ __forceinline__ constexpr int pair10(int j, int k) { return j * 4 - j * (j - 1) / 2 + (k - j); }
+// local pair (j,k), j < k  ->  0..5
+__device__ __forceinline__ constexpr int pair6(int j, int k) { return j * 3 - j * (j - 1) / 2 + (k - j - 1); }
 
 // `inrange` false: the lane has no element (grid padding); it runs on a clamped element index so that the warp stays
 // convergent for the cooperative reductions, and stores nothing.
@@ -324,28 +324,28 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       }
     }
   } else {
-    int code[10];
+    // off-diagonal pairs only: the diagonal blocks follow from the zero block-row sums in k_finalize_rows
+    int code[6];
 #pragma unroll
-    for (int q = 0; q < 10; ++q) code[q] = live ? as.bmap[q * ld + e] : -1;
+    for (int q = 0; q < 6; ++q) code[q] = live ? as.bmap[q * ld + e] : -1;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 3; ++j) {
       double bj[3][6];
 #pragma unroll
       for (int r = 0; r < 3; ++r)
 #pragma unroll
         for (int n = 0; n < 6; ++n) bj[r][n] = (j == 0) ? B0[r][n] : myB[(6 * (3 * (j - 1) + r) + n) * kV4Threads];
 #pragma unroll
-      for (int k = j; k < 4; ++k) {
-        const int cd = code[pair10(j, k)];
+      for (int k = j + 1; k < 4; ++k) {
+        const int cd = code[pair6(j, k)];
         double a[3][3];      // a[r][c] = (B_j B_k^T)(r,c)
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           double bk[6];
 #pragma unroll
-          for (int n = 0; n < 6; ++n) bk[n] = (k == j) ? bj[c][n] : myB[(6 * (3 * (k - 1) + c) + n) * kV4Threads];
+          for (int n = 0; n < 6; ++n) bk[n] = myB[(6 * (3 * (k - 1) + c) + n) * kV4Threads];
 #pragma unroll
           for (int r = 0; r < 3; ++r) {
-            if (j == k && r < c) { a[r][c] = a[c][r]; continue; }
             double t = 0.0;
 #pragma unroll
             for (int n = 0; n < 6; ++n) t += bj[r][n] * bk[n];
@@ -391,14 +391,51 @@ __global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4_tail(DevMesh m,
   }
 }
 
-// Block-CSR upper triangle -> reference-layout scalar CSR values, every entry written once.
-// list[b] = (dst0, dst row length, src0, transposed) for each of the nb blocks; one thread per scalar entry.
-static __global__ void __launch_bounds__(256) k_finalize_csr(const int4* __restrict__ list, int nb, const double* __restrict__ Ablk, double* __restrict__ A) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (int64_t)nb * 9) return;
-  const int b = (int)(i / 9), rc = (int)(i % 9), r = rc / 3, c = rc % 3;
-  const int4 v = __ldg(&list[b]);
-  A[(int64_t)v.x + (int64_t)r * v.y + c] = Ablk[(int64_t)v.z + (v.w ? c * 3 + r : r * 3 + c)];   // v.z = 9 * upper block
+// Block-CSR upper triangle -> reference-layout scalar CSR values (sparse_utils.cpp:155-163), every entry written once.
+// Half a warp per block-row gi, 15 active lanes: lane l handles the scalar columns q = l, l+15, l+30, ... of the row
+// (so its column-in-block c = l % 3 is fixed) for the three scalar rows r.  Off-diagonal block (gi,gj): read from the
+// upper-triangle copy (transposed when gj < gi), write, and accumulate the row sum.  Diagonal block: -(row sum of the
+// off-diagonal blocks + the K_e(free,pinned) blocks accumulated in its own slot), because every element matrix has
+// zero block-row sums.
+static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restrict__ blockptr, const int* __restrict__ diagblk, const int* __restrict__ fcode,
+                                                              int nF, const double* __restrict__ Ablk, double* __restrict__ A) {
+  const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int gi = (int)(gt >> 4), l = threadIdx.x & 15;
+  const bool rowok = gi < nF;
+  int p0 = 0, nbr = 0, dslot = -1;
+  if (rowok) { p0 = blockptr[gi]; nbr = blockptr[gi + 1] - p0; dslot = diagblk[gi] - p0; }
+  const int rowlen = 3 * nbr, c = l % 3;
+  const int64_t D0 = 9 * (int64_t)p0;
+  double acc[3] = {0.0, 0.0, 0.0}, dval[3] = {0.0, 0.0, 0.0};
+  int qd = -1;
+  if (l < 15) {
+    for (int q = l; q < rowlen; q += 15) {
+      const int slot = q / 3;
+      const int code = __ldg(&fcode[p0 + slot]);
+      const double* src = Ablk + 9 * (int64_t)(code >> 1);
+      if (slot == dslot) {
+        qd = q;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) dval[r] = src[3 * r + c];
+      } else {
+        const bool tr = code & 1;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          const double v = src[tr ? 3 * c + r : 3 * r + c];
+          A[D0 + (int64_t)r * rowlen + q] = v;
+          acc[r] += v;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    double t = acc[r] + __shfl_down_sync(0xffffffffu, acc[r], 3, 16);
+    t += __shfl_down_sync(0xffffffffu, t, 6, 16);
+    t += __shfl_down_sync(0xffffffffu, acc[r], 12, 16);
+    const double tot = __shfl_sync(0xffffffffu, t, c, 16);       // lanes 0..2 hold the totals of columns c = 0..2
+    if (qd >= 0) A[D0 + (int64_t)r * rowlen + qd] = -(dval[r] + tot);
+  }
 }
 
 static __global__ void __launch_bounds__(256) k_deinterleave_vec(const double* __restrict__ gxrh, int nF, double* __restrict__ gx, double* __restrict__ rh, int with_rhs) {
