@@ -139,6 +139,37 @@ int mfb_spmv_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* x_dev, do
 int mfb_pcg_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* b_dev, double* x_dev, int precond,
                 double tol, int max_iters, int* iters_out, double* relres_out);
 
+/* ---- device-resident Newton time step around the variable.  Replaces, for a scene with ONE mesh,
+ * the mixed-stretch variable and no contact:  NewtonOptimizer<DIM>::step (src/optimizers/newton_optimizer.cpp:14-139),
+ * linesearch_backtracking (src/linesearch.h:80-129), Displacement<DIM> (src/variables/displacement.cpp:21-96),
+ * BDF<1> (src/time_integrators/BDF.cpp:7-27), SystemMatrixPD (src/linear_solvers/linear_system.h:18-44) and the
+ * ConjugateGradient call of EigenIterativeSolver::solve (src/linear_solvers/eigen_iterative_solver.h:27-65) with the
+ * consistent mass matrix of deps/Bartels/src/linear_tet_mass_matrix.cpp:8-43 / linear_tri2d_mass_matrix.cpp:8-36. ---- */
+#define MFB_NEWTON_LOG_MAX 64
+typedef struct mfb_newton_opts {
+  int32_t outer_steps;    /* SimConfig::outer_steps (config.h:112, default 5) */
+  int32_t ls_iters;       /* SimConfig::ls_iters (config.h:113, default 20) */
+  double newton_tol;      /* SimConfig::newton_tol (config.h:127, default 1e-10) */
+  int32_t precond;        /* 0 none, 1 diagonal ("eigen-pcg-diag"), 2 block-Jacobi ("eigen-pcg-block_jacobi") */
+  double cg_tol;          /* SimConfig::itr_tol (config.h:131, default 1e-4) */
+  int32_t cg_max_iters;   /* SimConfig::max_iterative_solver_iters (default 500) */
+} mfb_newton_opts;
+typedef struct mfb_newton_log {   /* the OptimizerData columns of newton_optimizer.cpp:92-97 per Newton iteration */
+  int32_t n_iters;
+  int64_t cg_iters_total;
+  double energy[MFB_NEWTON_LOG_MAX], energy_res[MFB_NEWTON_LOG_MAX], decrement[MFB_NEWTON_LOG_MAX], alpha[MFB_NEWTON_LOG_MAX];
+  double cg_error[MFB_NEWTON_LOG_MAX];
+  int32_t cg_iters[MFB_NEWTON_LOG_MAX], ls_iters[MFB_NEWTON_LOG_MAX];
+} mfb_newton_log;
+/* Displacement::reset + BDF1 state: free_map as given to mfb_create; density = MaterialConfig::density; h = SimConfig::h;
+ * force = body force d-vector (NULL: gravity (0,-9.8,0)); x0 / v0 host d*nV or NULL (vec(Vref^T), zero).  Also builds
+ * PMP^T on the Assembler pattern. */
+int mfb_newton_init(mfb_ctx* ctx, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0);
+int mfb_newton_step(mfb_ctx* ctx, const mfb_newton_opts* opts, mfb_newton_log* log);   /* one time step = NewtonOptimizer::step() */
+int mfb_newton_positions(mfb_ctx* ctx, double* x_full);                                 /* host d*nV */
+int mfb_newton_positions_dev(mfb_ctx* ctx, double** x_full_dev, const double** mass_values_dev);
+void mfb_newton_free(mfb_ctx* ctx);
+
 /* ---- instrumentation ---- */
 int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
 int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0) */

@@ -28,6 +28,7 @@ EXPORTS = [
     "mfb_constraint_value_dev", "mfb_evaluate_constraint", "mfb_lhs_values", "mfb_lhs_values_dev", "mfb_product",
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
     "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
+    "mfb_newton_init", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
 ]
 
 
@@ -49,6 +50,22 @@ class _MeshDesc(C.Structure):
 class _Status(C.Structure):
     _fields_ = [("polar_maxiter", C.c_int64), ("polar_hfail", C.c_int64), ("nonfinite", C.c_int64),
                 ("polar_iters", C.c_int64), ("eig_sweeps", C.c_int64), ("psd_slow", C.c_int64)]
+
+
+NEWTON_LOG_MAX = 64
+
+
+class _NewtonOpts(C.Structure):
+    _fields_ = [("outer_steps", C.c_int32), ("ls_iters", C.c_int32), ("newton_tol", C.c_double), ("precond", C.c_int32),
+                ("cg_tol", C.c_double), ("cg_max_iters", C.c_int32)]
+
+
+class _NewtonLog(C.Structure):
+    _fields_ = [("n_iters", C.c_int32), ("cg_iters_total", C.c_int64),
+                ("energy", C.c_double * NEWTON_LOG_MAX), ("energy_res", C.c_double * NEWTON_LOG_MAX),
+                ("decrement", C.c_double * NEWTON_LOG_MAX), ("alpha", C.c_double * NEWTON_LOG_MAX),
+                ("cg_error", C.c_double * NEWTON_LOG_MAX),
+                ("cg_iters", C.c_int32 * NEWTON_LOG_MAX), ("ls_iters", C.c_int32 * NEWTON_LOG_MAX)]
 
 
 def build(force=False, verbose=False):
@@ -114,6 +131,12 @@ def lib():
     L.mfb_num_kernel_launches.argtypes = [vp, C.POINTER(C.c_int64), C.c_int]
     L.mfb_set_option.argtypes = [vp, C.c_char_p, C.c_int]
     L.mfb_kernel_time_ms.argtypes = [vp, dp, ip]
+    L.mfb_newton_init.argtypes = [vp, ip, C.c_double, C.c_double, dp, dp, dp]
+    L.mfb_newton_step.argtypes = [vp, C.POINTER(_NewtonOpts), C.POINTER(_NewtonLog)]
+    L.mfb_newton_positions.argtypes = [vp, dp]
+    L.mfb_newton_positions_dev.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    L.mfb_newton_free.argtypes = [vp]
+    L.mfb_newton_free.restype = None
     _lib = L
     return L
 
@@ -163,6 +186,32 @@ class MixedStretch:
         nF, nnz = C.c_int32(), C.c_int64()
         self.L.mfb_dims(self.h, None, None, None, C.byref(nF), None, C.byref(nnz))
         self.nfree, self.nnz = nF.value, nnz.value
+        self._free_map = fm
+
+    # ---- device-resident Newton time step (NewtonOptimizer<DIM>::step, newton_optimizer.cpp:14-139) ----
+    def newton_init(self, density=1000.0, h=0.0333, force=None, x0=None, v0=None):
+        """Displacement::reset + BDF1 + mass matrix (displacement.cpp:73-93); force = body-force d-vector (default gravity)."""
+        f = None if force is None else _f64(force)
+        x0 = None if x0 is None else _f64(x0)
+        v0 = None if v0 is None else _f64(v0)
+        self._check(self.L.mfb_newton_init(self.h, _ip(self._free_map), float(density), float(h), _dp(f) if f is not None else None,
+                                           _dp(x0) if x0 is not None else None, _dp(v0) if v0 is not None else None))
+
+    def newton_step(self, outer_steps=5, ls_iters=20, newton_tol=1e-10, precond=1, cg_tol=1e-4, cg_max_iters=500):
+        """One time step; returns the per-iteration columns the reference prints (newton_optimizer.cpp:92-97)."""
+        o = _NewtonOpts(outer_steps, ls_iters, newton_tol, precond, cg_tol, cg_max_iters)
+        log = _NewtonLog()
+        self._check(self.L.mfb_newton_step(self.h, C.byref(o), C.byref(log)))
+        n = min(log.n_iters, NEWTON_LOG_MAX)
+        return {"n_iters": log.n_iters, "cg_iters_total": log.cg_iters_total,
+                "energy": np.array(log.energy[:n]), "energy_res": np.array(log.energy_res[:n]),
+                "decrement": np.array(log.decrement[:n]), "alpha": np.array(log.alpha[:n]),
+                "cg_iters": np.array(log.cg_iters[:n]), "cg_error": np.array(log.cg_error[:n]), "ls_iters": np.array(log.ls_iters[:n])}
+
+    def newton_positions(self):
+        out = np.empty(self.dim * self.nV)
+        self._check(self.L.mfb_newton_positions(self.h, _dp(out)))
+        return out
 
     def _check(self, rc):
         if rc != 0:

@@ -335,7 +335,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
   if (dim == 3) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 16)); TRY(c->gxrh.alloc((size_t)6 * nF + 8)); TRY(c->slow_list.alloc((size_t)nE + 1)); }
   TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));
-  TRY(c->partials.alloc((size_t)c->grid() + 64)); TRY(c->scal.alloc(16));
+  TRY(c->partials.alloc((size_t)c->grid() + 1024)); TRY(c->scal.alloc(16));
   TRY(c->soa_tmp.alloc(N * ld)); TRY(c->soa_tmp2.alloc(N * ld));
 #undef TRY
   cudaError_t e1 = cudaMallocHost((void**)&c->h_scal, 16 * sizeof(double));
@@ -356,6 +356,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
 extern "C" void mfb_destroy(mfb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  mfb_newton_free(c);
   if (c->h_scal) cudaFreeHost(c->h_scal);
   delete c;
 }

@@ -82,6 +82,7 @@ struct mfb_ctx {
   int profile = 0;
   std::vector<cudaEvent_t> ev0, ev1;
   int ev_count = 0;
+  void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)
 
   mfb::DevMesh mesh() const {
     mfb::DevMesh m;

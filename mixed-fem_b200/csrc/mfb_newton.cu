@@ -1,0 +1,344 @@
+// Device-resident Newton time step around the mixed-stretch variable:
+//   NewtonOptimizer<DIM>::step / update_system / substep .... src/optimizers/newton_optimizer.cpp:14-139
+//   linesearch_backtracking (c = 0, p = 0.5) ................. src/linesearch.h:80-129
+//   Displacement<DIM>::energy / gradient / reset / post_solve  src/variables/displacement.cpp:21-96
+//   BDF<1>::x_tilde / update ................................. src/time_integrators/BDF.cpp:7-27
+//   SystemMatrixPD::pre_solve / post_solve ................... src/linear_solvers/linear_system.h:18-44
+//   EigenIterativeSolver::solve (initial guess, CG) .......... src/linear_solvers/eigen_iterative_solver.h:27-65
+//   consistent mass matrix ................................... deps/Bartels/src/linear_tet_mass_matrix.cpp:8-43,
+//                                                              linear_tri2d_mass_matrix.cpp:8-36 (+ assemble.cpp)
+// Vectors stay on the device; the host sees only the scalars the reference's control flow branches on (energies, the
+// decrement, the CG residual).  Contact (ipc::additive_ccd) is out of scope: the CCD step scale is 1.
+#include "mfb_ctx.cuh"
+#include <cmath>
+#include <cstring>
+
+using namespace mfb;
+
+#define CHECK_CTX(c) do { if (!(c)) { g_last_error = "null context"; return MFB_ERR_INVALID; } cudaSetDevice((c)->device); } while (0)
+
+namespace {
+
+inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
+
+// consistent element mass: block (j,k) = mass * (j == k ? c0 : c1) * I_d ; tets 1/10, 1/20 ; triangles 1/6, 1/12
+template <int DIM> struct MassCoef { static constexpr double c0 = DIM == 3 ? 0.1 : 1.0 / 6.0, c1 = DIM == 3 ? 0.05 : 1.0 / 12.0; };
+
+// PMP^T on the Assembler pattern: only the d diagonal entries of each d x d block are non-zero
+template <int DIM>
+__global__ void __launch_bounds__(128) k_mass_values(DevMesh m, double density, double* __restrict__ Mvals) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  const double mass = density * m.vol[e];
+#pragma unroll
+  for (int j = 0; j <= DIM; ++j) {
+    const int stride = m.sstride[j * ld + e];
+#pragma unroll
+    for (int k = 0; k <= DIM; ++k) {
+      const int idx = m.smap[(j * (DIM + 1) + k) * ld + e];
+      if (idx < 0) continue;
+      const double v = mass * (j == k ? MassCoef<DIM>::c0 : MassCoef<DIM>::c1);
+#pragma unroll
+      for (int r = 0; r < DIM; ++r) red_add(&Mvals[(int64_t)idx + (int64_t)r * stride + r], v);
+    }
+  }
+}
+
+// diff = x - x_tilde - h^2 f  (full vectors, d*nV ; f is one d-vector replicated: the body force of config.h:165-168)
+template <int DIM>
+__global__ void k_inertia_diff(const double* __restrict__ x, const double* __restrict__ xt, double h2fx, double h2fy, double h2fz, int nV, double* __restrict__ diff) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= DIM * nV) return;
+  const int l = i % DIM;
+  diff[i] = x[i] - xt[i] - (l == 0 ? h2fx : (l == 1 ? h2fy : h2fz));
+}
+
+// out(free rows) += sign * PM diff : element-wise product with the consistent mass blocks, all columns (pinned included)
+template <int DIM>
+__global__ void __launch_bounds__(128) k_mass_rows_apply(DevMesh m, double density, const double* __restrict__ diff, double sign, double* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  const double mass = sign * density * m.vol[e];
+  double d[DIM + 1][DIM], sum[DIM];
+#pragma unroll
+  for (int l = 0; l < DIM; ++l) sum[l] = 0.0;
+#pragma unroll
+  for (int k = 0; k <= DIM; ++k) {
+    const int v = m.T[k * ld + e];
+#pragma unroll
+    for (int l = 0; l < DIM; ++l) { d[k][l] = diff[DIM * (int64_t)v + l]; sum[l] += d[k][l]; }
+  }
+#pragma unroll
+  for (int j = 0; j <= DIM; ++j) {
+    const int f = m.fidx[j * ld + e];
+    if (f < 0) continue;
+#pragma unroll
+    for (int l = 0; l < DIM; ++l)
+      red_add(&out[DIM * (int64_t)f + l], mass * (MassCoef<DIM>::c1 * sum[l] + (MassCoef<DIM>::c0 - MassCoef<DIM>::c1) * d[j][l]));
+  }
+}
+
+// 0.5 diff^T M diff with the FULL mass matrix (displacement.cpp:21-33), per-block partial sums
+template <int DIM>
+__global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, double density, const double* __restrict__ diff, double* __restrict__ partials) {
+  __shared__ double sh[4];
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  double val = 0.0;
+  if (e < m.nE) {
+    const int64_t ld = m.ld;
+    double sum[DIM], sq = 0.0;
+#pragma unroll
+    for (int l = 0; l < DIM; ++l) sum[l] = 0.0;
+#pragma unroll
+    for (int k = 0; k <= DIM; ++k) {
+      const int v = m.T[k * ld + e];
+#pragma unroll
+      for (int l = 0; l < DIM; ++l) { const double a = diff[DIM * (int64_t)v + l]; sum[l] += a; sq += a * a; }
+    }
+    double ss = 0.0;
+#pragma unroll
+    for (int l = 0; l < DIM; ++l) ss += sum[l] * sum[l];
+    // sum_jk m_jk d_j.d_k = c1 |sum_j d_j|^2 + (c0 - c1) sum_j |d_j|^2
+    val = 0.5 * density * m.vol[e] * (MassCoef<DIM>::c1 * ss + (MassCoef<DIM>::c0 - MassCoef<DIM>::c1) * sq);
+  }
+  const double r = block_sum_128(val, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = r;
+}
+
+// y(full) = x(full) + a * P^T dx(free)
+template <int DIM>
+__global__ void k_unproject_axpy(const double* __restrict__ x, const int* __restrict__ vfree, const double* __restrict__ dx, double a, int nV, double* __restrict__ y) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= DIM * nV) return;
+  const int v = i / DIM, l = i % DIM, f = vfree[v];
+  y[i] = x[i] + (f >= 0 ? a * dx[DIM * (int64_t)f + l] : 0.0);
+}
+// guess(free) = -diff restricted to the free vertices (eigen_iterative_solver.h:44-52 with alpha = 1)
+template <int DIM>
+__global__ void k_guess(const double* __restrict__ diff, const int* __restrict__ vfree, int nV, double* __restrict__ g) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= DIM * nV) return;
+  const int v = i / DIM, l = i % DIM, f = vfree[v];
+  if (f >= 0) g[DIM * (int64_t)f + l] = -diff[i];
+}
+__global__ void k_axpy_out(const double* __restrict__ x, const double* __restrict__ d, double a, int64_t n, double* __restrict__ y) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = x[i] + a * d[i];
+}
+// max |v| over a component-major element array (rows e < nE only: the padding of ld is not initialised)
+__global__ void __launch_bounds__(256) k_absmax_soa(const double* __restrict__ v, int ncomp, int nE, int64_t ld, double* __restrict__ partials) {
+  __shared__ double sh[8];
+  double a = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < (int64_t)ncomp * nE; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t cidx = i / nE, e = i % nE;
+    a = fmax(a, fabs(v[cidx * ld + e]));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a = fmax(a, __shfl_down_sync(0xffffffffu, a, o));
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) { double r = 0.0; for (int i = 0; i < 8; ++i) r = fmax(r, sh[i]); partials[blockIdx.x] = r; }
+}
+__global__ void k_max_partials(const double* __restrict__ partials, int n, double* out) {
+  __shared__ double sh[8];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) a = fmax(a, partials[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a = fmax(a, __shfl_down_sync(0xffffffffu, a, o));
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) { double r = 0.0; for (int i = 0; i < (int)(blockDim.x >> 5); ++i) r = fmax(r, sh[i]); *out = r; }
+}
+// BDF1 (BDF.cpp:17-27): v = (x - x_prev) / h ; x_prev = x ; x_tilde = x + h v
+__global__ void k_bdf1_update(const double* __restrict__ x, double* __restrict__ xprev, double* __restrict__ vprev, double* __restrict__ xt, double h, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double v = (x[i] - xprev[i]) / h;
+  vprev[i] = v; xprev[i] = x[i]; xt[i] = x[i] + h * v;
+}
+
+int read_scalar(mfb_ctx* c, const double* dev, double* out) {
+  MFB_CUDA(cudaMemcpyAsync(c->h_scal, dev, 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  *out = c->h_scal[0];
+  return MFB_OK;
+}
+
+int sum_partials(mfb_ctx* c, int n, double* out) {
+  k_sum_partials<<<1, 256, 0, c->stream>>>(c->partials.p, n, c->scal.p);
+  c->launches += 1;
+  return read_scalar(c, c->scal.p, out);
+}
+
+}  // namespace
+
+struct mfb_newton_state {
+  double density = 1000.0, h = 0.0333, f[3] = {0, -9.8, 0};
+  DBuf<double> Mvals, x, xprev, vprev, xt, diff, xtrial, strial, dx, b;
+  DBuf<int> vfree;
+  bool ready = false;
+};
+
+static mfb_newton_state* nstate(mfb_ctx* c) { return (mfb_newton_state*)c->newton; }
+
+extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0) {
+  CHECK_CTX(c);
+  if (!free_map || !(h > 0) || !(density > 0)) { g_last_error = "mfb_newton_init: bad arguments"; return MFB_ERR_INVALID; }
+  if (c->newton) { delete nstate(c); c->newton = nullptr; }
+  mfb_newton_state* s = new mfb_newton_state();
+  c->newton = s;
+  s->density = density; s->h = h;
+  for (int l = 0; l < 3; ++l) s->f[l] = force ? (l < c->dim ? force[l] : 0.0) : (l == 1 ? -9.8 : 0.0);
+  const size_t nx = (size_t)c->dim * c->nV, nf = (size_t)c->dim * c->nF + 1;
+  int rc;
+  if ((rc = s->Mvals.alloc(c->nnz > 0 ? c->nnz : 1)) || (rc = s->x.alloc(nx)) || (rc = s->xprev.alloc(nx)) || (rc = s->vprev.alloc(nx)) ||
+      (rc = s->xt.alloc(nx)) || (rc = s->diff.alloc(nx)) || (rc = s->xtrial.alloc(nx)) || (rc = s->strial.alloc((size_t)c->N * c->ld)) ||
+      (rc = s->dx.alloc(nf)) || (rc = s->b.alloc(nf)) || (rc = s->vfree.alloc(c->nV)))
+    return rc;
+  cudaStream_t st = c->stream;
+  MFB_CUDA(cudaMemcpyAsync(s->vfree.p, free_map, (size_t)c->nV * 4, cudaMemcpyHostToDevice, st));
+  // Displacement::reset (displacement.cpp:73-93): x = vec(V^T), v0 from the mesh (zero unless given)
+  if (x0) MFB_CUDA(cudaMemcpyAsync(s->x.p, x0, nx * 8, cudaMemcpyHostToDevice, st));
+  else MFB_CUDA(cudaMemcpyAsync(s->x.p, c->vref.p, nx * 8, cudaMemcpyDeviceToDevice, st));
+  MFB_CUDA(cudaMemcpyAsync(s->xprev.p, s->x.p, nx * 8, cudaMemcpyDeviceToDevice, st));
+  if (v0) MFB_CUDA(cudaMemcpyAsync(s->vprev.p, v0, nx * 8, cudaMemcpyHostToDevice, st));
+  else MFB_CUDA(cudaMemsetAsync(s->vprev.p, 0, nx * 8, st));
+  // x_tilde = x_prev + h v_prev
+  k_axpy_out<<<nblk((int64_t)nx), 256, 0, st>>>(s->xprev.p, s->vprev.p, h, (int64_t)nx, s->xt.p);
+  MFB_CUDA(cudaMemsetAsync(s->Mvals.p, 0, (size_t)(c->nnz > 0 ? c->nnz : 1) * 8, st));
+  if (c->dim == 3) k_mass_values<3><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
+  else k_mass_values<2><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
+  c->launches += 2;
+  MFB_CUDA(cudaStreamSynchronize(st));
+  MFB_CUDA(cudaGetLastError());
+  s->ready = true;
+  return MFB_OK;
+}
+
+// energy_func(a) of newton_optimizer.cpp:63-78 : Displacement::energy(x + a dx) + h^2 psi(s + a ds) + constraint(x0, s + a ds)
+static int trial_energy(mfb_ctx* c, mfb_newton_state* s, double a, double* out) {
+  cudaStream_t st = c->stream;
+  const int nV = c->nV, dim = c->dim;
+  const double h2 = s->h * s->h;
+  const int64_t nx = (int64_t)dim * nV;
+  if (dim == 3) k_unproject_axpy<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, a, nV, s->xtrial.p);
+  else k_unproject_axpy<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, a, nV, s->xtrial.p);
+  if (dim == 3) k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->xtrial.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
+  else k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->xtrial.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);
+  if (dim == 3) k_inertia_energy<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
+  else k_inertia_energy<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
+  c->launches += 3;
+  double e_x = 0, e_s = 0, e_c = 0;
+  int rc = sum_partials(c, c->grid(), &e_x);
+  if (rc) return rc;
+  k_axpy_out<<<nblk((int64_t)c->N * c->ld), 256, 0, st>>>(c->s.p, c->ds.p, a, (int64_t)c->N * c->ld, s->strial.p);
+  c->launches += 1;
+  if ((rc = mfb_energy_dev(c, s->strial.p, &e_s))) return rc;
+  if ((rc = mfb_constraint_value_dev(c, s->xtrial.p, s->strial.p, &e_c))) return rc;
+  *out = e_x + h2 * e_s + e_c;
+  return MFB_OK;
+}
+
+extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_log* log) {
+  CHECK_CTX(c);
+  mfb_newton_state* s = nstate(c);
+  if (!s || !s->ready || !o || !log) { g_last_error = "mfb_newton_step: call mfb_newton_init first"; return MFB_ERR_INVALID; }
+  cudaStream_t st = c->stream;
+  const int dim = c->dim, nV = c->nV;
+  const int64_t nx = (int64_t)dim * nV, nf = (int64_t)dim * c->nF;
+  const double h2 = s->h * s->h;
+  int rc;
+  int i = 0;
+  double grad_norm = 0, E = 0, E_prev = 0, res = 0;
+  log->n_iters = 0; log->cg_iters_total = 0;
+  do {
+    // update_system(): var->update(unprojected x, dt)
+    if ((rc = mfb_update_dev(c, s->x.p, s->h))) return rc;
+    // SystemMatrixPD::pre_solve: rhs = -PM (x - x_tilde - h^2 f) + rhs_mixed ; lhs = PMP^T + A
+    const double* rhs_mixed = nullptr;
+    if ((rc = mfb_rhs_dev(c, &rhs_mixed))) return rc;
+    MFB_CUDA(cudaMemcpyAsync(s->b.p, rhs_mixed, (size_t)nf * 8, cudaMemcpyDeviceToDevice, st));
+    if (dim == 3) {
+      k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
+      k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
+      k_guess<3><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
+    } else {
+      k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);
+      k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
+      k_guess<2><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
+    }
+    c->launches += 3;
+    int cg_it = 0; double cg_res = 0;
+    if ((rc = mfb_pcg_dev(c, s->Mvals.p, s->b.p, s->dx.p, o->precond, o->cg_tol, o->cg_max_iters, &cg_it, &cg_res))) return rc;
+    // post_solve: x.delta = dx ; var->solve(dx)
+    if ((rc = mfb_solve_dev(c, s->dx.p))) return rc;
+    // substep(): decrement = max(|dx|_inf, |ds|_inf)
+    double mx = 0, ms = 0;
+    k_absmax_soa<<<256, 256, 0, st>>>(s->dx.p, 1, (int)nf, nf, c->partials.p);
+    k_max_partials<<<1, 256, 0, st>>>(c->partials.p, 256, c->scal.p);
+    if ((rc = read_scalar(c, c->scal.p, &mx))) return rc;
+    k_absmax_soa<<<256, 256, 0, st>>>(c->ds.p, c->N, c->nE, c->ld, c->partials.p);
+    k_max_partials<<<1, 256, 0, st>>>(c->partials.p, 256, c->scal.p);
+    if ((rc = read_scalar(c, c->scal.p, &ms))) return rc;
+    c->launches += 4;
+    grad_norm = mx > ms ? mx : ms;
+    double alpha = 1.0;
+    if ((rc = trial_energy(c, s, 0.0, &E))) return rc;
+    res = std::fabs((E - E_prev) / (E + 1e-6));
+    E_prev = E;
+    // linesearch_backtracking(state, alpha, energy, c = 0, p = 0.5): accept the first alpha with f(alpha) < f(0)
+    int iter = 0;
+    const double fx0 = E;
+    while (iter < o->ls_iters) {
+      double fx;
+      if ((rc = trial_energy(c, s, alpha, &fx))) return rc;
+      if (fx < fx0) break;
+      alpha *= 0.5;
+      ++iter;
+    }
+    if (iter < o->ls_iters) {
+      if (dim == 3) k_unproject_axpy<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, alpha, nV, s->x.p);
+      else k_unproject_axpy<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, alpha, nV, s->x.p);
+      k_axpy_out<<<nblk((int64_t)c->N * c->ld), 256, 0, st>>>(c->s.p, c->ds.p, alpha, (int64_t)c->N * c->ld, c->s.p);
+      c->launches += 2;
+    }
+    if (i < MFB_NEWTON_LOG_MAX) {
+      log->energy[i] = E; log->energy_res[i] = res; log->decrement[i] = grad_norm; log->alpha[i] = alpha;
+      log->cg_iters[i] = cg_it; log->cg_error[i] = cg_res; log->ls_iters[i] = iter;
+    }
+    log->cg_iters_total += cg_it;
+    ++i;
+  } while (i < o->outer_steps && grad_norm > o->newton_tol && res > 1e-12);
+  log->n_iters = i;
+  // post_solve: integrator update with the new positions, la_ = 0 (displacement.cpp:36-54, mixed_stretch.cpp:340-343)
+  k_bdf1_update<<<nblk(nx), 256, 0, st>>>(s->x.p, s->xprev.p, s->vprev.p, s->xt.p, s->h, (int)nx);
+  c->launches += 1;
+  if ((rc = mfb_post_solve(c))) return rc;
+  MFB_CUDA(cudaStreamSynchronize(st));
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
+
+extern "C" int mfb_newton_positions(mfb_ctx* c, double* x_full) {
+  CHECK_CTX(c);
+  mfb_newton_state* s = nstate(c);
+  if (!s || !s->ready || !x_full) return MFB_ERR_INVALID;
+  MFB_CUDA(cudaMemcpyAsync(x_full, s->x.p, (size_t)c->dim * c->nV * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_newton_positions_dev(mfb_ctx* c, double** x_full_dev, const double** mass_values_dev) {
+  CHECK_CTX(c);
+  mfb_newton_state* s = nstate(c);
+  if (!s || !s->ready) return MFB_ERR_INVALID;
+  if (x_full_dev) *x_full_dev = s->x.p;
+  if (mass_values_dev) *mass_values_dev = s->Mvals.p;
+  return MFB_OK;
+}
+
+extern "C" void mfb_newton_free(mfb_ctx* c) {
+  if (c && c->newton) { cudaSetDevice(c->device); delete nstate(c); c->newton = nullptr; }
+}
