@@ -296,6 +296,9 @@ def gpu_arm(args):
             "polar_iters_per_tet": st0["polar_iters"] / max(nE_l, 1), "eig_sweeps_per_tet": st0["eig_sweeps"] / max(nE_l, 1),
             "psd_slow_fraction": st0.get("psd_slow", 0) / max(nE_l, 1),
         }
+        if world == 1 and not args.no_newton:
+            ms.close()
+            out["newton_iteration"] = newton_leg(args)
         if world == 1 and not args.no_cpu:
             cx, cy, cz = args.cpu_grid
             _, info = cpu_arm(cx, cy, cz, args.cpu_seconds)
@@ -303,6 +306,38 @@ def gpu_arm(args):
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def newton_leg(args):
+    """Second metric of BASELINE.json (ms per Newton iteration) on config C3: 55^3 x 6 = 998 250 tets, ARAP, one time step
+    of the device-resident Newton driver with the reference's default solver settings (eigen-pcg-diag, itr_tol 1e-4,
+    <= 500 CG iterations, outer_steps 3): update + rhs + lhs = M + A + PCG + solve(dx) + line search per iteration."""
+    import torch
+    import mixed_fem_b200 as mf
+    from mixed_fem_b200 import meshgen
+    nx, ny, nz = args.newton_grid
+    h = 1.0 / nx
+    V, T = meshgen.kuhn_grid(nx, ny, nz, h=h)
+    fm = meshgen.pinned_free_map(V)
+    mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
+    ms = mf.MixedStretch(V, T, fm, [("ARAP", mu, la)])
+    ms.reset()
+    ms.newton_init(density=1000.0, h=DT)
+    ms.newton_step(outer_steps=1)                     # warm-up time step
+    torch.cuda.synchronize()
+    ms.launches(reset=True)
+    t0 = time.perf_counter()
+    lg = ms.newton_step(outer_steps=3, precond=1, cg_tol=1e-4, cg_max_iters=500)
+    torch.cuda.synchronize()
+    el = (time.perf_counter() - t0) * 1e3
+    n = max(int(lg["n_iters"]), 1)
+    out = {"workload": "C3: %dx%dx%d Kuhn grid = %d tets, ARAP, dt=%.4f, eigen-pcg-diag tol 1e-4" % (nx, ny, nz, T.shape[0], DT),
+           "ms_per_newton_iteration": el / n, "newton_iterations": n, "cg_iterations": [int(v) for v in lg["cg_iters"]],
+           "ms_per_cg_iteration_upper_bound": el / max(int(lg["cg_iters_total"]), 1),
+           "energy": [float(v) for v in lg["energy"]], "decrement": [float(v) for v in lg["decrement"]],
+           "alpha": [float(v) for v in lg["alpha"]], "gpu_launches": ms.launches(), "timing": "host wall clock around one time step (the loop branches on device scalars)"}
+    ms.close()
+    return out
 
 
 def reference_arm(args):
@@ -340,6 +375,8 @@ def main():
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-newton", action="store_true", help="skip the ms-per-Newton-iteration leg (config C3)")
+    ap.add_argument("--newton-grid", type=int, nargs=3, default=[55, 55, 55])
     ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): 3 v4 (default), 0 register B, 1 shared-memory B, 2 single fused launch")
     ap.add_argument("--asm", type=int, default=None, help="v4 assembly mode (library option asm_mode): 1 bulk reductions into block-CSR (default), 0 FP64 RED into scalar CSR")
     args = ap.parse_args()
