@@ -289,7 +289,7 @@ def gpu_arm(args):
             "gpu_launches": int(launches_all),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                         "traffic": traffic, "kernel": "k_update_tet<fuse_rhs,assemble>", "kernel_ms": k_ms,
+                         "traffic": traffic, "kernel": "k_update_tet_v4<fuse_rhs,coop-RED> + k_update_tet_v4_tail + k_finalize_rows + k_deinterleave_vec (one update())", "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": abytes, "bytes_per_tet": abytes / nE_l,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                          "kernel_share_of_step": k_ms / per_step if per_step > 0 else None},
