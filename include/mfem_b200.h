@@ -31,7 +31,7 @@ enum mfb_error {
 
 /* src/factories/material_model_factory.cpp:11-47 names: "Stable-Neohookean","Neohookean","Corot","FixedCorot","ARAP","Fung" */
 enum mfb_model { MFB_SNH = 0, MFB_NH = 1, MFB_COROT = 2, MFB_FCR = 3, MFB_ARAP = 4, MFB_FUNG = 5 };
-enum mfb_elem { MFB_TET = 0, MFB_TRI2D = 1 };
+enum mfb_elem { MFB_TET = 0, MFB_TRI2D = 1, MFB_SHELL = 2 };   /* TetrahedralMesh, Tri2DMesh, TriMesh (src/mesh/*.h) */
 
 typedef struct {          /* src/config.h:143-151 MaterialConfig (the fields the path reads) */
   int32_t model;
@@ -39,7 +39,7 @@ typedef struct {          /* src/config.h:143-151 MaterialConfig (the fields the
 } mfb_material;
 
 typedef struct {          /* what MixedStretch pulls from Mesh: src/mesh/mesh.h:82-105,151-171 */
-  int32_t elem_kind;      /* MFB_TET (TetrahedralMesh) or MFB_TRI2D (Tri2DMesh) */
+  int32_t elem_kind;      /* MFB_TET (TetrahedralMesh), MFB_TRI2D (Tri2DMesh) or MFB_SHELL (TriMesh: T is nE x 3, Vref is nV x 3) */
   int32_t nV, nE;
   const int32_t* T;       /* nE x (d+1) row-major vertex ids      (Mesh::T_) */
   const double* Vref;     /* nV x d row-major reference positions (Mesh::Vref_) */
@@ -48,6 +48,8 @@ typedef struct {          /* what MixedStretch pulls from Mesh: src/mesh/mesh.h:
   int32_t n_mat;
   const mfb_material* materials;
   int32_t device;         /* CUDA device ordinal */
+  const double* normals;  /* MFB_SHELL only: nE x 3 row-major per-face rest normals (TriMesh::N_, tri_mesh.cpp:31-36) */
+  double thickness;       /* MFB_SHELL only: MaterialConfig::thickness (volumes = doublearea*thickness/2, tri_mesh.cpp:38-41) */
 } mfb_mesh_desc;
 
 typedef struct {          /* SURVEY.md §5 failure detection: counts since the last update/reset */

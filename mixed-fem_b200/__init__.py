@@ -44,7 +44,7 @@ class _MeshDesc(C.Structure):
     _fields_ = [("elem_kind", C.c_int32), ("nV", C.c_int32), ("nE", C.c_int32),
                 ("T", C.POINTER(C.c_int32)), ("Vref", C.POINTER(C.c_double)), ("free_map", C.POINTER(C.c_int32)),
                 ("mat_id", C.POINTER(C.c_int32)), ("n_mat", C.c_int32), ("materials", C.POINTER(_Material)),
-                ("device", C.c_int32)]
+                ("device", C.c_int32), ("normals", C.POINTER(C.c_double)), ("thickness", C.c_double)]
 
 
 class _Status(C.Structure):
@@ -161,7 +161,8 @@ class MixedStretch:
 
     name = "mixed-stretch"   # src/variables/mixed_stretch.h:21-23
 
-    def __init__(self, V, T, free_map, materials, mat_id=None, device=0):
+    def __init__(self, V, T, free_map, materials, mat_id=None, device=0, normals=None, thickness=1e-3):
+        """normals (nE x 3) given => shell: TriMesh + MixedStretch<3> (src/mesh/tri_mesh.cpp), T is nE x 3, V is nV x 3."""
         self.L = lib()
         V = _f64(V)
         T = np.ascontiguousarray(T, dtype=np.int32)
@@ -176,7 +177,11 @@ class MixedStretch:
             mats[i].mu, mats[i].la = float(mu), float(la)
         mid = None if mat_id is None else np.ascontiguousarray(mat_id, dtype=np.int32)
         d = _MeshDesc()
-        d.elem_kind = 0 if self.dim == 3 else 1
+        self.shell = normals is not None
+        d.elem_kind = 2 if self.shell else (0 if self.dim == 3 else 1)
+        nrm = _f64(normals) if self.shell else None
+        d.normals = _dp(nrm) if self.shell else None
+        d.thickness = float(thickness)
         d.nV, d.nE = self.nV, self.nE
         d.T, d.Vref, d.free_map = _ip(T), _dp(V), _ip(fm)
         d.mat_id = _ip(mid) if mid is not None else None
@@ -349,7 +354,7 @@ class MixedStretch:
     def scatter_map(self):
         pm, ps = C.POINTER(C.c_int32)(), C.POINTER(C.c_int32)()
         self._check(self.L.mfb_scatter_map(self.h, C.byref(pm), C.byref(ps)))
-        npe = self.dim + 1
+        npe = 3 if self.shell else self.dim + 1
         m = np.ctypeslib.as_array(pm, shape=(self.nE, npe, npe)).copy()
         st = np.ctypeslib.as_array(ps, shape=(self.nE, npe)).copy()
         return m, st

@@ -86,7 +86,8 @@ extern "C" int mfb_reset(mfb_ctx* c, const double* x_or_null) {
   if (x_or_null) { int rc = upload_x(c, x_or_null); if (rc) return rc; xd = c->xdev.p; }
   else xd = c->vref.p;   // x = vec(V_^T) (mixed_stretch.cpp:314-317); row-major Vref is the same interleaving
   MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, c->stream));
-  if (c->dim == 3) k_reset<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), xd);
+  if (c->kind == MFB_SHELL) k_reset<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), xd);
+  else if (c->dim == 3) k_reset<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), xd);
   else k_reset<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), xd);
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
@@ -103,7 +104,9 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   if (!x_dev) return MFB_ERR_INVALID;
   cudaStream_t st = c->stream;
   const double h2 = dt * dt;
-  const bool v4 = c->dim == 3 && c->smem_b == 3;
+  if (c->kind == MFB_SHELL)   // rhs / solve / products re-form Jloc(x) from the positions of this update (TriMesh::update_jacobian)
+    MFB_CUDA(cudaMemcpyAsync(c->xupd.p, x_dev, (size_t)c->dim * c->nV * 8, cudaMemcpyDeviceToDevice, st));
+  const bool v4 = c->kind == MFB_TET && c->smem_b == 3;
   const bool bulk = v4 && c->asm_mode == 1;
   MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
   if (bulk) {
@@ -153,6 +156,9 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       else { k_update_tet_v4<false, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
       LAUNCHED(c, 1);
     }
+  } else if (c->kind == MFB_SHELL) {
+    if (c->fuse_rhs) k_update_shell<true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
+    else k_update_shell<false><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   } else if (c->dim == 3) {
     if (c->smem_b == 2) {
       static bool attr2_done = false;
@@ -184,7 +190,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   }
-  if (c->dim == 3 && c->nb > 0 && !bulk) {   // RED variants accumulate the upper triangle only
+  if (c->kind == MFB_TET && c->nb > 0 && !bulk) {   // RED variants accumulate the upper triangle only
     k_mirror_lower<<<nblk((int64_t)c->n_mirror * 9), 256, 0, st>>>(c->mirror.p, c->n_mirror, 3, c->Avals.p);
     LAUNCHED(c, 1);
   }
@@ -210,7 +216,8 @@ extern "C" int mfb_update(mfb_ctx* c, const double* x, double dt) {
 static int ensure_rhs(mfb_ctx* c) {
   if (c->rhs_valid) return MFB_OK;
   MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, (size_t)c->dim * c->nF * 8, c->stream));
-  if (c->dim == 3) k_rhs<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state());
+  if (c->kind == MFB_SHELL) k_rhs<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state());
+  else if (c->dim == 3) k_rhs<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state());
   else k_rhs<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state());
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
@@ -240,7 +247,8 @@ extern "C" int mfb_solve_dev(mfb_ctx* c, const double* dx_dev) {
   if (!dx_dev) return MFB_ERR_INVALID;
   int rc = ensure_rhs(c);   // solve() reads gl_, which rhs() produces (mixed_stretch.cpp:281)
   if (rc) return rc;
-  if (c->dim == 3) k_solve<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dx_dev);
+  if (c->kind == MFB_SHELL) k_solve<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dx_dev);
+  else if (c->dim == 3) k_solve<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dx_dev);
   else k_solve<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dx_dev);
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
@@ -284,7 +292,8 @@ extern "C" int mfb_energy_dev(mfb_ctx* c, const double* s_soa, double* e) {
   CHECK_CTX(c);
   if (!e) return MFB_ERR_INVALID;
   const double* sp = s_soa ? s_soa : c->s.p;
-  if (c->dim == 3) k_energy<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
+  if (c->kind == MFB_SHELL) k_energy<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
+  else if (c->dim == 3) k_energy<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
   else k_energy<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
@@ -301,7 +310,8 @@ extern "C" int mfb_constraint_value_dev(mfb_ctx* c, const double* x_dev, const d
   CHECK_CTX(c);
   if (!x_dev || !e) return MFB_ERR_INVALID;
   const double* sp = s_soa ? s_soa : c->s.p;
-  if (c->dim == 3) k_constraint<3, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
+  if (c->kind == MFB_SHELL) k_constraint<K_SHELL, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
+  else if (c->dim == 3) k_constraint<3, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
   else k_constraint<2, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
@@ -321,7 +331,8 @@ extern "C" int mfb_evaluate_constraint(mfb_ctx* c, const double* x, double* out)
   if (!x || !out) return MFB_ERR_INVALID;
   int rc = upload_x(c, x);
   if (rc) return rc;
-  if (c->dim == 3) k_constraint<3, true><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), c->xdev.p, c->s.p, nullptr, c->soa_tmp.p);
+  if (c->kind == MFB_SHELL) k_constraint<K_SHELL, true><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), c->xdev.p, c->s.p, nullptr, c->soa_tmp.p);
+  else if (c->dim == 3) k_constraint<3, true><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), c->xdev.p, c->s.p, nullptr, c->soa_tmp.p);
   else k_constraint<2, true><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), c->xdev.p, c->s.p, nullptr, c->soa_tmp.p);
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
@@ -360,7 +371,8 @@ extern "C" int mfb_product(mfb_ctx* c, int which, const double* x, double* out, 
     MFB_CUDA(cudaMemcpyAsync(stage.p, out, nEl * 8, cudaMemcpyHostToDevice, c->stream));
     k_aos_to_soa<<<nblk((int64_t)nEl), 256, 0, c->stream>>>(stage.p, c->soa_tmp2.p, c->N, c->nE, c->ld);
     o = c->soa_tmp2.p;
-    if (c->dim == 3) k_product<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, o);
+    if (c->kind == MFB_SHELL) k_product<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, o);
+    else if (c->dim == 3) k_product<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, o);
     else k_product<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, o);
     k_soa_to_aos<<<nblk((int64_t)nEl), 256, 0, c->stream>>>(o, stage.p, c->N, c->nE, c->ld);
     LAUNCHED(c, 3);
@@ -370,7 +382,8 @@ extern "C" int mfb_product(mfb_ctx* c, int which, const double* x, double* out, 
     mfb::DBuf<double> stage;
     rc = stage.alloc(nVx + 1); if (rc) return rc;
     MFB_CUDA(cudaMemcpyAsync(stage.p, out, nVx * 8, cudaMemcpyHostToDevice, c->stream));
-    if (c->dim == 3) k_product<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, stage.p);
+    if (c->kind == MFB_SHELL) k_product<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, stage.p);
+    else if (c->dim == 3) k_product<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, stage.p);
     else k_product<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), which, transposed, xin, stage.p);
     LAUNCHED(c, 1);
     MFB_CUDA(cudaMemcpyAsync(out, stage.p, nVx * 8, cudaMemcpyDeviceToHost, c->stream));

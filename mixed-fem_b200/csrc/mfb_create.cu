@@ -196,7 +196,7 @@ static int build_pattern(mfb_ctx* c) {
       if ((rc = c->mirror.alloc(c->n_mirror > 0 ? c->n_mirror : 1))) return rc;
       k_mirror_fill<<<nblk(nb), 256, 0, st>>>(c->blockptr.p, brow.p, c->bcol.p, c->bT.p, head.p, bid.p, nb, dim, c->mirror.p);
     }
-    if (dim == 3) {
+    if (c->kind == MFB_TET) {
       // v4 assembly: number the upper-triangle blocks, element->block map, finalize list
       DBuf<int> uflag, ub;
       if ((rc = uflag.alloc(nb)) || (rc = ub.alloc(nb)) || (rc = c->bmap.alloc((size_t)6 * c->ld)) || (rc = c->fcode.alloc(nb))) return rc;
@@ -243,14 +243,15 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
     g_last_error = "mfb_create: invalid descriptor";
     return MFB_ERR_INVALID;
   }
-  if (d->elem_kind != MFB_TET && d->elem_kind != MFB_TRI2D) { g_last_error = "unsupported elem_kind"; return MFB_ERR_UNSUPPORTED; }
+  if (d->elem_kind != MFB_TET && d->elem_kind != MFB_TRI2D && d->elem_kind != MFB_SHELL) { g_last_error = "unsupported elem_kind"; return MFB_ERR_UNSUPPORTED; }
+  if (d->elem_kind == MFB_SHELL && (!d->normals || !(d->thickness > 0))) { g_last_error = "MFB_SHELL needs per-face normals and a positive thickness"; return MFB_ERR_INVALID; }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     g_last_error = "no CUDA device visible: this library has no CPU fallback";
     return MFB_ERR_NO_DEVICE;
   }
   if (d->device < 0 || d->device >= ndev) { g_last_error = "bad device ordinal"; return MFB_ERR_INVALID; }
-  const int dim = d->elem_kind == MFB_TET ? 3 : 2;
+  const int dim = d->elem_kind == MFB_TRI2D ? 2 : 3;
   for (int i = 0; i < d->n_mat; ++i) {
     const int mdl = d->materials[i].model;
     if (mdl < 0 || mdl > 5) { g_last_error = "unknown material model"; return MFB_ERR_INVALID; }
@@ -262,7 +263,8 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   MFB_CUDA(cudaSetDevice(d->device));
   mfb_ctx* c = new mfb_ctx();
   c->device = d->device;
-  c->dim = dim; c->npe = dim + 1; c->N = dim == 3 ? 6 : 3; c->M = dim * dim; c->NP = c->N * (c->N + 1) / 2;
+  c->kind = d->elem_kind;
+  c->dim = dim; c->npe = d->elem_kind == MFB_TET ? 4 : 3; c->N = dim == 3 ? 6 : 3; c->M = dim * dim; c->NP = c->N * (c->N + 1) / 2;
   c->nV = d->nV; c->nE = d->nE;
   c->ld = ((int64_t)d->nE + 31) / 32 * 32;
   const int npe = c->npe, nE = c->nE;
@@ -273,7 +275,8 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
 
   // host precompute, component-major
   std::vector<int> hT((size_t)npe * ld, 0), hf((size_t)npe * ld, -1), hmat;
-  std::vector<double> hdphi((size_t)dim * dim * ld, 0.0), hvol((size_t)ld, 1.0);
+  std::vector<double> hdphi((size_t)dim * dim * ld, 0.0), hvol((size_t)ld, 1.0), hnrm;
+  if (d->elem_kind == MFB_SHELL) hnrm.assign((size_t)3 * ld, 0.0);
   for (int e = 0; e < nE; ++e) {
     const int32_t* t = &d->T[(size_t)e * npe];
     for (int k = 0; k < npe; ++k) {
@@ -281,7 +284,23 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
       hT[(size_t)k * ld + e] = t[k];
       hf[(size_t)k * ld + e] = d->free_map[t[k]];
     }
-    if (dim == 3) {
+    if (d->elem_kind == MFB_SHELL) {
+      // TriMesh: vol = |t0 x t1| thickness / 2 (tri_mesh.cpp:38-41); rows 1..2 of dphi = (T^T T)^-1 T^T, T = [t0 t1]
+      // (linear_tri3d_dphi_dX.cpp:5-17); components (k-1)*3 + c, k = 1, 2
+      const double* a = &d->Vref[3 * (size_t)t[0]]; const double* b = &d->Vref[3 * (size_t)t[1]]; const double* cc = &d->Vref[3 * (size_t)t[2]];
+      double t0[3], t1[3];
+      for (int l = 0; l < 3; ++l) { t0[l] = b[l] - a[l]; t1[l] = cc[l] - a[l]; }
+      const double cr[3] = {t0[1] * t1[2] - t0[2] * t1[1], t0[2] * t1[0] - t0[0] * t1[2], t0[0] * t1[1] - t0[1] * t1[0]};
+      hvol[e] = std::sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]) * (d->thickness / 2);
+      const double g00 = t0[0] * t0[0] + t0[1] * t0[1] + t0[2] * t0[2], g01 = t0[0] * t1[0] + t0[1] * t1[1] + t0[2] * t1[2],
+                   g11 = t1[0] * t1[0] + t1[1] * t1[1] + t1[2] * t1[2];
+      const double id = 1.0 / (g00 * g11 - g01 * g01);
+      for (int l = 0; l < 3; ++l) {
+        hdphi[(size_t)l * ld + e] = (g11 * id) * t0[l] + (-g01 * id) * t1[l];
+        hdphi[(size_t)(3 + l) * ld + e] = (-g01 * id) * t0[l] + (g00 * id) * t1[l];
+        hnrm[(size_t)l * ld + e] = d->normals[3 * (size_t)e + l];
+      }
+    } else if (dim == 3) {
       const double* a = &d->Vref[3 * (size_t)t[0]]; const double* b = &d->Vref[3 * (size_t)t[1]];
       const double* cc = &d->Vref[3 * (size_t)t[2]]; const double* dd = &d->Vref[3 * (size_t)t[3]];
       double ad[3], bd[3], cd[3];
@@ -315,6 +334,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
 #define TRY(x) do { rc = (x); if (rc) { delete c; return rc; } } while (0)
   { std::vector<double> hv(d->Vref, d->Vref + (size_t)dim * d->nV); TRY(upload(c->vref, hv, st)); MFB_CUDA(cudaStreamSynchronize(st)); }
   TRY(upload(c->T, hT, st)); TRY(upload(c->fidx, hf, st)); TRY(upload(c->dphi, hdphi, st)); TRY(upload(c->vol, hvol, st));
+  if (d->elem_kind == MFB_SHELL) { TRY(upload(c->nrest, hnrm, st)); TRY(c->xupd.alloc((size_t)3 * d->nV)); MFB_CUDA(cudaMemcpyAsync(c->xupd.p, c->vref.p, (size_t)3 * d->nV * 8, cudaMemcpyDeviceToDevice, st)); }
   if (d->mat_id) {
     hmat.assign((size_t)ld, 0);
     for (int e = 0; e < nE; ++e) {
@@ -330,10 +350,10 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   const size_t N = c->N, M = c->M, NP = c->NP;
   TRY(c->R.alloc(M * ld)); TRY(c->s.alloc(N * ld)); TRY(c->la.alloc(N * ld)); TRY(c->ds.alloc(N * ld)); TRY(c->S.alloc(N * ld));
   TRY(c->dSdF.alloc(M * N * ld)); TRY(c->g.alloc(N * ld)); TRY(c->H.alloc(NP * ld)); TRY(c->Hinv.alloc(NP * ld));
-  if (dim == 3) TRY(c->Lfac.alloc(NP * ld));
+  if (c->kind == MFB_TET) TRY(c->Lfac.alloc(NP * ld));
   TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
-  if (dim == 3) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 16)); TRY(c->gxrh.alloc((size_t)6 * nF + 8)); TRY(c->slow_list.alloc((size_t)nE + 1)); }
+  if (c->kind == MFB_TET) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 16)); TRY(c->gxrh.alloc((size_t)6 * nF + 8)); TRY(c->slow_list.alloc((size_t)nE + 1)); }
   TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));
   TRY(c->partials.alloc((size_t)c->grid() + 1024)); TRY(c->scal.alloc(16));
   TRY(c->soa_tmp.alloc(N * ld)); TRY(c->soa_tmp2.alloc(N * ld));

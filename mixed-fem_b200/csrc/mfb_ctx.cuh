@@ -7,6 +7,7 @@
 #include "../../include/mfem_b200.h"
 #include "mfb_kernels2.cuh"
 #include "mfb_kernels4.cuh"
+#include "mfb_kernels5.cuh"
 
 namespace mfb {
 
@@ -42,6 +43,7 @@ struct DBuf {   // plain device buffer
 struct mfb_ctx {
   int device = 0;
   cudaStream_t stream = 0;
+  int kind = 0;               // mfb_elem
   int dim = 3, npe = 4, N = 6, M = 9, NP = 21;
   int nV = 0, nE = 0, nF = 0, nb = 0;
   int64_t ld = 0, nnz = 0;
@@ -52,7 +54,7 @@ struct mfb_ctx {
   int asm_mode = 1;     // v4 assembly: 1 = warp-cooperative coalesced RED into the block-CSR upper triangle, 0 = FP64 RED into the scalar CSR
   // mesh (device)
   mfb::DBuf<int> T, fidx, matid, smap, sstride;
-  mfb::DBuf<double> dphi, vol, vref;
+  mfb::DBuf<double> dphi, vol, vref, nrest, xupd;   // xupd: shells, positions of the last update()
   mfb::DBuf<mfb::MaterialDev> mats;
   // CSR structure (device)
   mfb::DBuf<int> blockptr, brow, bcol, bT, diagblk, outer, inner;
@@ -89,6 +91,7 @@ struct mfb_ctx {
     m.dim = dim; m.npe = npe; m.nV = nV; m.nE = nE; m.nF = nF; m.ld = ld;
     m.T = T.p; m.fidx = fidx.p; m.dphi = dphi.p; m.vol = vol.p; m.matid = matid.p; m.mats = mats.p;
     m.smap = smap.p; m.sstride = sstride.p;
+    m.nrest = nrest.p; m.xlast = xupd.p;
     return m;
   }
   mfb::DevState state() const {

@@ -24,6 +24,8 @@ struct DevMesh {
   const MaterialDev* mats;
   const int* smap;       // [npe*npe][ld]  value index of entry (0,0) of block (j,k), -1 if pinned
   const int* sstride;    // [npe][ld]      CSR row length of block-row j
+  const double* nrest;   // [3][ld]        shells: rest normal of the face (TriMesh::N_), else nullptr
+  const double* xlast;   // shells: positions of the last update (their local Jacobian depends on x), else nullptr
 };
 
 struct DevState {

@@ -5,16 +5,95 @@
 
 namespace mfb {
 
-template <int DIM> struct Dims { static constexpr int N = DIM == 3 ? 6 : 3, M = DIM * DIM, NPE = DIM + 1, NP = N * (N + 1) / 2; };
+// Element kinds as template values: 3 = tetrahedra (TetrahedralMesh), 2 = 2D triangles (Tri2DMesh), K_SHELL = triangles in
+// 3D with a rest normal (TriMesh, src/mesh/tri_mesh.cpp).  SD = space dimension, NPE = vertices per element.
+constexpr int K_SHELL = 5;
+template <int DIM> struct Dims {
+  static constexpr int SD = DIM == 2 ? 2 : 3, N = SD == 3 ? 6 : 3, M = SD * SD, NPE = DIM == 3 ? 4 : 3, NP = N * (N + 1) / 2;
+};
 
 template <int DIM>
-__device__ __forceinline__ double symw(int k) { return k < DIM ? 1.0 : 2.0; }
+__device__ __forceinline__ double symw(int k) { return k < Dims<DIM>::SD ? 1.0 : 2.0; }
 template <int DIM>
-__device__ __forceinline__ double syminvw(int k) { return k < DIM ? 1.0 : 0.5; }
+__device__ __forceinline__ double syminvw(int k) { return k < Dims<DIM>::SD ? 1.0 : 0.5; }
+
+// ---- shells: F = J0 x + n(x) (x) N, Jloc = Jloc0 + N (I - n n^T) dn_dq / |v1 x v2|  (tri_mesh.cpp:104-190).
+// dphi rows 1..2 are stored (6 components: (k-1)*3 + c), row 0 = -(row1 + row2); Nr = rest normal of the face.
+struct ShellGeo { double dphi[6], Nr[3], v1[3], v2[3], n[3], il; };
+__device__ __forceinline__ void shell_geo(const DevMesh& m, int e, const double* __restrict__ x, ShellGeo& g) {
+  const int64_t ld = m.ld;
+  int v[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) v[k] = m.T[k * ld + e];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) g.dphi[i] = m.dphi[i * ld + e];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) g.Nr[i] = m.nrest[i * ld + e];
+#pragma unroll
+  for (int l = 0; l < 3; ++l) {
+    const double x0 = __ldg(&x[3 * (int64_t)v[0] + l]);
+    g.v1[l] = __ldg(&x[3 * (int64_t)v[1] + l]) - x0;
+    g.v2[l] = __ldg(&x[3 * (int64_t)v[2] + l]) - x0;
+  }
+  cross3(g.v1, g.v2, g.n);
+  const double len = sqrt(g.n[0] * g.n[0] + g.n[1] * g.n[1] + g.n[2] * g.n[2]);
+  g.il = 1.0 / len;
+#pragma unroll
+  for (int l = 0; l < 3; ++l) g.n[l] *= g.il;
+}
+__device__ __forceinline__ void shell_F(const ShellGeo& g, double* F) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) F[3 * c + r] = g.v1[r] * g.dphi[c] + g.v2[r] * g.dphi[3 + c] + g.n[r] * g.Nr[c];
+}
+// Jloc^T t for the 9-vector t: contributions a1, a2 to vertices 1, 2 (vertex 0 gets -(a1 + a2))
+__device__ __forceinline__ void shell_JT(const ShellGeo& g, const double* t, double* a1, double* a2) {
+  double w[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    a1[r] = g.dphi[0] * t[r] + g.dphi[1] * t[3 + r] + g.dphi[2] * t[6 + r];
+    a2[r] = g.dphi[3] * t[r] + g.dphi[4] * t[3 + r] + g.dphi[5] * t[6 + r];
+    w[r] = g.Nr[0] * t[r] + g.Nr[1] * t[3 + r] + g.Nr[2] * t[6 + r];
+  }
+  const double nw = g.n[0] * w[0] + g.n[1] * w[1] + g.n[2] * w[2];
+  double z[3], c1[3], c2[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) z[r] = (w[r] - g.n[r] * nw) * g.il;
+  cross3(g.v2, z, c1);      // (-[v2]x)^T z
+  cross3(g.v1, z, c2);      // ([v1]x)^T z = -(v1 x z)
+#pragma unroll
+  for (int r = 0; r < 3; ++r) { a1[r] += c1[r]; a2[r] -= c2[r]; }
+}
+// Jloc d for vertex displacements d0, d1, d2 -> 9-vector
+__device__ __forceinline__ void shell_J(const ShellGeo& g, const double* d0, const double* d1, const double* d2, double* out) {
+  double e1[3], e2[3], q1[3], q2[3], a[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) { e1[r] = d1[r] - d0[r]; e2[r] = d2[r] - d0[r]; }
+  cross3(g.v2, e1, q1);     // v2 x (d1 - d0)  -> enters with a minus sign
+  cross3(g.v1, e2, q2);     // v1 x (d2 - d0)
+#pragma unroll
+  for (int r = 0; r < 3; ++r) a[r] = q2[r] - q1[r];
+  const double na = g.n[0] * a[0] + g.n[1] * a[1] + g.n[2] * a[2];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) a[r] = (a[r] - g.n[r] * na) * g.il;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) out[3 * c + r] = g.dphi[c] * e1[r] + g.dphi[3 + c] * e2[r] + g.Nr[c] * a[r];
+}
 
 // F for either element kind; dphi gets the d*d stored rows
 template <int DIM>
 __device__ __forceinline__ void elem_F(const DevMesh& m, int e, const double* __restrict__ x, double* dphi, double* F) {
+  if constexpr (DIM == K_SHELL) {
+    ShellGeo g;
+    shell_geo(m, e, x, g);
+    shell_F(g, F);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) dphi[i] = i < 6 ? g.dphi[i] : 0.0;
+    return;
+  } else {
   const int64_t ld = m.ld;
   int v[DIM + 1];
 #pragma unroll
@@ -37,12 +116,13 @@ __device__ __forceinline__ void elem_F(const DevMesh& m, int e, const double* __
       for (int k = 0; k < DIM; ++k) a += dx[DIM * k + r] * dphi[DIM * k + c];
       F[DIM * c + r] = a;
     }
+  }
 }
 
 // polar without gradients from a given R (3D warm start; 2D closed form ignores R): stretch vector only
 template <int DIM>
 __device__ __forceinline__ void polar_stretch(double* R, const double* F, double* S, int* status, int* iters) {
-  if constexpr (DIM == 3) {
+  if constexpr (Dims<DIM>::SD == 3) {
     double Y[9];
     *iters = procrustes3(R, F, Y, 1e-6, 100, status);
     stretch6(R, F, S);
@@ -56,6 +136,20 @@ __device__ __forceinline__ void polar_stretch(double* R, const double* F, double
 // scatter  sign * vol * Jloc^T t  into a free-vertex vector (t is the M-vector of an element)
 template <int DIM>
 __device__ __forceinline__ void scatter_vertex(const DevMesh& m, int e, const double* dphi, const double* t, double scale, double* out) {
+  if constexpr (DIM == K_SHELL) {   // Jloc depends on the positions of the last update (m.xlast)
+    ShellGeo g;
+    shell_geo(m, e, m.xlast, g);
+    double a1[3], a2[3];
+    shell_JT(g, t, a1, a2);
+    const int f0 = m.fidx[e], f1 = m.fidx[m.ld + e], f2 = m.fidx[2 * m.ld + e];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      if (f1 >= 0) red_add(&out[3 * (int64_t)f1 + r], scale * a1[r]);
+      if (f2 >= 0) red_add(&out[3 * (int64_t)f2 + r], scale * a2[r]);
+      if (f0 >= 0) red_add(&out[3 * (int64_t)f0 + r], -scale * (a1[r] + a2[r]));
+    }
+    return;
+  } else {
   const int64_t ld = m.ld;
   double v0[DIM];
 #pragma unroll
@@ -78,11 +172,27 @@ __device__ __forceinline__ void scatter_vertex(const DevMesh& m, int e, const do
 #pragma unroll
     for (int r = 0; r < DIM; ++r) red_add(&out[DIM * (int64_t)f0 + r], v0[r]);
   }
+  }
 }
 
 // (PJW^T dx)_e : M-vector, = vol * sum_k dphi(k,c) dx[f_k][r] over free vertices
 template <int DIM>
 __device__ __forceinline__ void gather_Jdx(const DevMesh& m, int e, const double* __restrict__ dx, double vol, double* Jdx) {
+  if constexpr (DIM == K_SHELL) {
+    ShellGeo g;
+    shell_geo(m, e, m.xlast, g);
+    double d[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int f = m.fidx[k * m.ld + e];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) d[k][r] = (f >= 0) ? __ldg(&dx[3 * (int64_t)f + r]) : 0.0;
+    }
+    shell_J(g, d[0], d[1], d[2], Jdx);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) Jdx[i] *= vol;
+    return;
+  } else {
   const int64_t ld = m.ld;
   double d[DIM + 1][DIM], dp[DIM * DIM];
 #pragma unroll
@@ -106,6 +216,7 @@ __device__ __forceinline__ void gather_Jdx(const DevMesh& m, int e, const double
       Jdx[DIM * c + r] = vol * a;
     }
   }
+  }
 }
 
 // reset()  mixed_stretch.cpp:294-338 : R = I, polar with gradients, s_ = S_, la_ = 0, H_ = Hinv_ = I, g_ = 0
@@ -121,8 +232,8 @@ __global__ void __launch_bounds__(128) k_reset(DevMesh m, DevState st, const dou
 #pragma unroll
   for (int i = 0; i < D::M; ++i) R[i] = 0.0;
 #pragma unroll
-  for (int i = 0; i < DIM; ++i) R[i * DIM + i] = 1.0;
-  if constexpr (DIM == 3) {
+  for (int i = 0; i < D::SD; ++i) R[i * D::SD + i] = 1.0;
+  if constexpr (D::SD == 3) {
     double Y[9], Hinv3[6];
     iters = procrustes3(R, F, Y, 1e-6, 100, &status);
     stretch6(R, F, S);
@@ -276,7 +387,7 @@ __global__ void __launch_bounds__(128) k_energy(DevMesh m, const double* __restr
 #pragma unroll
     for (int k = 0; k < D::N; ++k) s[k] = s_soa[k * m.ld + e];
     const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
-    const double psi = (DIM == 3) ? material_energy6(mat.model, mat.mu, mat.la, s) : material_energy3(mat.model, mat.mu, mat.la, s);
+    const double psi = (D::SD == 3) ? material_energy6(mat.model, mat.mu, mat.la, s) : material_energy3(mat.model, mat.mu, mat.la, s);
     val = psi * m.vol[e];
   }
   const double r = block_sum_128(val, sh);

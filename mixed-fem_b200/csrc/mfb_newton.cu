@@ -186,6 +186,7 @@ static mfb_newton_state* nstate(mfb_ctx* c) { return (mfb_newton_state*)c->newto
 extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0) {
   CHECK_CTX(c);
   if (!free_map || !(h > 0) || !(density > 0)) { g_last_error = "mfb_newton_init: bad arguments"; return MFB_ERR_INVALID; }
+  if (c->kind == MFB_SHELL) { g_last_error = "mfb_newton_*: shells (TriMesh) are not wired into the device-resident time step yet"; return MFB_ERR_UNSUPPORTED; }
   if (c->newton) { delete nstate(c); c->newton = nullptr; }
   mfb_newton_state* s = new mfb_newton_state();
   c->newton = s;

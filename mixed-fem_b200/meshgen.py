@@ -78,6 +78,23 @@ def tri_grid(nx, ny, h=None):
     return V, T
 
 
+def shell_grid(nx, ny, h=None, bump=0.15):
+    """Cloth-like sheet for the TriMesh / shell path (config C5): the tri_grid in the x-z plane of 3D space with a
+    smooth out-of-plane bump so face normals vary.  Returns V (nV,3), T (nE,3), per-face unit rest normals N (nE,3)."""
+    V2, T = tri_grid(nx, ny, h)
+    L = max(V2[:, 0].max(), 1e-300)
+    y = bump * L * np.sin(np.pi * V2[:, 0] / L) * np.cos(0.5 * np.pi * V2[:, 1] / L)
+    V = np.stack([V2[:, 0], y, V2[:, 1]], axis=1)
+    return V, T, face_normals(V, T)
+
+
+def face_normals(V, T):
+    e1 = V[T[:, 1]] - V[T[:, 0]]
+    e2 = V[T[:, 2]] - V[T[:, 0]]
+    n = np.cross(e1, e2)
+    return n / np.linalg.norm(n, axis=1, keepdims=True)
+
+
 def pinned_free_map(V, ratio=0.01, axis=0):
     """free_map (nV,) int32: -1 for vertices with coord < min + ratio*range along `axis`, else ascending free id."""
     lo, hi = V[:, axis].min(), V[:, axis].max()

@@ -143,11 +143,17 @@ struct Mesh {
   std::vector<int> mat_id;       // nE
   std::vector<Material> mats;
   int nfree = 0;
+  // shells (TriMesh, src/mesh/tri_mesh.cpp): triangles in 3D, dim = 3, npe = 3
+  bool shell = false;
+  double thickness = 1e-3;
+  std::vector<double> Nrest;     // nE x 3 per-face rest normals (TriMesh::N_)
+  std::vector<double> Jloc0, Jloc;   // nE x (9 x 9), column-major: entry (row j, column 3k+l) at [ (3k+l)*9 + j ]
 
   void init() {
     nfree = 0;
     for (int v : free_map) nfree = std::max(nfree, v + 1);
     vols.resize(nE); dphi.resize((size_t)nE * npe * dim);
+    if (shell) { init_shell(); return; }
     for (int e = 0; e < nE; ++e) {
       const int* t = &T[(size_t)e * npe];
       if (dim == 3) {
@@ -188,6 +194,64 @@ struct Mesh {
       }
     }
   }
+  // TriMesh ctor / volumes / init_jacobian  (tri_mesh.cpp:31-41,71-102 ; linear_tri3d_dphi_dX.cpp:5-17)
+  void init_shell() {
+    Jloc0.assign((size_t)nE * 81, 0.0);
+    for (int e = 0; e < nE; ++e) {
+      const int* t = &T[(size_t)e * 3];
+      const double* a = &Vref[3 * t[0]]; const double* b = &Vref[3 * t[1]]; const double* c = &Vref[3 * t[2]];
+      double t0[3], t1[3];
+      for (int l = 0; l < 3; ++l) { t0[l] = b[l] - a[l]; t1[l] = c[l] - a[l]; }
+      // igl::doublearea (3D) = |t0 x t1| ; volumes = doublearea * thickness / 2
+      const double cr[3] = {t0[1] * t1[2] - t0[2] * t1[1], t0[2] * t1[0] - t0[0] * t1[2], t0[0] * t1[1] - t0[1] * t1[0]};
+      vols[e] = std::sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]) * (thickness / 2);
+      // rows 1..2 of dphi = (T^T T)^-1 T^T with T = [t0 t1] (3 x 2), row 0 = -column sums
+      const double g00 = t0[0] * t0[0] + t0[1] * t0[1] + t0[2] * t0[2], g01 = t0[0] * t1[0] + t0[1] * t1[1] + t0[2] * t1[2],
+                   g11 = t1[0] * t1[0] + t1[1] * t1[1] + t1[2] * t1[2];
+      const double det = g00 * g11 - g01 * g01, id = 1.0 / det;
+      double* P = &dphi[(size_t)e * 9];
+      for (int l = 0; l < 3; ++l) {
+        P[3 + l] = (g11 * id) * t0[l] + (-g01 * id) * t1[l];
+        P[6 + l] = (-g01 * id) * t0[l] + (g00 * id) * t1[l];
+        P[l] = -(P[3 + l] + P[6 + l]);
+      }
+      double* J = &Jloc0[(size_t)e * 81];
+      for (int k = 0; k < 3; ++k) for (int cc = 0; cc < 3; ++cc) for (int r = 0; r < 3; ++r) J[(3 * k + r) * 9 + 3 * cc + r] = P[k * 3 + cc];
+    }
+    Jloc = Jloc0;
+  }
+  // TriMesh::update_jacobian (tri_mesh.cpp:128-190): Jloc = Jloc0 + N (I - n n^T) dn_dq / |v1 x v2|
+  void update_jacobian(const double* x) {
+    if (!shell) return;
+    #pragma omp parallel for
+    for (int e = 0; e < nE; ++e) {
+      const int* t = &T[(size_t)e * 3];
+      double v1[3], v2[3];
+      for (int l = 0; l < 3; ++l) { v1[l] = x[3 * t[1] + l] - x[3 * t[0] + l]; v2[l] = x[3 * t[2] + l] - x[3 * t[0] + l]; }
+      double n[3] = {v1[1] * v2[2] - v1[2] * v2[1], v1[2] * v2[0] - v1[0] * v2[2], v1[0] * v2[1] - v1[1] * v2[0]};
+      const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+      for (int l = 0; l < 3; ++l) n[l] /= len;
+      auto crossmat = [](const double* v, double* m) {   // row-major 3x3
+        m[0] = 0; m[1] = -v[2]; m[2] = v[1]; m[3] = v[2]; m[4] = 0; m[5] = -v[0]; m[6] = -v[1]; m[7] = v[0]; m[8] = 0; };
+      double dx1[9], dx2[9], dn[27];   // dn: 3 x 9 row-major
+      crossmat(v1, dx1); crossmat(v2, dx2);
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) {
+        dn[r * 9 + c] = dx2[r * 3 + c] - dx1[r * 3 + c];
+        dn[r * 9 + 3 + c] = -dx2[r * 3 + c];
+        dn[r * 9 + 6 + c] = dx1[r * 3 + c];
+      }
+      double Pn[9];
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) Pn[r * 3 + c] = (r == c ? 1.0 : 0.0) - n[r] * n[c];
+      double PD[27];   // (I - n n^T) dn_dq / l
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 9; ++c) { double a = 0; for (int k = 0; k < 3; ++k) a += Pn[r * 3 + k] * dn[k * 9 + c]; PD[r * 9 + c] = a / len; }
+      const double* Nr = &Nrest[(size_t)e * 3];
+      const double* J0 = &Jloc0[(size_t)e * 81];
+      double* J = &Jloc[(size_t)e * 81];
+      // N (9 x 3): row 3c + r has N_c in column r
+      for (int col = 0; col < 9; ++col) for (int cc = 0; cc < 3; ++cc) for (int r = 0; r < 3; ++r)
+        J[col * 9 + 3 * cc + r] = J0[col * 9 + 3 * cc + r] + Nr[cc] * PD[r * 9 + col];
+    }
+  }
   static M3 inverse33(const M3& A) {  // EigenTypes.h:105-120
     const double det = A(0, 0) * (A(1, 1) * A(2, 2) - A(2, 1) * A(1, 2)) - A(0, 1) * (A(1, 0) * A(2, 2) - A(1, 2) * A(2, 0)) +
                        A(0, 2) * (A(1, 0) * A(2, 1) - A(1, 1) * A(2, 0));
@@ -222,6 +286,13 @@ struct Mesh {
           for (int kk = 0; kk < npe; ++kk) { const int k = order[kk]; s += P[k * dim + c] * x[dim * t[k] + r]; }
           F[(size_t)M * e + dim * c + r] = s;
         }
+      if (shell) {    // F += n(x) (x) N  (tri_mesh.cpp:104-126)
+        double v1[3], v2[3];
+        for (int l = 0; l < 3; ++l) { v1[l] = x[3 * t[1] + l] - x[3 * t[0] + l]; v2[l] = x[3 * t[2] + l] - x[3 * t[0] + l]; }
+        double n[3] = {v1[1] * v2[2] - v1[2] * v2[1], v1[2] * v2[0] - v1[0] * v2[2], v1[0] * v2[1] - v1[1] * v2[0]};
+        const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        for (int c = 0; c < 3; ++c) for (int r = 0; r < 3; ++r) F[(size_t)9 * e + 3 * c + r] += Nrest[(size_t)3 * e + c] * (n[r] / len);
+      }
     }
   }
   // out (dim*nfree) = PJW_ * tmp   (PJW_ = P J^T W, mesh.cpp:63) ; tmp is M*nE
@@ -236,7 +307,8 @@ struct Mesh {
         if (f < 0) continue;
         for (int r = 0; r < dim; ++r) {
           double s = 0;
-          for (int c = 0; c < dim; ++c) s += P[k * dim + c] * tmp[(size_t)M * e + dim * c + r];
+          if (shell) { const double* J = &Jloc[(size_t)e * 81 + (3 * k + r) * 9]; for (int j = 0; j < 9; ++j) s += J[j] * tmp[(size_t)9 * e + j]; }
+          else for (int c = 0; c < dim; ++c) s += P[k * dim + c] * tmp[(size_t)M * e + dim * c + r];
           out[(size_t)dim * f + r] += sign * vols[e] * s;
         }
       }
@@ -250,6 +322,14 @@ struct Mesh {
     for (int e = 0; e < nE; ++e) {
       const int* t = &T[(size_t)e * npe];
       const double* P = &dphi[(size_t)e * npe * dim];
+      if (shell) {
+        for (int j = 0; j < 9; ++j) {
+          double s = 0;
+          for (int k = 0; k < 3; ++k) { const int f = free_map[t[k]]; if (f >= 0) for (int l = 0; l < 3; ++l) s += Jloc[(size_t)e * 81 + (3 * k + l) * 9 + j] * dx[(size_t)3 * f + l]; }
+          out[(size_t)9 * e + j] = vols[e] * s;
+        }
+        continue;
+      }
       for (int c = 0; c < dim; ++c)
         for (int r = 0; r < dim; ++r) {
           double s = 0;
@@ -265,8 +345,8 @@ template <int DIM>
 struct MixedStretch {
   static constexpr int N = DIM == 3 ? 6 : 3;
   static constexpr int M = DIM * DIM;
-  static constexpr int NPE = DIM + 1;
-  static constexpr int LD = DIM * NPE;
+  static constexpr int NPEMAX = DIM + 1;
+  static constexpr int LDMAX = DIM * NPEMAX;
   Mesh* mesh = nullptr;
   int nelem = 0;
   std::vector<double> s, ds, la, rhs_, grad, grad_x, grad_la, gl, Jdx, evals;
@@ -323,11 +403,11 @@ struct MixedStretch {
     s.assign((size_t)N * nelem, 0); ds.assign((size_t)N * nelem, 0); la.assign((size_t)N * nelem, 0);
     R.assign((size_t)M * nelem, 0); S.assign((size_t)N * nelem, 0); H.assign((size_t)N * N * nelem, 0);
     g.assign((size_t)N * nelem, 0); dSdF.assign((size_t)M * N * nelem, 0); Hinv.assign((size_t)N * N * nelem, 0);
-    Hloc.assign((size_t)N * N * nelem, 0); Aloc.assign((size_t)LD * LD * nelem, 0); evals.assign(nelem, 0);
+    Hloc.assign((size_t)N * N * nelem, 0); Aloc.assign((size_t)(DIM * mesh->npe) * (DIM * mesh->npe) * nelem, 0); evals.assign(nelem, 0);
     gl.assign((size_t)N * nelem, 0); grad_la.assign((size_t)N * nelem, 0); grad.assign((size_t)N * nelem, 0);
     iters.assign(nelem, 0);
     assembler = Assembler();
-    assembler.init(mesh->T.data(), mesh->nE, NPE, DIM, mesh->free_map);
+    assembler.init(mesh->T.data(), mesh->nE, mesh->npe, DIM, mesh->free_map);
     for (int i = 0; i < nelem; ++i) for (int k = 0; k < N; ++k) { H[(size_t)i * N * N + k * N + k] = 1.0; Hinv[(size_t)i * N * N + k * N + k] = 1.0; }
     std::vector<double> def_grad;
     mesh->deformation_gradient(mesh->Vref.data(), def_grad);   // x = vec(V^T): interleaved == row-major V
@@ -435,11 +515,13 @@ struct MixedStretch {
       double K[M * M];
       for (int c = 0; c < M; ++c) for (int r = 0; r < M; ++r) { double a = 0; for (int k = 0; k < N; ++k) a += DH[k * M + r] * D[k * M + c]; K[c * M + r] = a; }
       // Jloc (M x LD): entry (DIM*c + r, DIM*k + l) = delta_rl * dphi(k,c)   (tet_mesh.cpp:17-27)
+      const int NPE = mesh->npe, LD = DIM * NPE;
       const double* P = &mesh->dphi[(size_t)i * NPE * DIM];
-      double Jl[M * LD];
+      double Jl[M * LDMAX];
       for (int q = 0; q < M * LD; ++q) Jl[q] = 0;
-      for (int k = 0; k < NPE; ++k) for (int c = 0; c < DIM; ++c) for (int r = 0; r < DIM; ++r) Jl[(DIM * k + r) * M + DIM * c + r] = P[k * DIM + c];
-      double KJ[M * LD];
+      if (mesh->shell) { for (int q = 0; q < 81; ++q) Jl[q] = mesh->Jloc[(size_t)i * 81 + q]; }   // TriMesh::local_jacobians()
+      else for (int k = 0; k < NPE; ++k) for (int c = 0; c < DIM; ++c) for (int r = 0; r < DIM; ++r) Jl[(DIM * k + r) * M + DIM * c + r] = P[k * DIM + c];
+      double KJ[M * LDMAX];
       for (int c = 0; c < LD; ++c) for (int r = 0; r < M; ++r) { double a = 0; for (int k = 0; k < M; ++k) a += K[k * M + r] * Jl[c * M + k]; KJ[c * M + r] = a; }
       double* A = &Aloc[(size_t)LD * LD * i];
       for (int c = 0; c < LD; ++c) for (int r = 0; r < LD; ++r) { double a = 0; for (int k = 0; k < M; ++k) a += Jl[r * M + k] * KJ[c * M + k]; A[c * LD + r] = a * (vol * vol); }
@@ -462,6 +544,7 @@ struct MixedStretch {
   }
   // update()   mixed_stretch.cpp:158-164
   void update(const double* x, double dt) {
+    mesh->update_jacobian(x);      // shells only: NewtonOptimizer::update_system does this before var->update (newton_optimizer.cpp:119-121)
     update_rotations(x);
     update_derivatives(dt);
     evaluate_constraint(x, grad_la);
@@ -558,6 +641,24 @@ void* orc_create(int dim, int nV, int nE, const int32_t* T, const double* Vref, 
   m.dim = dim; m.npe = dim + 1; m.nV = nV; m.nE = nE;
   m.T.assign(T, T + (size_t)nE * (dim + 1));
   m.Vref.assign(Vref, Vref + (size_t)nV * dim);
+  m.free_map.assign(free_map, free_map + nV);
+  m.mat_id.assign(nE, 0);
+  if (mat_id) m.mat_id.assign(mat_id, mat_id + nE);
+  for (int i = 0; i < n_mat; ++i) m.mats.push_back(Material{mats[i].model, mats[i].mu, mats[i].la});
+  m.init();
+  c->v3.mesh = &c->mesh; c->v2.mesh = &c->mesh;
+  return c;
+}
+// TriMesh + MixedStretch<3> (tri_mesh.cpp): triangles in 3D with per-face rest normals and a thickness
+void* orc_create_shell(int nV, int nE, const int32_t* T, const double* Vref, const int32_t* free_map, const double* normals, double thickness,
+                       const int32_t* mat_id, int n_mat, const orc_material* mats) {
+  Ctx* c = new Ctx();
+  c->dim = 3;
+  Mesh& m = c->mesh;
+  m.dim = 3; m.npe = 3; m.nV = nV; m.nE = nE; m.shell = true; m.thickness = thickness;
+  m.T.assign(T, T + (size_t)nE * 3);
+  m.Vref.assign(Vref, Vref + (size_t)nV * 3);
+  m.Nrest.assign(normals, normals + (size_t)nE * 3);
   m.free_map.assign(free_map, free_map + nV);
   m.mat_id.assign(nE, 0);
   if (mat_id) m.mat_id.assign(mat_id, mat_id + nE);

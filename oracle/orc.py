@@ -43,6 +43,8 @@ def lib(path=None):
     ip = C.POINTER(C.c_int32)
     L.orc_create.restype = C.c_void_p
     L.orc_create.argtypes = [C.c_int, C.c_int, C.c_int, ip, dp, ip, ip, C.c_int, C.POINTER(_Mat)]
+    L.orc_create_shell.restype = C.c_void_p
+    L.orc_create_shell.argtypes = [C.c_int, C.c_int, ip, dp, ip, dp, C.c_double, ip, C.c_int, C.POINTER(_Mat)]
     L.orc_destroy.argtypes = [C.c_void_p]
     L.orc_reset.argtypes = [C.c_void_p]
     L.orc_update.argtypes = [C.c_void_p, dp, C.c_double]
@@ -102,10 +104,12 @@ TIMER_KEYS = ("rotations", "derivatives", "Aloc", "assemble", "rhs", "solve", "e
 class OracleMixedStretch:
     """CPU MixedStretch<DIM> (src/variables/mixed_stretch.h:12-164) over plain numpy arrays."""
 
-    def __init__(self, V, T, free_map, materials, mat_id=None, libpath=None):
+    def __init__(self, V, T, free_map, materials, mat_id=None, libpath=None, normals=None, thickness=1e-3):
+        """normals given (nE x 3) => shell: TriMesh + MixedStretch<3> (src/mesh/tri_mesh.cpp), T is nE x 3, V is nV x 3."""
         self.L = lib(libpath)
         V = _f64(V)
         T = np.ascontiguousarray(T, dtype=np.int32)
+        self.shell = normals is not None
         self.dim = V.shape[1]
         self.nV, self.nE = V.shape[0], T.shape[0]
         self.N = 6 if self.dim == 3 else 3
@@ -117,8 +121,14 @@ class OracleMixedStretch:
             mats[i].mu, mats[i].la = float(mu), float(la)
         mid = None if mat_id is None else np.ascontiguousarray(mat_id, dtype=np.int32)
         self._keep = (V, T, fm, mid)
-        self.h = self.L.orc_create(self.dim, self.nV, self.nE, _ip(T), _dp(V), _ip(fm),
-                                   _ip(mid) if mid is not None else None, len(materials), mats)
+        if self.shell:
+            nrm = _f64(normals)
+            self._keep += (nrm,)
+            self.h = self.L.orc_create_shell(self.nV, self.nE, _ip(T), _dp(V), _ip(fm), _dp(nrm), float(thickness),
+                                             _ip(mid) if mid is not None else None, len(materials), mats)
+        else:
+            self.h = self.L.orc_create(self.dim, self.nV, self.nE, _ip(T), _dp(V), _ip(fm),
+                                       _ip(mid) if mid is not None else None, len(materials), mats)
         self.nfree = self.L.orc_nfree(self.h)
 
     def __del__(self):
@@ -198,7 +208,7 @@ class OracleMixedStretch:
         return outer, inner, vals
 
     def scatter_map(self):
-        npe = self.dim + 1
+        npe = 3 if self.shell else self.dim + 1
         m = np.empty((self.nE, npe, npe), dtype=np.int32)
         st = np.empty((self.nE, npe), dtype=np.int32)
         self.L.orc_scatter_map(self.h, _ip(m), _ip(st))

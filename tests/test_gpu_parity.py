@@ -222,3 +222,56 @@ def test_unsupported_2d_material_is_an_error(built):
     V, T, fm, h = mesh(2, (4, 4, 0))
     with pytest.raises(mf.MfbError):
         mf.MixedStretch(V, T, fm, [("Neohookean", MU, LA)])
+
+
+@pytest.mark.parametrize("model", ["Stable-Neohookean", "ARAP", "Neohookean"])
+def test_update_parity_shell(built, model):
+    """config C5: TriMesh + MixedStretch<3> (triangles in 3D with rest normals, src/mesh/tri_mesh.cpp): F = J0 x + n (x) N,
+    x-dependent local Jacobian, 9 x 9 element blocks.  update / rhs / solve / energy / constraint against the oracle."""
+    import mixed_fem_b200 as mf
+    from mixed_fem_b200 import meshgen
+    from oracle import orc
+    V, T, N = meshgen.shell_grid(14, 9)
+    fm = meshgen.pinned_free_map(V, ratio=0.05)
+    mu, la = meshgen.enu_to_lame(0.57e6, 0.3)          # apps/cloth_sim.cpp:64-71
+    mats = [(model, mu, la)]
+    gpu = mf.MixedStretch(V, T, fm, mats, normals=N, thickness=0.5e-3)
+    cpu = orc.OracleMixedStretch(V, T, fm, mats, normals=N, thickness=0.5e-3)
+    rng = np.random.default_rng(3)
+    x = (V @ meshgen._affine().T + 0.01 * rng.standard_normal(V.shape)).reshape(-1)
+    xprev = (V @ meshgen._affine().T + 0.005 * rng.standard_normal(V.shape)).reshape(-1)
+    lam = rng.uniform(-1, 1, size=6 * T.shape[0]) * mu * 1e-3
+    for o in (gpu, cpu):
+        o.reset()
+    go, gi = gpu.csr_pattern()
+    co, ci, _ = cpu.csr(values=False)
+    assert np.array_equal(go, co) and np.array_equal(gi, ci)
+    gm, gs = gpu.scatter_map()
+    cm, cs = cpu.scatter_map()
+    assert np.array_equal(gm, cm) and np.array_equal(gs, cs)
+    for f, w in (("R", 9), ("S", 6), ("s", 6), ("dSdF", 54)):
+        assert block_rel(gpu.get(f), cpu.get(f), w) <= TOL, f
+    for o in (gpu, cpu):
+        o.update(xprev, DT)
+        o.set("s", cpu.get("S") if o is cpu else gpu.get("S"))
+        o.set("la", lam)
+        o.update(x, DT)
+    check_update(gpu, cpu, 3)
+    dx = rng.standard_normal(3 * gpu.nfree) * 1e-3
+    for o in (gpu, cpu):
+        o.solve(dx)
+    assert block_rel(gpu.get("la"), cpu.get("la"), 6) <= TOL
+    assert block_rel(gpu.get("ds"), cpu.get("ds"), 6) <= 1e-8
+    s_trial = cpu.get("s") + 0.5 * cpu.get("ds")
+    x_trial = x + 1e-3 * rng.standard_normal(x.size)
+    assert abs(gpu.energy(x_trial, s_trial) - cpu.energy(x_trial, s_trial)) <= TOL * abs(cpu.energy(x_trial, s_trial))
+    cg, cc = gpu.constraint_value(x_trial, s_trial), cpu.constraint_value(x_trial, s_trial)
+    assert abs(cg - cc) <= 1e-9 * max(abs(cc), 1e-12)
+    # rhs() recomputed after the trial evaluation must still use the Jacobian of the update (TriMesh::update_jacobian)
+    gpu.set_option("fuse_rhs", 0)
+    gpu.update(x, DT)
+    assert vec_rel(gpu.rhs(), cpu.rhs()) <= TOL
+    xe = rng.standard_normal(6 * gpu.nE); xv = rng.standard_normal(3 * gpu.nfree)
+    for which, xin, out0, tr in (("jacobian_x", xe, xv, True), ("jacobian_x", xv, xe, False)):
+        assert vec_rel(gpu.product(which, xin, out0, tr), cpu.product(which, xin, out0, tr)) <= TOL, which
+    gpu.close()
