@@ -181,6 +181,8 @@ def gpu_arm(args):
         ms.set_option("smem_b", args.variant)
     if args.asm is not None:
         ms.set_option("asm_mode", args.asm)
+    if args.exp:
+        ms.set_option("exp", args.exp)
     # state: R, s from the 'previous' positions (polar from identity on the device), lambda seeded
     ms.reset(xb)
     ms.set("la", lam)
@@ -374,6 +376,7 @@ def main():
     ap.add_argument("--grid", type=int, nargs=3, default=[119, 119, 119])
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--exp", type=int, default=0, help="what-if experiment bits of the update kernel (results are WRONG; profiling aid only)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-newton", action="store_true", help="skip the ms-per-Newton-iteration leg (config C3)")
     ap.add_argument("--newton-grid", type=int, nargs=3, default=[55, 55, 55])

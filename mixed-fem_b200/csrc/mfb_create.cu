@@ -346,6 +346,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   std::vector<MaterialDev> hm(d->n_mat);
   for (int i = 0; i < d->n_mat; ++i) { hm[i].model = d->materials[i].model; hm[i].mu = d->materials[i].mu; hm[i].la = d->materials[i].la; }
   TRY(upload(c->mats, hm, st));
+  c->mat0_host = hm[0];
   TRY(build_pattern(c));
   const size_t N = c->N, M = c->M, NP = c->NP;
   TRY(c->R.alloc(M * ld)); TRY(c->s.alloc(N * ld)); TRY(c->la.alloc(N * ld)); TRY(c->ds.alloc(N * ld)); TRY(c->S.alloc(N * ld));

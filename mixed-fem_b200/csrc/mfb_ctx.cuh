@@ -51,11 +51,13 @@ struct mfb_ctx {
   int fuse_rhs = 1;
   int assembly = 0;
   int smem_b = 3;       // update kernel variant: 3 = k_update_tet_v4 (default), 0/1/2 = the earlier register / shared-memory / fused variants
+  int exp = 0;
   int asm_mode = 1;     // v4 assembly: 1 = warp-cooperative coalesced RED into the block-CSR upper triangle, 0 = FP64 RED into the scalar CSR
   // mesh (device)
   mfb::DBuf<int> T, fidx, matid, smap, sstride;
   mfb::DBuf<double> dphi, vol, vref, nrest, xupd;   // xupd: shells, positions of the last update()
   mfb::DBuf<mfb::MaterialDev> mats;
+  mfb::MaterialDev mat0_host{0, 0.0, 0.0};
   // CSR structure (device)
   mfb::DBuf<int> blockptr, brow, bcol, bT, diagblk, outer, inner;
   mfb::DBuf<int4> mirror;     // (dst0, dst stride, src0, src stride) per lower-triangle block, see k_mirror_lower
@@ -89,7 +91,7 @@ struct mfb_ctx {
   mfb::DevMesh mesh() const {
     mfb::DevMesh m;
     m.dim = dim; m.npe = npe; m.nV = nV; m.nE = nE; m.nF = nF; m.ld = ld;
-    m.T = T.p; m.fidx = fidx.p; m.dphi = dphi.p; m.vol = vol.p; m.matid = matid.p; m.mats = mats.p;
+    m.T = T.p; m.fidx = fidx.p; m.dphi = dphi.p; m.vol = vol.p; m.matid = matid.p; m.mats = mats.p; m.mat0 = mat0_host; m.exp = exp;
     m.smap = smap.p; m.sstride = sstride.p;
     m.nrest = nrest.p; m.xlast = xupd.p;
     return m;

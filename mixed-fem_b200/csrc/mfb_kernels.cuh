@@ -22,6 +22,8 @@ struct DevMesh {
   const double* vol;     // [ld]
   const int* matid;      // [ld] or nullptr
   const MaterialDev* mats;
+  int exp;               // experiment bits (what-if runs, option "exp"): 1 skip dSdF stores, 2 skip REDs, 4 skip H/Hinv stores, 8 skip lambda_max
+  MaterialDev mat0;      // materials[0] by value: lives in the kernel-parameter constant bank (no load when matid == nullptr)
   const int* smap;       // [npe*npe][ld]  value index of entry (0,0) of block (j,k), -1 if pinned
   const int* sstride;    // [npe][ld]      CSR row length of block-row j
   const double* nrest;   // [3][ld]        shells: rest normal of the face (TriMesh::N_), else nullptr
@@ -72,9 +74,9 @@ __device__ __forceinline__ void tet_F(const DevMesh& m, int e, const double* __r
   const int64_t ld = m.ld;
   int v[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) v[k] = m.T[k * ld + e];
+  for (int k = 0; k < 4; ++k) v[k] = __ldcs(&m.T[k * ld + e]);
 #pragma unroll
-  for (int i = 0; i < 9; ++i) dphi[i] = m.dphi[i * ld + e];
+  for (int i = 0; i < 9; ++i) dphi[i] = __ldcs(&m.dphi[i * ld + e]);
   double x0[3], dx[9];
 #pragma unroll
   for (int l = 0; l < 3; ++l) x0[l] = __ldg(&x[3 * (int64_t)v[0] + l]);

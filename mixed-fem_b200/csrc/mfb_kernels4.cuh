@@ -42,6 +42,13 @@ struct DevAsm {
   int* slow_list;        // [nE]
 };
 
+__device__ __forceinline__ void cp_async8(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory");
+}
+
 // Every lane holds NV values for NV contiguous doubles at base[target .. target+NV) (target < 0: nothing to add).
 // The warp re-distributes them through its shared-memory buffer so that each RED instruction covers runs of NV
 // contiguous doubles with NV adjacent lanes.  All 32 lanes must call this.
@@ -62,6 +69,11 @@ __device__ __forceinline__ void coop_red(double* __restrict__ base, const double
   }
 }
 
+// Per-element state is written once per update and not read again by this kernel: streaming (evict-first) stores keep
+// the L2 for the reduction targets (the blocks of one z-plane of a cube-major mesh are touched again a plane later).
+template <class T>
+__device__ __forceinline__ void st_stream(T* p, T v) { __stcs(p, v); }
+
 // local pair (j,k), j < k  ->  0..5
 __device__ __forceinline__ constexpr int pair6(int j, int k) { return j * 3 - j * (j - 1) / 2 + (k - j - 1); }
 
@@ -79,17 +91,28 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   double dphi[9], F[9], R[9], Y[9];
   tet_F(m, e, x, dphi, F);
 #pragma unroll
-  for (int i = 0; i < 9; ++i) R[i] = st.R[i * ld + e];
+  for (int i = 0; i < 9; ++i) R[i] = __ldcs(&st.R[i * ld + e]);
   double s[6];
 #pragma unroll
-  for (int k = 0; k < 6; ++k) s[k] = st.s[k * ld + e];
-  const double vol = m.vol[e];
+  for (int k = 0; k < 6; ++k) s[k] = __ldcs(&st.s[k * ld + e]);
+  const double vol = __ldcs(&m.vol[e]);
+  // step-3 inputs (la, element->block codes) start moving now, asynchronously and without registers, into the warp's
+  // reduction buffer, which is idle until step 3: layout la[n] at sW[n*32 + lane], code[q] at int(sW + 192)[q*32 + lane]
+  if (ASM == 1) {
+    __syncwarp();     // tail kernel: the previous element's last reduction round has finished reading the buffer
+#pragma unroll
+    for (int n = 0; n < 6; ++n) cp_async8(&sW[n * 32 + lane], &st.la[n * ld + e]);
+    int* sI = reinterpret_cast<int*>(sW + 192);
+#pragma unroll
+    for (int q = 0; q < 6; ++q) cp_async4(&sI[q * 32 + lane], &as.bmap[q * ld + e]);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
   if (!TAIL) {
     iters = procrustes3(R, F, Y, 1e-6, 100, &status);
     if (inrange) {
 #pragma unroll
-      for (int i = 0; i < 9; ++i) st.R[i * ld + e] = R[i];
-      st.iters[e] = iters;
+      for (int i = 0; i < 9; ++i) st_stream(&st.R[i * ld + e], R[i]);
+      st_stream(&st.iters[e], iters);
     }
   } else {
 #pragma unroll
@@ -106,7 +129,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     if (!TAIL) {
       if (inrange) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) st.S[k * ld + e] = S[k];
+        for (int k = 0; k < 6; ++k) st_stream(&st.S[k * ld + e], S[k]);
       }
       // evaluate_constraint's own polar from a copy of R_ (mixed_stretch.cpp:358-360): zero iterations when the
       // iterated Y = R F^T already passes the tolerance test, which it does unless the iteration cap was hit
@@ -121,7 +144,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       }
       if (inrange) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) st.grad_la[k * ld + e] = ((k < 3) ? 1.0 : 2.0) * (S[k] - s[k]) * vol;
+        for (int k = 0; k < 6; ++k) st_stream(&st.grad_la[k * ld + e], ((k < 3) ? 1.0 : 2.0) * (S[k] - s[k]) * vol);
       }
     }
   }
@@ -132,10 +155,10 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     for (int n = 0; n < 6; ++n) {
       double col[9];
       dsdf3_column(n, R, F, Hinv3, col);
-      if (!TAIL && inrange) {
+      if (!TAIL && inrange && !(m.exp & 1)) {
         const double sy = (n < 3) ? 1.0 : 2.0;
 #pragma unroll
-        for (int k = 0; k < 9; ++k) st.dSdF[(n * 9 + k) * ld + e] = sy * col[k];
+        for (int k = 0; k < 9; ++k) st_stream(&st.dSdF[(n * 9 + k) * ld + e], sy * col[k]);
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k)
@@ -150,7 +173,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   bool live = inrange;       // false: this lane stores / adds nothing from here on
   double L[21];
   {
-    const MaterialDev mat = m.mats[m.matid ? m.matid[e] : 0];
+    const MaterialDev mat = m.matid ? m.mats[m.matid[e]] : m.mat0;
     double g[6], Hinv[21], lmax;
     material_grad_hess6(mat.model, mat.mu, mat.la, s, h2, g, L);     // L holds H for now
     if (!TAIL) {
@@ -158,7 +181,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
       for (int i = 0; i < 21; ++i) Hm[i] = L[i];
       int nit;
-      const bool ok = psd_fast6(Hm, L, Hinv, 1e-8, 1e-5, &lmax, &nit);
+      const bool ok = psd_fast6(Hm, L, Hinv, 1e-8, 1e-5, &lmax, &nit, !(m.exp & 8));
       // elements that need the eigen-decomposition: append to the list (one atomic per warp); the lane goes idle
       const bool fail = inrange && !ok;
       const unsigned failm = __ballot_sync(0xffffffffu, fail);
@@ -181,7 +204,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
           for (int j = 0; j <= i; ++j) {
             const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
-            st.H[symidx(i, j) * ld + e] = iv * w * Hm[symidx(i, j)];
+            st_stream(&st.H[symidx(i, j) * ld + e], iv * w * Hm[symidx(i, j)]);
           }
       }
     } else {
@@ -193,17 +216,17 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
           for (int j = 0; j <= i; ++j) {
             const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
-            st.H[symidx(i, j) * ld + e] = iv * w * L[symidx(i, j)];
+            st_stream(&st.H[symidx(i, j) * ld + e], iv * w * L[symidx(i, j)]);
           }
       }
       cholesky6(L);
     }
-    if (live) {
+    if (live && !(m.exp & 4)) {
 #pragma unroll
-      for (int i = 0; i < 21; ++i) st.Hinv[i * ld + e] = Hinv[i];
+      for (int i = 0; i < 21; ++i) st_stream(&st.Hinv[i * ld + e], Hinv[i]);
 #pragma unroll
-      for (int k = 0; k < 6; ++k) st.g[k * ld + e] = g[k];
-      st.evals[e] = h2 * lmax;
+      for (int k = 0; k < 6; ++k) st_stream(&st.g[k * ld + e], g[k]);
+      st_stream(&st.evals[e], h2 * lmax);
       if (!(lmax == lmax) || lmax > 1e300) status |= ST_NONFINITE;
     }
     // u = Hfix (S - s) + g = L (L^T (S - s)) + g ; gl = Syminv u   (rhs(): gl = vol H_ Sym (S-s) + Syminv g)
@@ -218,7 +241,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       for (int i = 0; i < 6; ++i) { double a = g[i];
 #pragma unroll
         for (int j = 0; j <= i; ++j) a += L[symidx(i, j)] * t[j];
-        u[i] = a; if (live) st.gl[i * ld + e] = ((i < 3) ? 1.0 : 0.5) * a; }
+        u[i] = a; if (live) st_stream(&st.gl[i * ld + e], ((i < 3) ? 1.0 : 0.5) * a); }
     }
   }
 
@@ -227,8 +250,18 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
   for (int k = 0; k < 4; ++k) f[k] = live ? m.fidx[k * ld + e] : -1;
   double tl[6];
+  int code[6];
+  if (ASM == 1) {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    const int* sI = reinterpret_cast<const int*>(sW + 192);
 #pragma unroll
-  for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * st.la[n * ld + e];
+    for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * sW[n * 32 + lane];
+#pragma unroll
+    for (int q = 0; q < 6; ++q) code[q] = live ? sI[q * 32 + lane] : -1;
+  } else {
+#pragma unroll
+    for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * st.la[n * ld + e];
+  }
   const double sv = sqrt(vol);
   double B0[3][6];
 #pragma unroll
@@ -270,7 +303,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
           }
         }
       } else {
-        coop_red<6>(as.gxrh, vv, f[k + 1] >= 0 ? 6 * f[k + 1] : -1, sW, sC, lane);
+        coop_red<6>(as.gxrh, vv, (f[k + 1] >= 0 && !(m.exp & 2)) ? 6 * f[k + 1] : -1, sW, sC, lane);
       }
     }
     if (ASM == 0) {
@@ -282,7 +315,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
         }
       }
     } else {
-      coop_red<6>(as.gxrh, v0, f[0] >= 0 ? 6 * f[0] : -1, sW, sC, lane);
+      coop_red<6>(as.gxrh, v0, (f[0] >= 0 && !(m.exp & 2)) ? 6 * f[0] : -1, sW, sC, lane);
     }
   }
 
@@ -325,9 +358,6 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     }
   } else {
     // off-diagonal pairs only: the diagonal blocks follow from the zero block-row sums in k_finalize_rows
-    int code[6];
-#pragma unroll
-    for (int q = 0; q < 6; ++q) code[q] = live ? as.bmap[q * ld + e] : -1;
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       double bj[3][6];
@@ -358,7 +388,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
         for (int r = 0; r < 3; ++r)
 #pragma unroll
           for (int c = 0; c < 3; ++c) v[3 * r + c] = tr ? a[c][r] : a[r][c];
-        coop_red<9>(as.Ablk, v, cd >= 0 ? 9 * (cd >> 1) : -1, sW, sC, lane);
+        coop_red<9>(as.Ablk, v, (cd >= 0 && !(m.exp & 2)) ? 9 * (cd >> 1) : -1, sW, sC, lane);
       }
     }
   }

@@ -412,7 +412,7 @@ MFB_HD void tridiag6_step(double* A) {
   A[symidx(K + 1, K)] = alpha;
 }
 
-MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, double relpiv, double* lmax, int* newton_iters) {
+MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, double relpiv, double* lmax, int* newton_iters, bool want_lmax = true) {
   bool ok = true;
   // ---- 1. Cholesky with pivot check; id[j] = 1 / L_jj
   double id[6];
@@ -473,6 +473,7 @@ MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, doub
   ok = ok && fok;
   fro = fok ? fro : 1.0;
   const double inrm = fast_rsqrt(fro), nrm = fro * inrm;
+  if (!want_lmax) { *lmax = nrm; *newton_iters = 0; return ok; }
 #pragma unroll
   for (int i = 0; i < 21; ++i) A[i] = H[i] * inrm;
   tridiag6_step<0>(A); tridiag6_step<1>(A); tridiag6_step<2>(A); tridiag6_step<3>(A);
