@@ -74,7 +74,7 @@ struct mfb_ctx {
   // scratch
   mfb::DBuf<double> xdev, vecF, partials, scal, aos, soa_tmp, soa_tmp2;
   // pcg work vectors
-  mfb::DBuf<double> pcg_r, pcg_p, pcg_z, pcg_t, pcg_dinv;
+  mfb::DBuf<double> pcg_r, pcg_p, pcg_z, pcg_t, pcg_dinv, pcg_part, pcg_lhs;
   double* h_scal = nullptr;   // pinned
   // host copies (lazy)
   std::vector<int32_t> h_outer, h_inner, h_smap, h_sstride;

@@ -5,8 +5,7 @@
 // recurrence is hand-written in src/linear_solvers/pcg.h:11-80).
 //
 // SpMV is HBM-bound: 8 B per stored value (+8 B when M is given) + 4/d^2 B of column index per value (one block-column
-// index per d x d block, not one per scalar entry) + the vectors.  One warp owns one block-row: its d*d*nbr values
-// are contiguous in the CSR value array, so the warp streams them with coalesced 256-byte reads.
+// index per d x d block, not one per scalar entry) + the vectors.
 #include "mfb_ctx.cuh"
 
 using namespace mfb;
@@ -16,37 +15,45 @@ static inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t -
 
 namespace {
 
+// Half a warp per block-row, one lane per d x d block (an interior vertex of a tet mesh has ~15 blocks): the lane reads
+// its d contiguous values of each of the d scalar rows, adjacent lanes adjacent 8d-byte pieces (tools/ubench_spmv.cu:
+// 50 us per product at 1M tets against 64 us for a warp per block-row; a plain read of the values takes 43 us).
 template <int DIM, bool HAS_M>
 __global__ void __launch_bounds__(256) k_spmv(const int* __restrict__ blockptr, const int* __restrict__ bcol, int nF,
                                               const double* __restrict__ A, const double* __restrict__ Mv,
                                               const double* __restrict__ x, double* __restrict__ y) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (warp >= nF) return;
-  const int b0 = blockptr[warp], nbr = blockptr[warp + 1] - b0;
+  const int lane = threadIdx.x & 31, hl = lane & 15;
+  const int row = (blockIdx.x * 8 + (threadIdx.x >> 5)) * 2 + (lane >> 4);
+  int b0 = 0, nbr = 0;
+  if (row < nF) { b0 = blockptr[row]; nbr = blockptr[row + 1] - b0; }
   const int rowlen = DIM * nbr;
   const int64_t base = (int64_t)DIM * DIM * b0;
   double acc[DIM];
 #pragma unroll
   for (int r = 0; r < DIM; ++r) acc[r] = 0.0;
-  for (int q = lane; q < rowlen; q += 32) {     // q = position inside one scalar row
-    const int col = DIM * bcol[b0 + q / DIM] + (q % DIM);
-    const double xv = __ldg(&x[col]);
+  for (int k = hl; k < nbr; k += 16) {
+    const int col = DIM * bcol[b0 + k];
+    double xv[DIM];
 #pragma unroll
-    for (int r = 0; r < DIM; ++r) {
-      double a = A[base + (int64_t)r * rowlen + q];
-      if (HAS_M) a += Mv[base + (int64_t)r * rowlen + q];
-      acc[r] += a * xv;
-    }
+    for (int c = 0; c < DIM; ++c) xv[c] = __ldg(&x[col + c]);
+#pragma unroll
+    for (int r = 0; r < DIM; ++r)
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) {
+        const int64_t i = base + (int64_t)r * rowlen + DIM * k + c;
+        double a = A[i];
+        if (HAS_M) a += Mv[i];
+        acc[r] = fma(a, xv[c], acc[r]);
+      }
   }
 #pragma unroll
   for (int r = 0; r < DIM; ++r) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc[r] += __shfl_down_sync(0xffffffffu, acc[r], o);
+    for (int o = 8; o > 0; o >>= 1) acc[r] += __shfl_down_sync(0xffffffffu, acc[r], o, 16);
   }
-  if (lane == 0) {
+  if (hl == 0 && row < nF) {
 #pragma unroll
-    for (int r = 0; r < DIM; ++r) y[DIM * warp + r] = acc[r];
+    for (int r = 0; r < DIM; ++r) y[DIM * row + r] = acc[r];
   }
 }
 
@@ -155,26 +162,180 @@ __global__ void k_apply_precond(const double* __restrict__ dinv, const double* _
     z[DIM * gi + a] = s;
   }
 }
-// scal[0]=absNew, scal[1]=pAp  ->  alpha ; x += alpha p ; r -= alpha t
-__global__ void k_cg_update(const double* __restrict__ scal, const double* __restrict__ p, const double* __restrict__ t,
-                            double* __restrict__ x, double* __restrict__ r, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const double alpha = scal[0] / scal[1];
-  x[i] += alpha * p[i];
-  r[i] -= alpha * t[i];
+// ---------------------------------------------------------------------------------------------------------------
+// Fused CG iteration: three launches, no host round trip.
+//   k_pcg_spmv_dot : t = L p (L = M + A summed once per solve), block partials of p.t
+//   k_pcg_update   : alpha = absOld / p.t ; x += alpha p ; r -= alpha t ; z = Dinv r ; block partials of r.r, r.z;
+//                    |r|^2 < threshold -> done (the reference breaks before counting that iteration)
+//   k_pcg_dir      : beta = r.z / absOld ; p = z + beta p
+// (forming p on the fly inside the SpMV gather instead of k_pcg_dir was measured: the second gathered vector costs
+// more than the 11 us launch it saves at 1M tets.)
+// The LAST block of a launch to finish (ticket counter) sums the block partials in fixed order and writes the scalars,
+// so no single-block "finish" launch sits between the kernels and the sums do not depend on block scheduling.
+// scal[]: [0],[1] r.z by iteration parity (iteration k reads k-1's while writing its own), [2] done flag,
+// [3] completed iterations, [4] |b|^2, [5] |r|^2, [6] threshold, [7] p.t.  Once `done` is set every later launch of
+// the batch returns at once; the host looks at the flag once per batch of iterations.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kPcgBlocks = 1184;       // 8 x 148 SMs, 256 threads each (vector kernels)
+constexpr int kSpmvBlocks = 740;       // 5 x 148: what is resident at the SpMV's 48 registers (tools/ubench_spmv.cu)
+
+__device__ __forceinline__ double block_sum_256(double v, double* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  __syncthreads();                                  // sh may still be read from a previous call
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double r = 0.0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r += sh[i];           // same order in every thread and block
+  return r;
 }
-// scal[0]=absOld, scal[2]=absNew -> beta ; p = z + beta p
-__global__ void k_cg_dir(const double* __restrict__ scal, const double* __restrict__ z, double* __restrict__ p, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const double beta = scal[2] / scal[0];
-  p[i] = z[i] + beta * p[i];
+// sum of this launch's block partials in fixed order
+__device__ __forceinline__ double sum_partials_all(const double* partials, double* sh) {
+  double v = 0.0;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += 256) v += __ldcg(&partials[i]);     // L2: written by other blocks
+  return block_sum_256(v, sh);
 }
-__global__ void k_copy_scalar(double* scal, int dst, int src) { scal[dst] = scal[src]; }
+
+// Half a warp per block-row, one lane per d x d block (an interior vertex of a tet mesh has ~15 blocks): the lane reads
+// its d contiguous values of each of the d scalar rows (adjacent lanes read adjacent 8d-byte pieces) and the d entries
+// of the direction.  The row pointers of the half-warp's NEXT block-row are fetched before the current one is
+// consumed, so the blockptr -> values dependency does not leave the memory pipe idle between rows.
+// true in exactly one block per launch: the last one to arrive; its view of every block's partials is complete
+__device__ __forceinline__ bool last_block_done(unsigned* ticket) {
+  __shared__ bool last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned tk = atomicAdd(ticket, 1u);
+    last = (tk == gridDim.x - 1);
+    if (last) *ticket = 0u;                           // ready for the next launch
+  }
+  __syncthreads();
+  if (last) __threadfence();
+  return last;
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(256) k_pcg_spmv_dot(const int* __restrict__ blockptr, const int* __restrict__ bcol, int nF,
+                                                      const double* __restrict__ A, const double* __restrict__ p,
+                                                      double* __restrict__ t, double* __restrict__ scal,
+                                                      double* __restrict__ partials, unsigned* __restrict__ ticket) {
+  __shared__ double sh[8];
+  if (scal[2] != 0.0) return;
+  const int lane = threadIdx.x & 31, hl = lane & 15;
+  const int stride = gridDim.x * 16;                  // half-warps in the grid
+  double dot = 0.0;
+  int row = (blockIdx.x * 8 + (threadIdx.x >> 5)) * 2 + (lane >> 4);
+  int b0 = 0, b1 = 0;
+  if (row < nF) { b0 = blockptr[row]; b1 = blockptr[row + 1]; }
+  for (int row0 = row - (lane >> 4); row0 < nF; row0 += stride, row += stride) {     // warp-uniform trip count
+    const int nxt = row + stride;
+    int n0 = 0, n1 = 0;
+    if (nxt < nF) { n0 = blockptr[nxt]; n1 = blockptr[nxt + 1]; }
+    const int nbr = (row < nF) ? b1 - b0 : 0;
+    const int rowlen = DIM * nbr;
+    const double* Ar = A + (int64_t)DIM * DIM * b0;
+    double acc[DIM];
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) acc[r] = 0.0;
+    for (int k = hl; k < nbr; k += 16) {
+      const int col = DIM * bcol[b0 + k];
+      double xv[DIM];
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) xv[c] = __ldg(&p[col + c]);
+#pragma unroll
+      for (int r = 0; r < DIM; ++r)
+#pragma unroll
+        for (int c = 0; c < DIM; ++c) acc[r] = fma(Ar[(int64_t)r * rowlen + DIM * k + c], xv[c], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < DIM; ++r) {
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) acc[r] += __shfl_down_sync(0xffffffffu, acc[r], o, 16);
+    }
+    if (hl == 0 && row < nF) {
+#pragma unroll
+      for (int r = 0; r < DIM; ++r) { t[DIM * row + r] = acc[r]; dot = fma(acc[r], p[DIM * row + r], dot); }
+    }
+    b0 = n0; b1 = n1;
+  }
+  const double s = block_sum_256(dot, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = s;
+  if (last_block_done(ticket)) {
+    const double pt = sum_partials_all(partials, sh);
+    if (threadIdx.x == 0) scal[7] = pt;
+  }
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, int iter, unsigned* __restrict__ ticket,
+                                                    const double* __restrict__ p, const double* __restrict__ t,
+                                                    double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
+                                                    const double* __restrict__ dinv, int nF, int mode,
+                                                    double* __restrict__ part_out) {
+  __shared__ double sh[8];
+  if (scal[2] != 0.0) return;
+  const double alpha = scal[(iter + 1) & 1] / scal[7];
+  double rr = 0.0, rz = 0.0;
+  for (int gi = blockIdx.x * 256 + threadIdx.x; gi < nF; gi += gridDim.x * 256) {
+    double rv[DIM], zv[DIM];
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) {
+      const int i = DIM * gi + k;
+      x[i] += alpha * p[i];
+      rv[k] = r[i] - alpha * t[i];
+      r[i] = rv[k];
+    }
+    if (mode == 0) {
+#pragma unroll
+      for (int k = 0; k < DIM; ++k) zv[k] = rv[k];
+    } else {
+#pragma unroll
+      for (int a = 0; a < DIM; ++a) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) s += dinv[(int64_t)gi * DIM * DIM + a * DIM + k] * rv[k];
+        zv[a] = s;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) { z[DIM * gi + k] = zv[k]; rr += rv[k] * rv[k]; rz += rv[k] * zv[k]; }
+  }
+  const double s0 = block_sum_256(rr, sh);
+  const double s1 = block_sum_256(rz, sh);
+  if (threadIdx.x == 0) { part_out[blockIdx.x] = s0; part_out[kPcgBlocks + blockIdx.x] = s1; }
+  if (last_block_done(ticket)) {
+    const double rr2 = sum_partials_all(part_out, sh);
+    const double rz2 = sum_partials_all(part_out + kPcgBlocks, sh);
+    if (threadIdx.x == 0) {
+      scal[5] = rr2;
+      scal[iter & 1] = rz2;
+      if (rr2 < scal[6]) { scal[2] = 1.0; scal[3] = (double)iter; }
+      else scal[3] = (double)(iter + 1);
+    }
+  }
+}
+
+// beta = r.z of this iteration over r.z of the previous one ; p = z + beta p
+__global__ void __launch_bounds__(256) k_pcg_dir(const double* __restrict__ scal, int iter, const double* __restrict__ z,
+                                                 double* __restrict__ p, int n) {
+  if (scal[2] != 0.0) return;
+  const double beta = scal[iter & 1] / scal[(iter + 1) & 1];
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) p[i] = fma(beta, p[i], z[i]);
+}
+// lhs = A + M, once per solve (linear_system.h: lhs_ = M + A is formed once per Newton iteration)
+__global__ void k_sum_values(const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ o, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) o[i] = a[i] + b[i];
+}
+// scal[4] = |b|^2, scal[5] = |r|^2, scal[0] = r.z are in place; "iteration -1" has parity 1
+__global__ void k_pcg_init(double* scal, double tol, unsigned* tickets) {
+  scal[1] = scal[0]; scal[2] = 0.0; scal[3] = 0.0; scal[6] = tol * tol * scal[4]; scal[7] = 0.0;
+  tickets[0] = 0u; tickets[1] = 0u;
+}
 
 int spmv(mfb_ctx* c, const double* Mv, const double* x, double* y) {
-  const int64_t threads = (int64_t)c->nF * 32;
+  const int64_t threads = (int64_t)c->nF * 16;
   if (c->nF == 0) return MFB_OK;
   if (c->dim == 3) {
     if (Mv) k_spmv<3, true><<<nblk(threads), 256, 0, c->stream>>>(c->blockptr.p, c->bcol.p, c->nF, c->Avals.p, Mv, x, y);
@@ -219,20 +380,30 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
       return rc;
   }
   if (c->partials.n < (size_t)2 * kDotBlocks) { if ((rc = c->partials.alloc((size_t)2 * kDotBlocks + c->grid()))) return rc; }
+  if (c->pcg_part.n < (size_t)5 * kPcgBlocks) { if ((rc = c->pcg_part.alloc((size_t)5 * kPcgBlocks))) return rc; }
   cudaStream_t st = c->stream;
   double *r = c->pcg_r.p, *p = c->pcg_p.p, *z = c->pcg_z.p, *t = c->pcg_t.p;
-  if (precond) {
-    if (c->dim == 3) k_build_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, c->Avals.p, Mv, precond, c->pcg_dinv.p);
-    else k_build_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, c->Avals.p, Mv, precond, c->pcg_dinv.p);
+  // the operator of this solve: one value array, L = A + M
+  const double* L = c->Avals.p;
+  if (Mv) {
+    if (c->pcg_lhs.n < (size_t)c->nnz + 1) { if ((rc = c->pcg_lhs.alloc((size_t)c->nnz + 1))) return rc; }
+    k_sum_values<<<kPcgBlocks, 256, 0, st>>>(c->Avals.p, Mv, c->pcg_lhs.p, c->nnz);
     c->launches += 1;
+    L = c->pcg_lhs.p;
   }
-  auto apply_prec = [&](const double* rr, double* zz) {
-    if (c->dim == 3) k_apply_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, rr, zz, c->nF, precond);
-    else k_apply_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, rr, zz, c->nF, precond);
+  auto spmv_L = [&](const double* xx, double* yy) {
+    const int64_t threads = (int64_t)c->nF * 16;
+    if (c->dim == 3) k_spmv<3, false><<<nblk(threads), 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, nullptr, xx, yy);
+    else k_spmv<2, false><<<nblk(threads), 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, nullptr, xx, yy);
     c->launches += 1;
   };
-  // residual = b - A x ; rhsNorm2
-  if ((rc = spmv(c, Mv, x, t))) return rc;
+  if (precond) {
+    if (c->dim == 3) k_build_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
+    else k_build_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
+    c->launches += 1;
+  }
+  // residual = b - L x ; |b|^2 ; |r|^2
+  if (c->nF) spmv_L(x, t);
   k_residual<<<nblk(n), 256, 0, st>>>(b, t, r, n); c->launches += 1;
   if ((rc = dot2(c, b, b, r, r, n, 4, 5))) return rc;                 // scal[4] = |b|^2, scal[5] = |r|^2
   MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -246,24 +417,40 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
     return MFB_OK;
   }
   const double threshold = tol * tol * rhsNorm2;
-  if (resNorm2 >= threshold) {
-    apply_prec(r, p);
+  if (resNorm2 >= threshold && max_iters > 0) {
+    // p = Dinv r ; absNew = r.p
+    if (c->dim == 3) k_apply_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
+    else k_apply_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
+    c->launches += 1;
     if ((rc = dot2(c, r, p, nullptr, nullptr, n, 0, -1))) return rc;  // scal[0] = absNew
-    while (it < max_iters) {
-      if ((rc = spmv(c, Mv, p, t))) return rc;
-      if ((rc = dot2(c, p, t, nullptr, nullptr, n, 1, -1))) return rc;     // scal[1] = p.Ap
-      k_cg_update<<<nblk(n), 256, 0, st>>>(c->scal.p, p, t, x, r, n); c->launches += 1;
-      apply_prec(r, z);
-      if ((rc = dot2(c, r, r, r, z, n, 5, 2))) return rc;               // scal[5] = |r|^2, scal[2] = r.z
+    double* part = c->pcg_part.p;                   // pt[G] | rr[G] | rz[G] | two ticket counters
+    unsigned* tickets = reinterpret_cast<unsigned*>(part + 3 * kPcgBlocks);
+    k_pcg_init<<<1, 1, 0, st>>>(c->scal.p, tol, tickets); c->launches += 1;
+    const unsigned gv = nblk(c->nF) < (unsigned)kPcgBlocks ? nblk(c->nF) : (unsigned)kPcgBlocks;      // one vertex per thread
+    const unsigned gn = nblk(n) < (unsigned)kPcgBlocks ? nblk(n) : (unsigned)kPcgBlocks;
+    const unsigned gs = nblk((int64_t)c->nF * 16) < (unsigned)kSpmvBlocks ? nblk((int64_t)c->nF * 16) : (unsigned)kSpmvBlocks;
+    int launched = 0, batch = 8;
+    while (launched < max_iters) {
+      const int nb = (max_iters - launched < batch) ? max_iters - launched : batch;
+      for (int k = launched; k < launched + nb; ++k) {
+        if (c->dim == 3) {
+          k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
+          k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks);
+        } else {
+          k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
+          k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks);
+        }
+        k_pcg_dir<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
+      }
+      launched += nb;
+      c->launches += 3 * nb;
       MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
       MFB_CUDA(cudaStreamSynchronize(st));
-      resNorm2 = c->h_scal[5];
-      if (resNorm2 < threshold) break;
-      k_cg_dir<<<nblk(n), 256, 0, st>>>(c->scal.p, z, p, n);
-      k_copy_scalar<<<1, 1, 0, st>>>(c->scal.p, 0, 2);
-      c->launches += 2;
-      ++it;
+      if (c->h_scal[2] != 0.0) break;
+      if (batch < 64) batch *= 2;
     }
+    it = (int)c->h_scal[3];
+    resNorm2 = c->h_scal[5];
   }
   MFB_CUDA(cudaGetLastError());
   if (iters_out) *iters_out = it;
