@@ -190,11 +190,28 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     double g[6], Hinv[21], lmax;
     material_grad_hess6(mat.model, mat.mu, mat.la, s, h2, g, L);     // L holds H for now
     if (!TAIL) {
+      // H_ and Hinv_ leave as soon as they exist: a lane that later turns out to need the eigen-decomposition has
+      // them overwritten by the tail kernel, and the 42 values do not stay live across the lambda_max iteration
       double Hm[21];
 #pragma unroll
       for (int i = 0; i < 21; ++i) Hm[i] = L[i];
+      if (inrange) {
+        const double iv = 1.0 / vol;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) {
+            const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
+            st_stream(&st.H[symidx(i, j) * ld + e], iv * w * Hm[symidx(i, j)]);
+          }
+      }
+      bool ok = psd_fast6_factor(Hm, L, Hinv, 1e-8, 1e-5);
+      if (inrange && !(m.exp & 4)) {
+#pragma unroll
+        for (int i = 0; i < 21; ++i) st_stream(&st.Hinv[i * ld + e], Hinv[i]);
+      }
       int nit;
-      const bool ok = psd_fast6(Hm, L, Hinv, 1e-8, 1e-5, &lmax, &nit, !(m.exp & 8));
+      if (m.exp & 8) { lmax = 1.0; nit = 0; } else ok = psd_fast6_lmax(Hm, &lmax, &nit) && ok;
       // elements that need the eigen-decomposition: append to the list (one atomic per warp); the lane goes idle
       const bool fail = inrange && !ok;
       const unsigned failm = __ballot_sync(0xffffffffu, fail);
@@ -209,16 +226,6 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
           count_status(st.counters, inrange ? status : 0, inrange ? iters : 0, 0);
           return;
         }
-      }
-      if (live) {
-        const double iv = 1.0 / vol;
-#pragma unroll
-        for (int i = 0; i < 6; ++i)
-#pragma unroll
-          for (int j = 0; j <= i; ++j) {
-            const double w = ((i < 3) ? 1.0 : 0.5) * ((j < 3) ? 1.0 : 0.5);
-            st_stream(&st.H[symidx(i, j) * ld + e], iv * w * Hm[symidx(i, j)]);
-          }
       }
     } else {
       lmax = psd_fix_invert<6>(L, Hinv, 1e-8, &sweeps);
@@ -235,8 +242,10 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       cholesky6(L);
     }
     if (live && !(m.exp & 4)) {
+      if (TAIL) {
 #pragma unroll
-      for (int i = 0; i < 21; ++i) st_stream(&st.Hinv[i * ld + e], Hinv[i]);
+        for (int i = 0; i < 21; ++i) st_stream(&st.Hinv[i * ld + e], Hinv[i]);
+      }
 #pragma unroll
       for (int k = 0; k < 6; ++k) st_stream(&st.g[k * ld + e], g[k]);
       st_stream(&st.evals[e], h2 * lmax);

@@ -412,7 +412,8 @@ MFB_HD void tridiag6_step(double* A) {
   A[symidx(K + 1, K)] = alpha;
 }
 
-MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, double relpiv, double* lmax, int* newton_iters, bool want_lmax = true) {
+// steps 1 and 2: Cholesky factor, inverse, lambda_min certificate
+MFB_HD bool psd_fast6_factor(const double* H, double* L, double* Hinv, double tol, double relpiv) {
   bool ok = true;
   // ---- 1. Cholesky with pivot check; id[j] = 1 / L_jj
   double id[6];
@@ -462,7 +463,12 @@ MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, doub
       if (i == j) tr += a;
     }
   ok = ok && (tr * tol < 1.0);          // lambda_min >= 1 / trace(H^-1) > tol ; false on NaN
-  // ---- 3. lambda_max
+  return ok;
+}
+
+// step 3: lambda_max
+MFB_HD bool psd_fast6_lmax(const double* H, double* lmax, int* newton_iters) {
+  bool ok = true;
   double A[21];
   double fro = 0.0;
 #pragma unroll
@@ -473,7 +479,6 @@ MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, doub
   ok = ok && fok;
   fro = fok ? fro : 1.0;
   const double inrm = fast_rsqrt(fro), nrm = fro * inrm;
-  if (!want_lmax) { *lmax = nrm; *newton_iters = 0; return ok; }
 #pragma unroll
   for (int i = 0; i < 21; ++i) A[i] = H[i] * inrm;
   tridiag6_step<0>(A); tridiag6_step<1>(A); tridiag6_step<2>(A); tridiag6_step<3>(A);
@@ -506,6 +511,13 @@ MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, doub
   *lmax = sg * nrm;
   *newton_iters = it;
   return ok;
+}
+
+
+MFB_HD bool psd_fast6(const double* H, double* L, double* Hinv, double tol, double relpiv, double* lmax, int* newton_iters) {
+  const bool ok1 = psd_fast6_factor(H, L, Hinv, tol, relpiv);
+  const bool ok2 = psd_fast6_lmax(H, lmax, newton_iters);
+  return ok1 && ok2;
 }
 
 // -----------------------------------------------------------------------------------------------------------------
