@@ -175,7 +175,7 @@ def gpu_arm(args):
     else:
         loc, Vl, Tl, fml = None, V, T, fm
     del V, T
-    ms = mf.MixedStretch(Vl, Tl, fml, [("Stable-Neohookean", mu, la)], device=local_rank)
+    ms = mf.MixedStretch(Vl, Tl, fml, [(args.material, mu, la)], device=local_rank)
     ms.set_stream(torch.cuda.current_stream().cuda_stream)
     if args.variant is not None:
         ms.set_option("smem_b", args.variant)
@@ -281,8 +281,8 @@ def gpu_arm(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": "C4: synthetic %dx%dx%d Kuhn box grid = %d tets / %d vertices, Stable-Neohookean E=1e6 nu=0.45, dt=0.0333, "
-                                   "MixedStretch::update() + fused Schur rhs" % (nx, ny, nz, nE_total, nV_total),
+            "config": {"workload": ("C4: synthetic %dx%dx%d Kuhn box grid = %d tets / %d vertices, " % (nx, ny, nz, nE_total, nV_total))
+                                   + args.material + " E=1e6 nu=0.45, dt=0.0333, MixedStretch::update() + fused Schur rhs",
                        "partition": "1 GPU" if world == 1 else "%d element slabs, NCCL all-reduce of interface grad_x_/rhs_" % world,
                        "l2": "inputs larger than L2 (%.1f GB of per-element state per step), no flush needed" % (1372.0 * nE_total / world / 1e9),
                        "states": "x alternates between two seeded states each step so the warm-started polar iterates"},
@@ -378,6 +378,7 @@ def main():
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--exp", type=int, default=0, help="what-if experiment bits of the update kernel (results are WRONG; profiling aid only)")
+    ap.add_argument("--material", default="Stable-Neohookean", help="material of the timed update (the headline metric is quoted on the default)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-newton", action="store_true", help="skip the ms-per-Newton-iteration leg (config C3)")
     ap.add_argument("--newton-grid", type=int, nargs=3, default=[55, 55, 55])

@@ -487,19 +487,34 @@ MFB_HD bool psd_fast6_lmax(const double* H, double* lmax, int* newton_iters) {
   for (int i = 0; i < 6; ++i) d[i] = A[symidx(i, i)];
 #pragma unroll
   for (int i = 0; i < 5; ++i) e2[i] = A[symidx(i + 1, i)] * A[symidx(i + 1, i)];
+  // Deflation: a negligible off-diagonal (|e| <= 1e-12 |A|_F) splits T.  A 1x1 block IS an eigenvalue and is taken out
+  // of the polynomial (factor 1): constant Hessians (ARAP: diagonal; Corot and SNH at rest: the shear block 4 mu I)
+  // have a multiple top eigenvalue made of such blocks, on which Newton would only converge linearly.
+  double w[6], liso = -1.0;
+  int nfree = 0;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) e2[i] = (e2[i] <= 1e-24) ? 0.0 : e2[i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const bool iso = (i == 0 || e2[i - 1] == 0.0) && (i == 5 || e2[i] == 0.0);
+    w[i] = iso ? 0.0 : 1.0;
+    liso = iso ? fmax(liso, d[i]) : liso;
+    nfree += iso ? 0 : 1;
+  }
   double sg = 1.0;                      // |A|_F = 1 >= lambda_max(A)
   bool conv = false;
   int it = 0;
+  if (nfree == 0) { sg = liso; conv = true; }
 #if defined(__CUDA_ARCH__)
 #pragma unroll 1
 #endif
-  for (; it < 24; ++it) {
-    double p0 = 1.0, p1 = sg - d[0], q0 = 0.0, q1 = 1.0;
+  for (; it < 24 && nfree > 0; ++it) {
+    double p0 = 1.0, p1 = (w[0] != 0.0) ? sg - d[0] : 1.0, q0 = 0.0, q1 = w[0];
 #pragma unroll
     for (int i = 1; i < 6; ++i) {
-      const double t = sg - d[i];
+      const double t = (w[i] != 0.0) ? sg - d[i] : 1.0;
       const double p2 = fma(t, p1, -e2[i - 1] * p0);
-      const double q2 = fma(t, q1, fma(-e2[i - 1], q0, p1));
+      const double q2 = fma(t, q1, fma(-e2[i - 1], q0, w[i] * p1));
       p0 = p1; p1 = p2; q0 = q1; q1 = q2;
     }
     if (!(q1 > 0.0)) break;             // cannot happen above the largest root; guards NaN
@@ -507,6 +522,7 @@ MFB_HD bool psd_fast6_lmax(const double* H, double* lmax, int* newton_iters) {
     sg -= dl;
     if (!(dl > 1e-15)) { conv = dl > -1e-12; ++it; break; }   // a large negative step = noise near a clustered root
   }
+  sg = fmax(sg, liso);
   ok = ok && conv;
   *lmax = sg * nrm;
   *newton_iters = it;
