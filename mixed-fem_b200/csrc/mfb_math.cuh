@@ -505,6 +505,25 @@ MFB_HD bool psd_fast6_lmax(const double* H, double* lmax, int* newton_iters) {
   bool conv = false;
   int it = 0;
   if (nfree == 0) { sg = liso; conv = true; }
+  if (nfree == 6) {                     // the common case: nothing deflated, plain recurrence
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (; it < 24; ++it) {
+      double p0 = 1.0, p1 = sg - d[0], q0 = 0.0, q1 = 1.0;
+#pragma unroll
+      for (int i = 1; i < 6; ++i) {
+        const double t = sg - d[i];
+        const double p2 = fma(t, p1, -e2[i - 1] * p0);
+        const double q2 = fma(t, q1, fma(-e2[i - 1], q0, p1));
+        p0 = p1; p1 = p2; q0 = q1; q1 = q2;
+      }
+      if (!(q1 > 0.0)) break;
+      const double dl = p1 * fast_rcp(q1);
+      sg -= dl;
+      if (!(dl > 1e-15)) { conv = dl > -1e-12; ++it; break; }
+    }
+  } else
 #if defined(__CUDA_ARCH__)
 #pragma unroll 1
 #endif
