@@ -22,23 +22,26 @@ namespace {
 inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
 
 // consistent element mass: block (j,k) = mass * (j == k ? c0 : c1) * I_d ; tets 1/10, 1/20 ; triangles 1/6, 1/12
-template <int DIM> struct MassCoef { static constexpr double c0 = DIM == 3 ? 0.1 : 1.0 / 6.0, c1 = DIM == 3 ? 0.05 : 1.0 / 12.0; };
+// (shells: TriMesh::mass_matrix, src/mesh/tri_mesh.cpp:43-69, same triangle weights on vol = doublearea*thickness/2).
+// K = element kind (3 tets, 2 triangles in 2D, K_SHELL triangles in 3D): Dims<K>::SD dofs per vertex, ::NPE vertices.
+template <int K> struct MassCoef { static constexpr double c0 = Dims<K>::NPE == 4 ? 0.1 : 1.0 / 6.0, c1 = Dims<K>::NPE == 4 ? 0.05 : 1.0 / 12.0; };
 
 // PMP^T on the Assembler pattern: only the d diagonal entries of each d x d block are non-zero
-template <int DIM>
+template <int K>
 __global__ void __launch_bounds__(128) k_mass_values(DevMesh m, double density, double* __restrict__ Mvals) {
+  constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
   const double mass = density * m.vol[e];
 #pragma unroll
-  for (int j = 0; j <= DIM; ++j) {
+  for (int j = 0; j < NPE; ++j) {
     const int stride = m.sstride[j * ld + e];
 #pragma unroll
-    for (int k = 0; k <= DIM; ++k) {
-      const int idx = m.smap[(j * (DIM + 1) + k) * ld + e];
+    for (int k = 0; k < NPE; ++k) {
+      const int idx = m.smap[(j * NPE + k) * ld + e];
       if (idx < 0) continue;
-      const double v = mass * (j == k ? MassCoef<DIM>::c0 : MassCoef<DIM>::c1);
+      const double v = mass * (j == k ? MassCoef<K>::c0 : MassCoef<K>::c1);
 #pragma unroll
       for (int r = 0; r < DIM; ++r) red_add(&Mvals[(int64_t)idx + (int64_t)r * stride + r], v);
     }
@@ -55,34 +58,36 @@ __global__ void k_inertia_diff(const double* __restrict__ x, const double* __res
 }
 
 // out(free rows) += sign * PM diff : element-wise product with the consistent mass blocks, all columns (pinned included)
-template <int DIM>
+template <int K>
 __global__ void __launch_bounds__(128) k_mass_rows_apply(DevMesh m, double density, const double* __restrict__ diff, double sign, double* __restrict__ out) {
+  constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
   const double mass = sign * density * m.vol[e];
-  double d[DIM + 1][DIM], sum[DIM];
+  double d[NPE][DIM], sum[DIM];
 #pragma unroll
   for (int l = 0; l < DIM; ++l) sum[l] = 0.0;
 #pragma unroll
-  for (int k = 0; k <= DIM; ++k) {
+  for (int k = 0; k < NPE; ++k) {
     const int v = m.T[k * ld + e];
 #pragma unroll
     for (int l = 0; l < DIM; ++l) { d[k][l] = diff[DIM * (int64_t)v + l]; sum[l] += d[k][l]; }
   }
 #pragma unroll
-  for (int j = 0; j <= DIM; ++j) {
+  for (int j = 0; j < NPE; ++j) {
     const int f = m.fidx[j * ld + e];
     if (f < 0) continue;
 #pragma unroll
     for (int l = 0; l < DIM; ++l)
-      red_add(&out[DIM * (int64_t)f + l], mass * (MassCoef<DIM>::c1 * sum[l] + (MassCoef<DIM>::c0 - MassCoef<DIM>::c1) * d[j][l]));
+      red_add(&out[DIM * (int64_t)f + l], mass * (MassCoef<K>::c1 * sum[l] + (MassCoef<K>::c0 - MassCoef<K>::c1) * d[j][l]));
   }
 }
 
 // 0.5 diff^T M diff with the FULL mass matrix (displacement.cpp:21-33), per-block partial sums
-template <int DIM>
+template <int K>
 __global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, double density, const double* __restrict__ diff, double* __restrict__ partials) {
+  constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   __shared__ double sh[4];
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   double val = 0.0;
@@ -92,7 +97,7 @@ __global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, double densit
 #pragma unroll
     for (int l = 0; l < DIM; ++l) sum[l] = 0.0;
 #pragma unroll
-    for (int k = 0; k <= DIM; ++k) {
+    for (int k = 0; k < NPE; ++k) {
       const int v = m.T[k * ld + e];
 #pragma unroll
       for (int l = 0; l < DIM; ++l) { const double a = diff[DIM * (int64_t)v + l]; sum[l] += a; sq += a * a; }
@@ -101,7 +106,7 @@ __global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, double densit
 #pragma unroll
     for (int l = 0; l < DIM; ++l) ss += sum[l] * sum[l];
     // sum_jk m_jk d_j.d_k = c1 |sum_j d_j|^2 + (c0 - c1) sum_j |d_j|^2
-    val = 0.5 * density * m.vol[e] * (MassCoef<DIM>::c1 * ss + (MassCoef<DIM>::c0 - MassCoef<DIM>::c1) * sq);
+    val = 0.5 * density * m.vol[e] * (MassCoef<K>::c1 * ss + (MassCoef<K>::c0 - MassCoef<K>::c1) * sq);
   }
   const double r = block_sum_128(val, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = r;
@@ -186,7 +191,6 @@ static mfb_newton_state* nstate(mfb_ctx* c) { return (mfb_newton_state*)c->newto
 extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0) {
   CHECK_CTX(c);
   if (!free_map || !(h > 0) || !(density > 0)) { g_last_error = "mfb_newton_init: bad arguments"; return MFB_ERR_INVALID; }
-  if (c->kind == MFB_SHELL) { g_last_error = "mfb_newton_*: shells (TriMesh) are not wired into the device-resident time step yet"; return MFB_ERR_UNSUPPORTED; }
   if (c->newton) { delete nstate(c); c->newton = nullptr; }
   mfb_newton_state* s = new mfb_newton_state();
   c->newton = s;
@@ -209,7 +213,8 @@ extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double densi
   // x_tilde = x_prev + h v_prev
   k_axpy_out<<<nblk((int64_t)nx), 256, 0, st>>>(s->xprev.p, s->vprev.p, h, (int64_t)nx, s->xt.p);
   MFB_CUDA(cudaMemsetAsync(s->Mvals.p, 0, (size_t)(c->nnz > 0 ? c->nnz : 1) * 8, st));
-  if (c->dim == 3) k_mass_values<3><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
+  if (c->kind == MFB_SHELL) k_mass_values<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
+  else if (c->dim == 3) k_mass_values<3><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
   else k_mass_values<2><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
   c->launches += 2;
   MFB_CUDA(cudaStreamSynchronize(st));
@@ -228,7 +233,8 @@ static int trial_energy(mfb_ctx* c, mfb_newton_state* s, double a, double* out) 
   else k_unproject_axpy<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, a, nV, s->xtrial.p);
   if (dim == 3) k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->xtrial.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
   else k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->xtrial.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);
-  if (dim == 3) k_inertia_energy<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
+  if (c->kind == MFB_SHELL) k_inertia_energy<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
+  else if (dim == 3) k_inertia_energy<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
   else k_inertia_energy<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
   c->launches += 3;
   double e_x = 0, e_s = 0, e_c = 0;
@@ -263,7 +269,8 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
     MFB_CUDA(cudaMemcpyAsync(s->b.p, rhs_mixed, (size_t)nf * 8, cudaMemcpyDeviceToDevice, st));
     if (dim == 3) {
       k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
-      k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
+      if (c->kind == MFB_SHELL) k_mass_rows_apply<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
+      else k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
       k_guess<3><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
     } else {
       k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);

@@ -9,7 +9,8 @@ mixed-stretch variable and no contact, on top of the oracle's MixedStretch (orac
   BDF<1> .................................................. src/time_integrators/BDF.cpp:7-27
   SystemMatrixPD::pre_solve / post_solve .................. src/linear_solvers/linear_system.h:18-44
   consistent mass matrix (assembled over elements) ........ deps/Bartels/src/linear_tet_mass_matrix.cpp:8-43,
-                                                            linear_tri2d_mass_matrix.cpp:8-36
+                                                            linear_tri2d_mass_matrix.cpp:8-36,
+                                                            shells: src/mesh/tri_mesh.cpp:43-69
 The linear system is solved directly (scipy SuperLU) unless cg=(precond, tol, max_iters) is given, in which case the
 Eigen ConjugateGradient restatement of oracle/pcg.py runs from the reference's initial guess
 (eigen_iterative_solver.h:44-57; the additive-CCD scale is 1 without contact).  PARITY UNPINNED: the reference ships
@@ -26,7 +27,8 @@ def mass_matrix(V, T, vols, density):
     """d*nV square consistent mass matrix: element blocks mass*(c0 on the diagonal, c1 off it) (x) I_d."""
     nV, d = V.shape
     npe = T.shape[1]
-    c0, c1 = (0.1, 0.05) if d == 3 else (1.0 / 6.0, 1.0 / 12.0)
+    # tets 1/10, 1/20 ; triangles (2D and shells: TriMesh::mass_matrix, src/mesh/tri_mesh.cpp:43-69) 1/6, 1/12
+    c0, c1 = (0.1, 0.05) if npe == 4 else (1.0 / 6.0, 1.0 / 12.0)
     mass = density * np.asarray(vols)
     rows, cols, vals = [], [], []
     for j in range(npe):

@@ -62,3 +62,25 @@ def test_newton_with_reference_default_solver_settings(built):
     assert np.all(np.diff(lg["energy"]) <= 1e-9 * np.abs(lg["energy"][:-1]))
     assert lg["cg_iters_total"] > 0
     gpu.close()
+
+
+def test_newton_history_matches_oracle_shell(built):
+    """config C5: TriMesh shell (x-dependent local Jacobian, triangle mass weights on doublearea*thickness/2) through two
+    device-resident time steps, cloth parameters of apps/cloth_sim.cpp:64-71."""
+    V, T, N = meshgen.shell_grid(12, 8)
+    fm = meshgen.pinned_free_map(V, ratio=0.05)
+    mu, la = meshgen.enu_to_lame(0.57e6, 0.3)
+    mats = [("Stable-Neohookean", mu, la)]
+    cpu = orc.OracleMixedStretch(V, T, fm, mats, normals=N, thickness=1e-3); cpu.reset()
+    gpu = mf.MixedStretch(V, T, fm, mats, normals=N, thickness=1e-3); gpu.reset()
+    ont = onewton.OracleNewton(cpu, V, T, fm, density=100.0, h=0.01)
+    gpu.newton_init(density=100.0, h=0.01)
+    for _ in range(2):
+        lo = ont.step(outer_steps=6, newton_tol=1e-10)
+        lg = gpu.newton_step(outer_steps=6, newton_tol=1e-10, precond=2, cg_tol=1e-13, cg_max_iters=5000)
+        compare_histories(lg, lo)
+        assert vec_rel(gpu.newton_positions(), ont.x) <= 1e-9
+        assert vec_rel(gpu.get("s"), cpu.get("s")) <= 1e-9
+    st = gpu.status()
+    assert st["nonfinite"] == 0 and st["polar_maxiter"] == 0
+    gpu.close()

@@ -63,3 +63,25 @@ def test_newton_history_behaves_like_newton():
         # second step starts from the new velocity
         log2 = nt.step(outer_steps=3)
         assert np.isfinite(log2["energy"]).all()
+
+
+def test_shell_newton_step_on_the_oracle():
+    """config C5 (TriMesh shell) through the time step: triangle mass weights on vol = doublearea*thickness/2
+    (tri_mesh.cpp:38-69), energy decreases monotonically, the decrement contracts, direct and CG solves agree."""
+    V, T, N = meshgen.shell_grid(8, 5)
+    fm = meshgen.pinned_free_map(V, ratio=0.05)
+    mu, la = meshgen.enu_to_lame(0.57e6, 0.3)
+    logs = []
+    for cg in (None, (2, 1e-13, 5000)):
+        var = orc.OracleMixedStretch(V, T, fm, [("Stable-Neohookean", mu, la)], normals=N, thickness=1e-3)
+        var.reset()
+        vols = var.get("vols")
+        M = onewton.mass_matrix(V, T, vols, 100.0)
+        one = np.tile(np.eye(3)[1], V.shape[0])
+        assert abs(one @ (M @ one) - 100.0 * vols.sum()) <= 1e-12 * 100.0 * vols.sum()
+        nt = onewton.OracleNewton(var, V, T, fm, density=100.0, h=0.01)
+        logs.append(nt.step(outer_steps=6, newton_tol=1e-10, cg=cg))
+    lo = logs[0]
+    assert np.all(np.diff(lo["energy"]) <= 1e-9 * np.abs(lo["energy"][:-1]))
+    assert lo["decrement"][-1] < 1e-3 * lo["decrement"][0]
+    compare_histories(logs[1], logs[0])
