@@ -26,6 +26,10 @@ struct MeshView {               // what MixedStretch pulls from mfem::Mesh (src/
   const int32_t* mat_id = nullptr;   // nE or null
   std::vector<mfb_material> materials;
   int device = 0;
+  // TriMesh (src/mesh/tri_mesh.cpp): triangles in 3D, dim = 3, T is nE x 3, per-face rest normals and a thickness
+  bool shell = false;
+  const double* normals = nullptr;   // nE x 3 row-major
+  double thickness = 1e-3;           // MaterialConfig::thickness (config.h:150)
 };
 
 template <int DIM>
@@ -38,7 +42,9 @@ class MixedStretch {
   explicit MixedStretch(const MeshView& mesh) {
     if (mesh.dim != DIM) throw std::runtime_error("MixedStretch: mesh dimension mismatch");
     mfb_mesh_desc d{};
-    d.elem_kind = DIM == 3 ? MFB_TET : MFB_TRI2D;
+    if (mesh.shell && DIM != 3) throw std::runtime_error("MixedStretch: a TriMesh shell is a DIM = 3 variable");
+    d.elem_kind = mesh.shell ? MFB_SHELL : (DIM == 3 ? MFB_TET : MFB_TRI2D);
+    d.normals = mesh.normals; d.thickness = mesh.thickness;
     d.nV = mesh.nV; d.nE = mesh.nE; d.T = mesh.T; d.Vref = mesh.Vref; d.free_map = mesh.free_map; d.mat_id = mesh.mat_id;
     d.n_mat = (int32_t)mesh.materials.size(); d.materials = mesh.materials.data(); d.device = mesh.device;
     check(mfb_create(&ctx_, &d));
@@ -135,6 +141,49 @@ class MixedStretch {
   int64_t nnz_ = 0;
   std::vector<double> s_, ds_, la_, s_dev_, la_dev_, lhs_vals_;
   bool lhs_valid_ = false;
+};
+
+// The linear solve of the condensed system as the reference's solver factory names it (linear_solver_factory.cpp:107-173):
+// lhs = M + A on the Assembler pattern, Eigen's ConjugateGradient recurrence, device vectors.
+struct PcgSolver {
+  int precond = 1;          // "eigen-pcg-diag" ; 2 = "eigen-pcg-block_jacobi" ; 0 = identity
+  double tol = 1e-4;        // SimConfig::itr_tol
+  int max_iters = 500;      // SimConfig::max_iterative_solver_iters
+  static PcgSolver by_name(const std::string& n) {
+    PcgSolver s;
+    if (n == "eigen-pcg-diag") s.precond = 1;
+    else if (n == "eigen-pcg-block_jacobi") s.precond = 2;
+    else if (n == "eigen-pcg-identity") s.precond = 0;
+    else throw std::runtime_error("PcgSolver: no device implementation of solver '" + n + "'");
+    return s;
+  }
+};
+
+// NewtonOptimizer<DIM>::step (src/optimizers/newton_optimizer.cpp:14-139) for one mesh, the mixed-stretch variable and no
+// contact, resident on the device: Displacement + BDF1 + SystemMatrixPD + line search (include/mfem_b200.h, mfb_newton_*).
+template <int DIM>
+class NewtonStep {
+ public:
+  NewtonStep(MixedStretch<DIM>& var, const MeshView& mesh, double density, double h, const double* force = nullptr,
+             const double* x0 = nullptr, const double* v0 = nullptr) : var_(var), nx_((size_t)DIM * mesh.nV) {
+    check(mfb_newton_init(var_.ctx(), mesh.free_map, density, h, force, x0, v0));
+  }
+  ~NewtonStep() { mfb_newton_free(var_.ctx()); }
+  // one time step; returns the OptimizerData columns (newton_optimizer.cpp:92-97)
+  mfb_newton_log step(const PcgSolver& solver = PcgSolver(), int outer_steps = 5, int ls_iters = 20, double newton_tol = 1e-10) {
+    mfb_newton_opts o{};
+    o.outer_steps = outer_steps; o.ls_iters = ls_iters; o.newton_tol = newton_tol;
+    o.precond = solver.precond; o.cg_tol = solver.tol; o.cg_max_iters = solver.max_iters;
+    mfb_newton_log log{};
+    check(mfb_newton_step(var_.ctx(), &o, &log));
+    return log;
+  }
+  std::vector<double> positions() { std::vector<double> x(nx_); check(mfb_newton_positions(var_.ctx(), x.data())); return x; }
+
+ private:
+  void check(int rc) const { if (rc != MFB_OK) throw std::runtime_error(std::string("mfem_b200: ") + mfb_last_error_string()); }
+  MixedStretch<DIM>& var_;
+  size_t nx_;
 };
 
 }  // namespace mfb

@@ -209,7 +209,10 @@ def test_host_cpp_shim_compiles_and_links(built, tmp_path):
     src.write_text('#include "mixed-fem_b200/host/mixed_stretch.hpp"\n'
                    'template class mfb::MixedStretch<3>;\ntemplate class mfb::MixedStretch<2>;\n'
                    'int main(int argc, char**) { if (argc > 99) { mfb::MeshView m; mfb::MixedStretch<3> v(m); v.reset(); '
-                   'std::vector<double> x; v.update(x, 0.1); auto r = v.rhs(); v.solve(r); return (int)v.lhs().nnz; } return 0; }\n')
+                   'std::vector<double> x; v.update(x, 0.1); auto r = v.rhs(); v.solve(r); '
+                   'mfb::MeshView sh; sh.shell = true; mfb::MixedStretch<3> w(sh); '
+                   'mfb::NewtonStep<3> nt(v, m, 1000.0, 0.0333); auto lg = nt.step(mfb::PcgSolver::by_name("eigen-pcg-block_jacobi")); '
+                   'return (int)v.lhs().nnz + lg.n_iters + (int)nt.positions().size(); } return 0; }\n')
     exe = tmp_path / "shim"
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     libdir = os.path.join(ROOT, "mixed-fem_b200")
