@@ -172,6 +172,22 @@ int mfb_newton_positions(mfb_ctx* ctx, double* x_full);                         
 int mfb_newton_positions_dev(mfb_ctx* ctx, double** x_full_dev, const double** mass_values_dev);
 void mfb_newton_free(mfb_ctx* ctx);
 
+/* ---- multi-GPU (the reference has no counterpart: it is a single-address-space OpenMP code).
+ * One process per GPU, each with a context on ITS slab of elements (locally renumbered vertices).  The assembled
+ * matrix stays sub-assembled; vectors are summed at the free vertices shared between slabs with one ncclAllReduce over
+ * a packed buffer laid out over ALL shared vertices.  After mfb_comm_init + mfb_comm_set_interface, mfb_pcg_dev and
+ * mfb_newton_step run distributed: every rank calls them collectively with consistent (already summed) vectors. ---- */
+int mfb_comm_unique_id(char* id128);                                  /* rank 0: ncclGetUniqueId; broadcast the 128 bytes */
+int mfb_comm_init(mfb_ctx* ctx, const char* id128, int rank, int world);   /* ncclCommInitRank on the context's device */
+/* if_local[i] = local free vertex id of this rank's i-th interface vertex, if_pos[i] = its slot among the n_shared
+ * shared vertices (same numbering on all ranks); dot_weight[nF local] = 1 for interior vertices and for interface
+ * vertices this rank owns, 0 for copies owned by another rank (so that global dot products count every vertex once) */
+int mfb_comm_set_interface(mfb_ctx* ctx, const int32_t* if_local, const int32_t* if_pos, int32_t n_if_local, int32_t n_shared,
+                           const double* dot_weight);
+/* a (ncomp_a doubles per local free vertex) and optionally b <- sum over ranks at interface vertices, one collective */
+int mfb_interface_sum_dev(mfb_ctx* ctx, double* a_dev, int ncomp_a, double* b_dev, int ncomp_b);
+int mfb_allreduce_dev(mfb_ctx* ctx, double* v_dev, int n, int op);   /* op 0 sum, 1 max; stream-ordered */
+
 /* ---- instrumentation ---- */
 int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
 int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0) */

@@ -29,6 +29,7 @@ EXPORTS = [
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
     "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
     "mfb_newton_init", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
+    "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_interface_sum_dev", "mfb_allreduce_dev",
 ]
 
 
@@ -106,6 +107,11 @@ def lib():
     L.mfb_scatter_map.argtypes = [vp, C.POINTER(ip), C.POINTER(ip)]
     L.mfb_reset.argtypes = [vp, dp]
     L.mfb_update.argtypes = [vp, dp, C.c_double]
+    L.mfb_comm_unique_id.argtypes = [C.c_char_p]
+    L.mfb_comm_init.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+    L.mfb_comm_set_interface.argtypes = [vp, ip, ip, C.c_int32, C.c_int32, dp]
+    L.mfb_interface_sum_dev.argtypes = [vp, vp, C.c_int, vp, C.c_int]
+    L.mfb_allreduce_dev.argtypes = [vp, vp, C.c_int, C.c_int]
     L.mfb_update_dev.argtypes = [vp, vp, C.c_double]
     L.mfb_rhs.argtypes = [vp, dp]
     L.mfb_rhs_dev.argtypes = [vp, C.POINTER(vp)]
@@ -186,6 +192,7 @@ class MixedStretch:
         d.T, d.Vref, d.free_map = _ip(T), _dp(V), _ip(fm)
         d.mat_id = _ip(mid) if mid is not None else None
         d.n_mat, d.materials, d.device = len(materials), mats, device
+        self.device = device
         self.h = C.c_void_p()
         self._check(self.L.mfb_create(C.byref(self.h), C.byref(d)))
         nF, nnz = C.c_int32(), C.c_int64()
@@ -212,6 +219,12 @@ class MixedStretch:
                 "energy": np.array(log.energy[:n]), "energy_res": np.array(log.energy_res[:n]),
                 "decrement": np.array(log.decrement[:n]), "alpha": np.array(log.alpha[:n]),
                 "cg_iters": np.array(log.cg_iters[:n]), "cg_error": np.array(log.cg_error[:n]), "ls_iters": np.array(log.ls_iters[:n])}
+
+    def newton_positions_dev(self):
+        """(device pointer of x, d*nV ; device pointer of the PMP^T values on the Assembler pattern)"""
+        xp, mp = C.c_void_p(), C.c_void_p()
+        self._check(self.L.mfb_newton_positions_dev(self.h, C.byref(xp), C.byref(mp)))
+        return xp.value, mp.value
 
     def newton_positions(self):
         out = np.empty(self.dim * self.nV)
@@ -396,6 +409,30 @@ class MixedStretch:
         n = C.c_int64()
         self._check(self.L.mfb_num_kernel_launches(self.h, C.byref(n), int(reset)))
         return n.value
+
+    # ---- multi-GPU (one process per GPU; `local` is this rank's partition.LocalProblem) ----
+    def comm_init(self, local):
+        """NCCL communicator inside the library (id broadcast through torch.distributed: plumbing) + the interface
+        description.  Afterwards pcg_dev / newton_step are collective calls."""
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        idbuf = C.create_string_buffer(128)
+        if rank == 0:
+            self._check(self.L.mfb_comm_unique_id(idbuf))
+        t = torch.frombuffer(bytearray(idbuf.raw), dtype=torch.uint8).clone()
+        if dist.get_backend() == "nccl":
+            t = t.cuda(self.device)
+        dist.broadcast(t, 0)
+        raw = bytes(t.cpu().numpy().tobytes())
+        self._check(self.L.mfb_comm_init(self.h, raw, rank, world))
+        il = np.ascontiguousarray(local.if_local, dtype=np.int32)
+        ipos = np.ascontiguousarray(local.if_pos, dtype=np.int32)
+        w = _f64(local.dot_weight)
+        self._check(self.L.mfb_comm_set_interface(self.h, _ip(il), _ip(ipos), int(il.size), int(local.n_shared), _dp(w)))
+
+    def interface_sum_dev(self, a_ptr, ncomp_a, b_ptr=None, ncomp_b=0):
+        self._check(self.L.mfb_interface_sum_dev(self.h, C.c_void_p(a_ptr), ncomp_a, C.c_void_p(b_ptr) if b_ptr else None, ncomp_b))
 
     # ---- linear solver side (device pointers) ----
     def spmv_dev(self, x_ptr, y_ptr, M_ptr=None):

@@ -378,6 +378,7 @@ extern "C" void mfb_destroy(mfb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   mfb_newton_free(c);
+  mfb::comm_free(c);
   if (c->h_scal) cudaFreeHost(c->h_scal);
   delete c;
 }

@@ -40,6 +40,14 @@ struct DBuf {   // plain device buffer
 
 }  // namespace mfb
 
+struct mfb_ctx;
+namespace mfb {
+// mfb_dist.cu (no-ops when world == 1)
+int interface_sum(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns);
+int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop);
+void comm_free(mfb_ctx* c);
+}  // namespace mfb
+
 struct mfb_ctx {
   int device = 0;
   cudaStream_t stream = 0;
@@ -87,6 +95,13 @@ struct mfb_ctx {
   std::vector<cudaEvent_t> ev0, ev1;
   int ev_count = 0;
   void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)
+  // multi-GPU (mfb_dist.cu): NCCL communicator, this rank's interface vertices (local free id, slot in the packed
+  // buffer over all shared vertices), dot-product weights (1 interior / owned interface vertex, 0 copy owned elsewhere)
+  void* comm = nullptr;
+  int rank = 0, world = 1;
+  mfb::DBuf<int> if_local, if_pos;
+  int n_if_local = 0, n_shared = 0;
+  mfb::DBuf<double> if_buf, dot_w;
 
   mfb::DevMesh mesh() const {
     mfb::DevMesh m;

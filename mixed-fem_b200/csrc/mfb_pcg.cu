@@ -7,6 +7,7 @@
 // SpMV is HBM-bound: 8 B per stored value (+8 B when M is given) + 4/d^2 B of column index per value (one block-column
 // index per d x d block, not one per scalar entry) + the vectors.
 #include "mfb_ctx.cuh"
+#include <algorithm>
 
 using namespace mfb;
 
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
                                                     const double* __restrict__ p, const double* __restrict__ t,
                                                     double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
                                                     const double* __restrict__ dinv, int nF, int mode,
-                                                    double* __restrict__ part_out) {
+                                                    double* __restrict__ part_out, const double* __restrict__ w, int dist) {
   __shared__ double sh[8];
   if (scal[2] != 0.0) return;
   const double alpha = scal[(iter + 1) & 1] / scal[7];
@@ -300,7 +301,12 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
       }
     }
 #pragma unroll
-    for (int k = 0; k < DIM; ++k) { z[DIM * gi + k] = zv[k]; rr += rv[k] * rv[k]; rz += rv[k] * zv[k]; }
+    for (int k = 0; k < DIM; ++k) z[DIM * gi + k] = zv[k];
+    double lr = 0.0, lz = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) { lr += rv[k] * rv[k]; lz += rv[k] * zv[k]; }
+    const double wi = w ? w[gi] : 1.0;               // multi-GPU: every global vertex is counted by exactly one rank
+    rr += wi * lr; rz += wi * lz;
   }
   const double s0 = block_sum_256(rr, sh);
   const double s1 = block_sum_256(rz, sh);
@@ -309,10 +315,13 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
     const double rr2 = sum_partials_all(part_out, sh);
     const double rz2 = sum_partials_all(part_out + kPcgBlocks, sh);
     if (threadIdx.x == 0) {
-      scal[5] = rr2;
-      scal[iter & 1] = rz2;
-      if (rr2 < scal[6]) { scal[2] = 1.0; scal[3] = (double)iter; }
-      else scal[3] = (double)(iter + 1);
+      if (dist) { scal[8] = rr2; scal[9] = rz2; }     // local sums: all-reduced, then k_pcg_dir_dist decides
+      else {
+        scal[5] = rr2;
+        scal[iter & 1] = rz2;
+        if (rr2 < scal[6]) { scal[2] = 1.0; scal[3] = (double)iter; }
+        else scal[3] = (double)(iter + 1);
+      }
     }
   }
 }
@@ -323,6 +332,95 @@ __global__ void __launch_bounds__(256) k_pcg_dir(const double* __restrict__ scal
   if (scal[2] != 0.0) return;
   const double beta = scal[iter & 1] / scal[(iter + 1) & 1];
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) p[i] = fma(beta, p[i], z[i]);
+}
+// multi-GPU: scal[8], scal[9] = global r.r, r.z of this iteration (all-reduced).  Every block takes the same decision; a
+// block that starts after block 0 has set the flag returns early, which is harmless (the flag means: converged).
+__global__ void __launch_bounds__(256) k_pcg_dir_dist(double* __restrict__ scal, int iter, const double* __restrict__ z,
+                                                      double* __restrict__ p, int n) {
+  if (scal[2] != 0.0) return;
+  const double rr = scal[8], rz = scal[9], absOld = scal[(iter + 1) & 1];
+  const bool conv = rr < scal[6];
+  if (!conv) {
+    const double beta = rz / absOld;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) p[i] = fma(beta, p[i], z[i]);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    scal[5] = rr;
+    if (conv) { scal[2] = 1.0; scal[3] = (double)iter; }
+    else { scal[iter & 1] = rz; scal[3] = (double)(iter + 1); }
+  }
+}
+// weighted two-stage dots (w per vertex, dim entries each)
+__global__ void __launch_bounds__(256) k_dot2w(const double* __restrict__ a, const double* __restrict__ b, const double* __restrict__ c2,
+                                               const double* __restrict__ d2, const double* __restrict__ w, int dim, int n,
+                                               double* partials, int np) {
+  __shared__ double sh[2][8];
+  double s0 = 0.0, s1 = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double wi = w[i / dim];
+    s0 += wi * a[i] * b[i];
+    if (c2) s1 += wi * c2[i] * d2[i];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { s0 += __shfl_down_sync(0xffffffffu, s0, o); s1 += __shfl_down_sync(0xffffffffu, s1, o); }
+  if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s0; sh[1][threadIdx.x >> 5] = s1; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r0 = 0.0, r1 = 0.0;
+    for (int i = 0; i < 8; ++i) { r0 += sh[0][i]; r1 += sh[1][i]; }
+    partials[blockIdx.x] = r0; partials[np + blockIdx.x] = r1;
+  }
+}
+// diagonal d x d blocks of the (local, sub-assembled) operator, d*d per block-row: summed over ranks, then inverted
+template <int DIM>
+__global__ void k_extract_diag(const int* __restrict__ blockptr, const int* __restrict__ diagblk, int nF, const double* __restrict__ A,
+                               double* __restrict__ D) {
+  const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gi >= nF) return;
+  const int b0 = blockptr[gi], nbr = blockptr[gi + 1] - b0, rank = diagblk[gi] - b0;
+  const int64_t base = (int64_t)DIM * DIM * b0;
+#pragma unroll
+  for (int r = 0; r < DIM; ++r)
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) D[(int64_t)gi * DIM * DIM + r * DIM + c] = A[base + (int64_t)r * DIM * nbr + DIM * rank + c];
+}
+template <int DIM>
+__global__ void k_invert_diag(int nF, int mode, double* __restrict__ D) {
+  const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gi >= nF) return;
+  double* d = D + (int64_t)gi * DIM * DIM;
+  double a[DIM][DIM], I[DIM][DIM];
+#pragma unroll
+  for (int r = 0; r < DIM; ++r)
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) a[r][c] = d[r * DIM + c];
+  if (mode == 1) {
+#pragma unroll
+    for (int r = 0; r < DIM; ++r)
+#pragma unroll
+      for (int c = 0; c < DIM; ++c) I[r][c] = (r == c) ? ((a[r][r] != 0.0) ? 1.0 / a[r][r] : 1.0) : 0.0;
+  } else if constexpr (DIM == 2) {
+    const double id = 1.0 / (a[0][0] * a[1][1] - a[0][1] * a[1][0]);
+    I[0][0] = a[1][1] * id; I[0][1] = -a[0][1] * id; I[1][0] = -a[1][0] * id; I[1][1] = a[0][0] * id;
+  } else {
+    const double c00 = a[1][1] * a[2][2] - a[1][2] * a[2][1];
+    const double c01 = a[1][2] * a[2][0] - a[1][0] * a[2][2];
+    const double c02 = a[1][0] * a[2][1] - a[1][1] * a[2][0];
+    const double id = 1.0 / (a[0][0] * c00 + a[0][1] * c01 + a[0][2] * c02);
+    I[0][0] = c00 * id;
+    I[0][1] = (a[0][2] * a[2][1] - a[0][1] * a[2][2]) * id;
+    I[0][2] = (a[0][1] * a[1][2] - a[0][2] * a[1][1]) * id;
+    I[1][0] = c01 * id;
+    I[1][1] = (a[0][0] * a[2][2] - a[0][2] * a[2][0]) * id;
+    I[1][2] = (a[0][2] * a[1][0] - a[0][0] * a[1][2]) * id;
+    I[2][0] = c02 * id;
+    I[2][1] = (a[0][1] * a[2][0] - a[0][0] * a[2][1]) * id;
+    I[2][2] = (a[0][0] * a[1][1] - a[0][1] * a[1][0]) * id;
+  }
+#pragma unroll
+  for (int r = 0; r < DIM; ++r)
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) d[r * DIM + c] = I[r][c];
 }
 // lhs = A + M, once per solve (linear_system.h: lhs_ = M + A is formed once per Newton iteration)
 __global__ void k_sum_values(const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ o, int64_t n) {
@@ -371,6 +469,9 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
                            int* iters_out, double* relres_out) {
   CHECK_CTX(c);
   if (!b || !x || precond < 0 || precond > 2) return MFB_ERR_INVALID;
+  const bool dist = c->world > 1;
+  if (dist && !c->dot_w.p) { g_last_error = "mfb_pcg_dev: multi-GPU context without mfb_comm_set_interface"; return MFB_ERR_INVALID; }
+  const double* w = dist ? c->dot_w.p : nullptr;
   const int n = c->dim * c->nF;
   const int dd = c->dim * c->dim;
   int rc;
@@ -383,7 +484,7 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
   if (c->pcg_part.n < (size_t)5 * kPcgBlocks) { if ((rc = c->pcg_part.alloc((size_t)5 * kPcgBlocks))) return rc; }
   cudaStream_t st = c->stream;
   double *r = c->pcg_r.p, *p = c->pcg_p.p, *z = c->pcg_z.p, *t = c->pcg_t.p;
-  // the operator of this solve: one value array, L = A + M
+  // the operator of this solve: one value array, L = A + M (multi-GPU: this rank's sub-assembled part of it)
   const double* L = c->Avals.p;
   if (Mv) {
     if (c->pcg_lhs.n < (size_t)c->nnz + 1) { if ((rc = c->pcg_lhs.alloc((size_t)c->nnz + 1))) return rc; }
@@ -393,19 +494,39 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
   }
   auto spmv_L = [&](const double* xx, double* yy) {
     const int64_t threads = (int64_t)c->nF * 16;
+    if (c->nF == 0) return;
     if (c->dim == 3) k_spmv<3, false><<<nblk(threads), 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, nullptr, xx, yy);
     else k_spmv<2, false><<<nblk(threads), 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, nullptr, xx, yy);
     c->launches += 1;
   };
-  if (precond) {
-    if (c->dim == 3) k_build_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
-    else k_build_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
-    c->launches += 1;
+  auto dots = [&](const double* a0, const double* b0, const double* a1, const double* b1, int out0, int out1) -> int {
+    if (!dist) return dot2(c, a0, b0, a1, b1, n, out0, out1);
+    k_dot2w<<<kDotBlocks, 256, 0, st>>>(a0, b0, a1, b1, w, c->dim, n, c->partials.p, kDotBlocks);
+    k_finish2<<<1, 256, 0, st>>>(c->partials.p, kDotBlocks, c->scal.p + out0, out1 >= 0 ? c->scal.p + out1 : nullptr);
+    c->launches += 2;
+    int e = allreduce_scalars(c, c->scal.p + out0, 1, false);
+    if (!e && out1 >= 0) e = allreduce_scalars(c, c->scal.p + out1, 1, false);
+    return e;
+  };
+  if (precond && c->nF) {
+    if (!dist) {
+      if (c->dim == 3) k_build_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
+      else k_build_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
+      c->launches += 1;
+    } else {       // the diagonal blocks of the GLOBAL operator: local blocks summed at the interface, then inverted
+      if (c->dim == 3) k_extract_diag<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, c->pcg_dinv.p);
+      else k_extract_diag<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, c->pcg_dinv.p);
+      if ((rc = interface_sum(c, c->pcg_dinv.p, dd, nullptr, 0, nullptr, 0))) return rc;
+      if (c->dim == 3) k_invert_diag<3><<<nblk(c->nF), 256, 0, st>>>(c->nF, precond, c->pcg_dinv.p);
+      else k_invert_diag<2><<<nblk(c->nF), 256, 0, st>>>(c->nF, precond, c->pcg_dinv.p);
+      c->launches += 2;
+    }
   }
   // residual = b - L x ; |b|^2 ; |r|^2
-  if (c->nF) spmv_L(x, t);
-  k_residual<<<nblk(n), 256, 0, st>>>(b, t, r, n); c->launches += 1;
-  if ((rc = dot2(c, b, b, r, r, n, 4, 5))) return rc;                 // scal[4] = |b|^2, scal[5] = |r|^2
+  spmv_L(x, t);
+  if (dist && (rc = interface_sum(c, t, c->dim, nullptr, 0, nullptr, 0))) return rc;
+  if (n) { k_residual<<<nblk(n), 256, 0, st>>>(b, t, r, n); c->launches += 1; }
+  if ((rc = dots(b, b, r, r, 4, 5))) return rc;                        // scal[4] = |b|^2, scal[5] = |r|^2
   MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
   MFB_CUDA(cudaStreamSynchronize(st));
   const double rhsNorm2 = c->h_scal[4];
@@ -419,28 +540,35 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
   const double threshold = tol * tol * rhsNorm2;
   if (resNorm2 >= threshold && max_iters > 0) {
     // p = Dinv r ; absNew = r.p
-    if (c->dim == 3) k_apply_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
-    else k_apply_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
-    c->launches += 1;
-    if ((rc = dot2(c, r, p, nullptr, nullptr, n, 0, -1))) return rc;  // scal[0] = absNew
+    if (c->nF) {
+      if (c->dim == 3) k_apply_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
+      else k_apply_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
+      c->launches += 1;
+    }
+    if ((rc = dots(r, p, nullptr, nullptr, 0, -1))) return rc;         // scal[0] = absNew
     double* part = c->pcg_part.p;                   // pt[G] | rr[G] | rz[G] | two ticket counters
     unsigned* tickets = reinterpret_cast<unsigned*>(part + 3 * kPcgBlocks);
     k_pcg_init<<<1, 1, 0, st>>>(c->scal.p, tol, tickets); c->launches += 1;
-    const unsigned gv = nblk(c->nF) < (unsigned)kPcgBlocks ? nblk(c->nF) : (unsigned)kPcgBlocks;      // one vertex per thread
-    const unsigned gn = nblk(n) < (unsigned)kPcgBlocks ? nblk(n) : (unsigned)kPcgBlocks;
-    const unsigned gs = nblk((int64_t)c->nF * 16) < (unsigned)kSpmvBlocks ? nblk((int64_t)c->nF * 16) : (unsigned)kSpmvBlocks;
+    const unsigned one = 1u;
+    const unsigned gv = std::max(one, std::min(nblk(c->nF), (unsigned)kPcgBlocks));      // one vertex per thread
+    const unsigned gn = std::max(one, std::min(nblk(n), (unsigned)kPcgBlocks));
+    const unsigned gs = std::max(one, std::min(nblk((int64_t)c->nF * 16), (unsigned)kSpmvBlocks));
     int launched = 0, batch = 8;
     while (launched < max_iters) {
       const int nb = (max_iters - launched < batch) ? max_iters - launched : batch;
       for (int k = launched; k < launched + nb; ++k) {
-        if (c->dim == 3) {
-          k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
-          k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks);
+        if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
+        else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
+        // multi-GPU: t <- sum over ranks at the interface and p.t <- sum of the local p.(L_r p), one collective
+        if (dist && (rc = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1))) return rc;
+        if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0);
+        else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0);
+        if (dist) {
+          if ((rc = allreduce_scalars(c, c->scal.p + 8, 2, false))) return rc;
+          k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
         } else {
-          k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
-          k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks);
+          k_pcg_dir<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
         }
-        k_pcg_dir<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
       }
       launched += nb;
       c->launches += 3 * nb;

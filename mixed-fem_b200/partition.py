@@ -25,7 +25,7 @@ def partition_elements(V, T, nparts):
 class LocalProblem:
     """The piece of the global problem one rank owns."""
 
-    def __init__(self, V, T, free_map, elems, shared_free_ids):
+    def __init__(self, V, T, free_map, elems, shared_free_ids, shared_owner=None, rank=0):
         elems = np.asarray(elems)
         Tg = T[elems]
         self.vmap = np.unique(Tg)                         # local vertex -> global vertex (ascending)
@@ -46,6 +46,11 @@ class LocalProblem:
         self.if_local = np.nonzero(hit)[0].astype(np.int64)     # local free ids on the interface
         self.if_pos = pos[hit].astype(np.int64)                 # their slots in the packed buffer
         self.n_shared = int(shared_free_ids.size)
+        # global dot products count every vertex once: weight 1 for interior vertices and for interface vertices this
+        # rank owns (owner = lowest rank touching the vertex), 0 for copies owned elsewhere
+        self.dot_weight = np.ones(self.free_l2g.size)
+        if shared_owner is not None and self.if_local.size:
+            self.dot_weight[self.if_local] = (np.asarray(shared_owner)[self.if_pos] == rank).astype(np.float64)
 
     def restrict_vertex_vector(self, xg, dim):
         """global vertex vector (dim*nV) -> local (dim*nVl)"""
@@ -55,21 +60,30 @@ class LocalProblem:
         return np.ascontiguousarray(vg.reshape(-1, n)[self.elems]).reshape(-1)
 
 
-def shared_free_vertices(T, free_map, parts):
-    """ascending global free ids of the vertices touched by more than one part"""
+def shared_free_vertices(T, free_map, parts, with_owner=False):
+    """ascending global free ids of the vertices touched by more than one part (and, optionally, the lowest rank
+    touching each: its owner)"""
     nV = len(free_map)
     count = np.zeros(nV, dtype=np.int32)
-    for p in parts:
-        count[np.unique(T[p])] += 1
+    owner = np.full(nV, -1, dtype=np.int32)
+    for r, p in enumerate(parts):
+        u = np.unique(T[p])
+        count[u] += 1
+        first = u[owner[u] < 0]
+        owner[first] = r
     fm = np.asarray(free_map)
     sh = np.nonzero((count > 1) & (fm >= 0))[0]
-    return np.sort(fm[sh]).astype(np.int64)
+    order = np.argsort(fm[sh], kind="stable")
+    ids = fm[sh][order].astype(np.int64)
+    if with_owner:
+        return ids, owner[sh][order]
+    return ids
 
 
 def make_local(V, T, free_map, nparts, rank):
     parts = partition_elements(V, T, nparts)
-    shared = shared_free_vertices(T, free_map, parts)
-    return LocalProblem(V, T, free_map, parts[rank], shared), parts, shared
+    shared, owner = shared_free_vertices(T, free_map, parts, with_owner=True)
+    return LocalProblem(V, T, free_map, parts[rank], shared, owner, rank), parts, shared
 
 
 def interface_sum_numpy(local, vec, dim, allreduce):
