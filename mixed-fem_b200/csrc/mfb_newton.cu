@@ -171,6 +171,16 @@ int read_scalar(mfb_ctx* c, const double* dev, double* out) {
   return MFB_OK;
 }
 
+// multi-GPU: a host scalar summed over ranks (through the device: NCCL reduces device memory)
+int rank_sum(mfb_ctx* c, double* v) {
+  if (c->world <= 1) return MFB_OK;
+  c->h_scal[8] = *v;
+  MFB_CUDA(cudaMemcpyAsync(c->scal.p + 12, c->h_scal + 8, 8, cudaMemcpyHostToDevice, c->stream));
+  int rc = allreduce_scalars(c, c->scal.p + 12, 1, false);
+  if (rc) return rc;
+  return read_scalar(c, c->scal.p + 12, v);
+}
+
 int sum_partials(mfb_ctx* c, int n, double* out) {
   k_sum_partials<<<1, 256, 0, c->stream>>>(c->partials.p, n, c->scal.p);
   c->launches += 1;
@@ -244,8 +254,8 @@ static int trial_energy(mfb_ctx* c, mfb_newton_state* s, double a, double* out) 
   c->launches += 1;
   if ((rc = mfb_energy_dev(c, s->strial.p, &e_s))) return rc;
   if ((rc = mfb_constraint_value_dev(c, s->xtrial.p, s->strial.p, &e_c))) return rc;
-  *out = e_x + h2 * e_s + e_c;
-  return MFB_OK;
+  *out = e_x + h2 * e_s + e_c;          // multi-GPU: the three terms are sums over this rank's elements
+  return rank_sum(c, out);
 }
 
 extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_log* log) {
@@ -278,6 +288,8 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
       k_guess<2><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
     }
     c->launches += 3;
+    // multi-GPU: both parts of b are element sums of this rank's slab: one interface sum makes b consistent
+    if ((rc = interface_sum(c, s->b.p, dim, nullptr, 0, nullptr, 0))) return rc;
     int cg_it = 0; double cg_res = 0;
     if ((rc = mfb_pcg_dev(c, s->Mvals.p, s->b.p, s->dx.p, o->precond, o->cg_tol, o->cg_max_iters, &cg_it, &cg_res))) return rc;
     // post_solve: x.delta = dx ; var->solve(dx)
@@ -285,12 +297,14 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
     // substep(): decrement = max(|dx|_inf, |ds|_inf)
     double mx = 0, ms = 0;
     k_absmax_soa<<<256, 256, 0, st>>>(s->dx.p, 1, (int)nf, nf, c->partials.p);
-    k_max_partials<<<1, 256, 0, st>>>(c->partials.p, 256, c->scal.p);
-    if ((rc = read_scalar(c, c->scal.p, &mx))) return rc;
-    k_absmax_soa<<<256, 256, 0, st>>>(c->ds.p, c->N, c->nE, c->ld, c->partials.p);
-    k_max_partials<<<1, 256, 0, st>>>(c->partials.p, 256, c->scal.p);
-    if ((rc = read_scalar(c, c->scal.p, &ms))) return rc;
+    k_max_partials<<<1, 256, 0, st>>>(c->partials.p, 256, c->scal.p + 10);
+    k_absmax_soa<<<256, 256, 0, st>>>(c->ds.p, c->N, c->nE, c->ld, c->partials.p + 256);
+    k_max_partials<<<1, 256, 0, st>>>(c->partials.p + 256, 256, c->scal.p + 11);
     c->launches += 4;
+    if ((rc = allreduce_scalars(c, c->scal.p + 10, 2, true))) return rc;      // multi-GPU: max over ranks
+    MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p + 10, 16, cudaMemcpyDeviceToHost, st));
+    MFB_CUDA(cudaStreamSynchronize(st));
+    mx = c->h_scal[0]; ms = c->h_scal[1];
     grad_norm = mx > ms ? mx : ms;
     double alpha = 1.0;
     if ((rc = trial_energy(c, s, 0.0, &E))) return rc;

@@ -29,3 +29,9 @@ def test_distributed_pcg_matches_single_gpu(built):
     if _ngpu() < 2:
         pytest.skip("needs 2 GPUs")
     _torchrun("run_dist_pcg.py", 2, 29531)
+
+
+def test_distributed_newton_step_matches_single_gpu(built):
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    _torchrun("run_dist_newton.py", 2, 29533)
