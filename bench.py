@@ -194,14 +194,15 @@ def gpu_arm(args):
     rhs_host = torch.empty(3 * ms.nfree, dtype=torch.float64).pin_memory()
     iface = None
     if world > 1:
-        iface = partition.TorchInterface(loc, 3, dev)
-        gx = torch.as_tensor(DevArray(ms.field_dev("grad_x")[0], (ms.nfree, 3)), device=dev)
-        rh = torch.as_tensor(DevArray(ms.rhs_dev(), (ms.nfree, 3)), device=dev)
+        # the exchange step lives in the library: pack -> ncclAllReduce -> unpack of grad_x_ | rhs_ at the shared vertices
+        ms.comm_init(loc)
+        gx_ptr, rh_ptr = ms.field_dev("grad_x")[0], ms.rhs_dev()
+        iface = lambda: ms.interface_sum_dev(gx_ptr, 3, rh_ptr, 3)
 
     def step(i):
         ms.update_dev(xs_dev[i % 2].data_ptr(), DT)
         if iface is not None:
-            iface.sum2(gx, rh)
+            iface()
 
     def sync():
         torch.cuda.synchronize()
@@ -237,7 +238,7 @@ def gpu_arm(args):
         xh = xs_host[i % 2]
         ms._check(ms.L.mfb_update(ms.h, C.cast(xh.data_ptr(), C.POINTER(C.c_double)), DT))
         if iface is not None:
-            iface.sum2(gx, rh)
+            iface()
         ms._check(ms.L.mfb_rhs(ms.h, C.cast(rhs_host.data_ptr(), C.POINTER(C.c_double))))
     for i in range(2):
         e2e_step(i)
@@ -299,9 +300,12 @@ def gpu_arm(args):
             "polar_iters_per_tet": st0["polar_iters"] / max(nE_l, 1), "eig_sweeps_per_tet": st0["eig_sweeps"] / max(nE_l, 1),
             "psd_slow_fraction": st0.get("psd_slow", 0) / max(nE_l, 1),
         }
-        if world == 1 and not args.no_newton:
-            ms.close()
-            out["newton_iteration"] = newton_leg(args)
+    if not args.no_newton:
+        ms.close()
+        nl = newton_leg(args, rank, world, local_rank)
+        if rank == 0:
+            out["newton_iteration"] = nl
+    if rank == 0:
         if world == 1 and not args.no_cpu:
             cx, cy, cz = args.cpu_grid
             _, info = cpu_arm(cx, cy, cz, args.cpu_seconds)
@@ -311,34 +315,51 @@ def gpu_arm(args):
         dist.destroy_process_group()
 
 
-def newton_leg(args):
-    """Second metric of BASELINE.json (ms per Newton iteration) on config C3: 55^3 x 6 = 998 250 tets, ARAP, one time step
+def newton_leg(args, rank=0, world=1, local_rank=0):
+    """Metric m2 of SURVEY.md section 8d: ms per Newton iteration on config C3 (55^3 x 6 = 998 250 tets, ARAP), one time step
     of the device-resident Newton driver with the reference's default solver settings (eigen-pcg-diag, itr_tol 1e-4,
-    <= 500 CG iterations, outer_steps 3): update + rhs + lhs = M + A + PCG + solve(dx) + line search per iteration."""
+    <= 500 CG iterations, outer_steps 3): update + rhs + lhs = M + A + PCG + solve(dx) + line search per iteration.
+    N > 1: the same mesh in N element slabs, mfb_newton_step as a collective call (distributed PCG inside the library)."""
     import torch
+    import torch.distributed as dist
     import mixed_fem_b200 as mf
-    from mixed_fem_b200 import meshgen
+    from mixed_fem_b200 import meshgen, partition
     nx, ny, nz = args.newton_grid
     h = 1.0 / nx
     V, T = meshgen.kuhn_grid(nx, ny, nz, h=h)
     fm = meshgen.pinned_free_map(V)
     mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
-    ms = mf.MixedStretch(V, T, fm, [("ARAP", mu, la)])
-    ms.reset()
+    nE = T.shape[0]
+    if world > 1:
+        loc, _, _ = partition.make_local(V, T, fm, world, rank)
+        ms = mf.MixedStretch(loc.V, loc.T, loc.free_map, [("ARAP", mu, la)], device=local_rank)
+        ms.reset()
+        ms.comm_init(loc)
+    else:
+        ms = mf.MixedStretch(V, T, fm, [("ARAP", mu, la)], device=local_rank)
+        ms.reset()
     ms.newton_init(density=1000.0, h=DT)
     ms.newton_step(outer_steps=1)                     # warm-up time step
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     ms.launches(reset=True)
     t0 = time.perf_counter()
     lg = ms.newton_step(outer_steps=3, precond=1, cg_tol=1e-4, cg_max_iters=500)
     torch.cuda.synchronize()
     el = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        t = torch.tensor([el], dtype=torch.float64, device=torch.device("cuda", local_rank))
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t[0])
     n = max(int(lg["n_iters"]), 1)
-    out = {"workload": "C3: %dx%dx%d Kuhn grid = %d tets, ARAP, dt=%.4f, eigen-pcg-diag tol 1e-4" % (nx, ny, nz, T.shape[0], DT),
-           "ms_per_newton_iteration": el / n, "newton_iterations": n, "cg_iterations": [int(v) for v in lg["cg_iters"]],
+    out = {"workload": "C3: %dx%dx%d Kuhn grid = %d tets, ARAP, dt=%.4f, eigen-pcg-diag tol 1e-4" % (nx, ny, nz, nE, DT),
+           "n_gpus": world, "ms_per_newton_iteration": el / n, "newton_iterations": n, "cg_iterations": [int(v) for v in lg["cg_iters"]],
            "ms_per_cg_iteration_upper_bound": el / max(int(lg["cg_iters_total"]), 1),
            "energy": [float(v) for v in lg["energy"]], "decrement": [float(v) for v in lg["decrement"]],
-           "alpha": [float(v) for v in lg["alpha"]], "gpu_launches": ms.launches(), "timing": "host wall clock around one time step (the loop branches on device scalars)"}
+           "alpha": [float(v) for v in lg["alpha"]], "gpu_launches": ms.launches(),
+           "timing": "host wall clock around one time step, max over ranks (the loop branches on device scalars)"}
     ms.close()
     return out
 

@@ -99,7 +99,7 @@ struct mfb_ctx {
   // buffer over all shared vertices), dot-product weights (1 interior / owned interface vertex, 0 copy owned elsewhere)
   void* comm = nullptr;
   int rank = 0, world = 1;
-  mfb::DBuf<int> if_local, if_pos;
+  mfb::DBuf<int> if_local, if_pos, if_inv;   // if_inv[slot] = local free id or -1
   int n_if_local = 0, n_shared = 0;
   mfb::DBuf<double> if_buf, dot_w;
 

@@ -53,30 +53,32 @@ int nccl_fail(const char* what, ncclResult_t r) {
 
 inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
 
-// buf[(pos, 0..na+nb)] = (a | b) at this rank's interface vertices
-__global__ void k_if_pack(const int* __restrict__ if_local, const int* __restrict__ if_pos, int n, const double* __restrict__ a, int na,
-                          const double* __restrict__ b, int nb, double* __restrict__ buf) {
+// buf over ALL shared vertices: (a | b) where this rank has a copy (inv[pos] = local free id), zero elsewhere; the
+// ns scalars ride at the end (one collective instead of two).  One launch packs, one unpacks.
+__global__ void k_if_pack(const int* __restrict__ inv, int n_shared, const double* __restrict__ a, int na, const double* __restrict__ b, int nb,
+                          const double* __restrict__ scal, int ns, double* __restrict__ buf) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int w = na + nb;
-  if (i >= n * w) return;
+  const int w = na + nb, nv = n_shared * w;
+  if (i >= nv + ns) return;
+  if (i >= nv) { buf[i] = scal[i - nv]; return; }
   const int v = i / w, k = i - v * w;
-  const int64_t l = if_local[v];
-  buf[(int64_t)if_pos[v] * w + k] = (k < na) ? a[l * na + k] : b[l * nb + (k - na)];
+  const int64_t l = inv[v];
+  buf[i] = l < 0 ? 0.0 : ((k < na) ? a[l * na + k] : b[l * nb + (k - na)]);
 }
-__global__ void k_if_unpack(const int* __restrict__ if_local, const int* __restrict__ if_pos, int n, double* __restrict__ a, int na,
-                            double* __restrict__ b, int nb, const double* __restrict__ buf) {
+__global__ void k_if_unpack(const int* __restrict__ inv, int n_shared, double* __restrict__ a, int na, double* __restrict__ b, int nb,
+                            double* __restrict__ scal, int ns, const double* __restrict__ buf) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int w = na + nb;
-  if (i >= n * w) return;
+  const int w = na + nb, nv = n_shared * w;
+  if (i >= nv + ns) return;
+  if (i >= nv) { scal[i - nv] = buf[i]; return; }
   const int v = i / w, k = i - v * w;
-  const int64_t l = if_local[v];
-  const double val = buf[(int64_t)if_pos[v] * w + k];
-  if (k < na) a[l * na + k] = val; else b[l * nb + (k - na)] = val;
+  const int64_t l = inv[v];
+  if (l < 0) return;
+  if (k < na) a[l * na + k] = buf[i]; else b[l * nb + (k - na)] = buf[i];
 }
-// extra scalars ride at the end of the interface buffer (one collective instead of two)
-__global__ void k_copy_n(const double* __restrict__ src, double* __restrict__ dst, int n) {
+__global__ void k_if_invert(const int* __restrict__ if_local, const int* __restrict__ if_pos, int n, int* __restrict__ inv) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) dst[i] = src[i];
+  if (i < n) inv[if_pos[i]] = if_local[i];
 }
 
 }  // namespace
@@ -92,16 +94,12 @@ int interface_sum(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal
   const size_t need = (size_t)c->n_shared * w + ns;
   if (c->if_buf.n < need + 1) { int rc = c->if_buf.alloc(need + 1); if (rc) return rc; }
   cudaStream_t st = c->stream;
-  MFB_CUDA(cudaMemsetAsync(c->if_buf.p, 0, need * sizeof(double), st));
-  if (c->n_if_local > 0 && w > 0)
-    k_if_pack<<<nblk((int64_t)c->n_if_local * w), 256, 0, st>>>(c->if_local.p, c->if_pos.p, c->n_if_local, a, na, b, b ? nb : 0, c->if_buf.p);
-  if (ns > 0) k_copy_n<<<1, 32, 0, st>>>(scal, c->if_buf.p + (size_t)c->n_shared * w, ns);
+  if (need == 0) return MFB_OK;
+  k_if_pack<<<nblk((int64_t)need), 256, 0, st>>>(c->if_inv.p, c->n_shared, a, na, b, b ? nb : 0, scal, ns, c->if_buf.p);
   ncclResult_t r = api->AllReduce(c->if_buf.p, c->if_buf.p, need, ncclDouble, ncclSum, (ncclComm_t)c->comm, st);
   if (r != ncclSuccess) return nccl_fail("ncclAllReduce", r);
-  if (c->n_if_local > 0 && w > 0)
-    k_if_unpack<<<nblk((int64_t)c->n_if_local * w), 256, 0, st>>>(c->if_local.p, c->if_pos.p, c->n_if_local, a, na, b, b ? nb : 0, c->if_buf.p);
-  if (ns > 0) k_copy_n<<<1, 32, 0, st>>>(c->if_buf.p + (size_t)c->n_shared * w, scal, ns);
-  c->launches += 4;
+  k_if_unpack<<<nblk((int64_t)need), 256, 0, st>>>(c->if_inv.p, c->n_shared, a, na, b, b ? nb : 0, scal, ns, c->if_buf.p);
+  c->launches += 2;
   MFB_CUDA(cudaGetLastError());
   return MFB_OK;
 }
@@ -158,6 +156,9 @@ extern "C" int mfb_comm_set_interface(mfb_ctx* c, const int32_t* if_local, const
     MFB_CUDA(cudaMemcpyAsync(c->if_pos.p, if_pos, (size_t)n_if_local * 4, cudaMemcpyHostToDevice, c->stream));
   }
   MFB_CUDA(cudaMemcpyAsync(c->dot_w.p, dot_weight, (size_t)c->nF * 8, cudaMemcpyHostToDevice, c->stream));
+  if ((rc = c->if_inv.alloc((size_t)n_shared + 1))) return rc;
+  MFB_CUDA(cudaMemsetAsync(c->if_inv.p, 0xff, ((size_t)n_shared + 1) * 4, c->stream));       // -1
+  if (n_if_local > 0) k_if_invert<<<nblk(n_if_local), 256, 0, c->stream>>>(c->if_local.p, c->if_pos.p, n_if_local, c->if_inv.p);
   MFB_CUDA(cudaStreamSynchronize(c->stream));
   c->n_if_local = n_if_local; c->n_shared = n_shared;
   return MFB_OK;

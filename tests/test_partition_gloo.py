@@ -121,3 +121,106 @@ def test_partition_is_a_partition():
             assert np.array_equal(free, np.arange(free.size))
             assert np.all(np.diff(loc.free_l2g) > 0)
             assert np.array_equal(shared[loc.if_pos], loc.free_l2g[loc.if_local])
+
+
+def _cg_worker(rank, world, port, q):
+    """the distributed CG of mixed-fem_b200/csrc/mfb_pcg.cu restated in numpy on top of the SAME host-side interface
+    description the library consumes (LocalProblem.if_local / if_pos / dot_weight): sub-assembled operator, interface
+    sum of the product and of the diagonal blocks, owner-weighted dot products summed over ranks."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import mixed_fem_b200  # noqa: F401
+    from mixed_fem_b200 import meshgen, partition
+    from oracle import orc
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    orc.lib().orc_set_num_threads(1)
+    V, T = meshgen.kuhn_grid(6, 3, 3)
+    fm = meshgen.pinned_free_map(V, ratio=0.01)
+    mu, la = meshgen.enu_to_lame(1e6, 0.45)
+    st = meshgen.synthetic_state(V, T, 1.0 / 6, mu)
+    loc, parts, shared = partition.make_local(V, T, fm, world, rank)
+    o = orc.OracleMixedStretch(loc.V, loc.T, loc.free_map, [("Stable-Neohookean", mu, la)])
+    o.reset()
+    o.set("R", st["R"].reshape(-1, 9)[loc.elems].reshape(-1))
+    o.set("s", loc.restrict_element_vector(st["s"], 6)); o.set("la", loc.restrict_element_vector(st["la"], 6))
+    o.update(loc.restrict_vertex_vector(st["x"], 3), 0.0333)
+    outer, inner, vals = o.csr()
+    n = outer.size - 1
+    A = sp.csr_matrix((vals, inner, outer), shape=(n, n))
+
+    def allreduce(buf):
+        dist.all_reduce(torch.from_numpy(buf))
+
+    def gsum(v):
+        t = torch.tensor([v], dtype=torch.float64)
+        dist.all_reduce(t)
+        return float(t[0])
+
+    w3 = np.repeat(loc.dot_weight, 3)
+    wdot = lambda a, b: gsum(float((w3 * a) @ b))
+    nFg = int(fm.max()) + 1
+    b = np.random.default_rng(2).standard_normal(3 * nFg).reshape(-1, 3)[loc.free_l2g].reshape(-1)
+    # Jacobi preconditioner from the summed diagonal
+    d = partition.interface_sum_numpy(loc, A.diagonal().copy(), 3, allreduce)
+    x = np.zeros(n)
+    r = b.copy()
+    thr = (1e-10) ** 2 * wdot(b, b)
+    p = r / d
+    absnew = wdot(r, p)
+    it = 0
+    while it < 2000:
+        t = partition.interface_sum_numpy(loc, A @ p, 3, allreduce)
+        # p.(A p) from the UNSUMMED local products would be sum_r p_r.(A_r p_r); with the summed t it needs the weights
+        alpha = absnew / wdot(p, t)
+        x += alpha * p
+        r -= alpha * t
+        z = r / d
+        rr, rz = wdot(r, r), wdot(r, z)
+        if rr < thr:
+            break
+        p = z + (rz / absnew) * p
+        absnew = rz
+        it += 1
+    q.put((rank, loc.free_l2g, x, it, float(loc.dot_weight.sum())))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_distributed_cg_with_owner_weights_matches_global_solve(world):
+    import scipy.sparse.linalg as spla
+    import torch.multiprocessing as mp
+    from mixed_fem_b200 import meshgen
+    from oracle import orc
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cg_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    V, T = meshgen.kuhn_grid(6, 3, 3)
+    fm = meshgen.pinned_free_map(V, ratio=0.01)
+    mu, la = meshgen.enu_to_lame(1e6, 0.45)
+    st = meshgen.synthetic_state(V, T, 1.0 / 6, mu)
+    o = orc.OracleMixedStretch(V, T, fm, [("Stable-Neohookean", mu, la)])
+    o.reset()
+    o.set("R", st["R"]); o.set("s", st["s"]); o.set("la", st["la"])
+    o.update(st["x"], 0.0333)
+    outer, inner, vals = o.csr()
+    A = sp.csr_matrix((vals, inner, outer), shape=(outer.size - 1, outer.size - 1))
+    b = np.random.default_rng(2).standard_normal(A.shape[0])
+    xg = spla.spsolve(A.tocsc(), b).reshape(-1, 3)
+    # every global free vertex is counted exactly once by the dot-product weights
+    assert abs(sum(r[4] for r in res) - xg.shape[0]) < 1e-9
+    its = {r[3] for r in res}
+    assert len(its) == 1 and 0 < its.pop() < 2000          # same control flow on every rank
+    for rank, l2g, x, it, _ in res:
+        assert np.linalg.norm(x.reshape(-1, 3) - xg[l2g]) <= 1e-7 * np.linalg.norm(xg)
