@@ -120,6 +120,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   }
   const DevMesh m = c->mesh();
   const DevState s = c->state();
+  bool vec_recorded = false;
   int slot = -1;
   if (c->profile && c->ev_count < 4096) {
     slot = c->ev_count++;
@@ -149,8 +150,11 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     if (bulk) {
       if (c->fuse_rhs) { k_update_tet_v4<true, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
       else { k_update_tet_v4<false, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
-      if (c->nb > 0) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, c->nF, c->Ablk.p, c->Avals.p);
+      // vertex vectors first: grad_x_ / rhs_ are final after this launch (a host reader copies them out while the
+      // CSR values are still being written, see mfb_rhs)
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
+      if (c->ev_vec) { MFB_CUDA(cudaEventRecord(c->ev_vec, st)); vec_recorded = true; }
+      if (c->nb > 0) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, c->nF, c->Ablk.p, c->Avals.p);
       LAUNCHED(c, 3);
     } else {
       if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
@@ -199,6 +203,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
   c->rhs_valid = c->fuse_rhs != 0;
+  c->ev_vec_valid = vec_recorded && c->rhs_valid;
   c->updated = true;
   return MFB_OK;
 }
@@ -206,11 +211,19 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
 extern "C" int mfb_update(mfb_ctx* c, const double* x, double dt) {
   CHECK_CTX(c);
   if (!x) return MFB_ERR_INVALID;
+  if (!c->copy_stream) {
+    MFB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    MFB_CUDA(cudaEventCreateWithFlags(&c->ev_in, cudaEventDisableTiming));
+    MFB_CUDA(cudaEventCreateWithFlags(&c->ev_vec, cudaEventDisableTiming));
+  }
   int rc = upload_x(c, x);
   if (rc) return rc;
+  MFB_CUDA(cudaEventRecord(c->ev_in, c->stream));
   rc = mfb_update_dev(c, c->xdev.p, dt);
   if (rc) return rc;
-  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  // The caller's buffer is free once the upload has finished.  The kernels are stream-ordered: every entry point that
+  // hands results to the host synchronises on what it reads, so update() does not wait for the device here.
+  MFB_CUDA(cudaEventSynchronize(c->ev_in));
   return MFB_OK;
 }
 
@@ -223,6 +236,7 @@ static int ensure_rhs(mfb_ctx* c) {
   LAUNCHED(c, 1);
   MFB_CUDA(cudaGetLastError());
   c->rhs_valid = true;
+  c->ev_vec_valid = false;
   return MFB_OK;
 }
 
@@ -238,6 +252,12 @@ extern "C" int mfb_rhs(mfb_ctx* c, double* out) {
   if (!out) return MFB_ERR_INVALID;
   int rc = ensure_rhs(c);
   if (rc) return rc;
+  if (c->ev_vec_valid && c->copy_stream) {       // rhs_ came out of the fused update: do not wait for the CSR values
+    MFB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_vec, 0));
+    MFB_CUDA(cudaMemcpyAsync(out, c->rhs.p, (size_t)c->dim * c->nF * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+    MFB_CUDA(cudaStreamSynchronize(c->copy_stream));
+    return MFB_OK;
+  }
   MFB_CUDA(cudaMemcpyAsync(out, c->rhs.p, (size_t)c->dim * c->nF * 8, cudaMemcpyDeviceToHost, c->stream));
   MFB_CUDA(cudaStreamSynchronize(c->stream));
   return MFB_OK;

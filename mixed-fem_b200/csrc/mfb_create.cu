@@ -379,6 +379,7 @@ extern "C" void mfb_destroy(mfb_ctx* c) {
   cudaSetDevice(c->device);
   mfb_newton_free(c);
   mfb::comm_free(c);
+  if (c->copy_stream) { cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->ev_in); cudaEventDestroy(c->ev_vec); }
   if (c->h_scal) cudaFreeHost(c->h_scal);
   delete c;
 }

@@ -95,6 +95,11 @@ struct mfb_ctx {
   std::vector<cudaEvent_t> ev0, ev1;
   int ev_count = 0;
   void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)
+  // host-buffer entry points (mfb_update / mfb_rhs): the device->host copy of rhs_ runs on its own stream as soon as
+  // the vertex vectors are final, beside the kernel that writes the CSR values
+  cudaStream_t copy_stream = 0;
+  cudaEvent_t ev_in = 0, ev_vec = 0;
+  bool ev_vec_valid = false;
   // multi-GPU (mfb_dist.cu): NCCL communicator, this rank's interface vertices (local free id, slot in the packed
   // buffer over all shared vertices), dot-product weights (1 interior / owned interface vertex, 0 copy owned elsewhere)
   void* comm = nullptr;

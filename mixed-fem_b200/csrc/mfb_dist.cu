@@ -168,6 +168,7 @@ extern "C" int mfb_interface_sum_dev(mfb_ctx* c, double* a_dev, int ncomp_a, dou
   CHECK_CTX(c);
   if (!a_dev || ncomp_a <= 0 || (b_dev && ncomp_b <= 0)) return MFB_ERR_INVALID;
   if (c->world > 1 && !c->dot_w.p) { g_last_error = "mfb_interface_sum_dev: mfb_comm_set_interface has not been called"; return MFB_ERR_INVALID; }
+  c->ev_vec_valid = false;     // rhs_ / grad_x_ may be among the summed vectors: host readers must wait for this stream
   return interface_sum(c, a_dev, ncomp_a, b_dev, ncomp_b, nullptr, 0);
 }
 
