@@ -148,8 +148,35 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     }
     const int tail_grid = c->grid() < 148 * 3 ? c->grid() : 148 * 3;
     if (bulk) {
-      if (c->fuse_rhs) { k_update_tet_v4<true, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
-      else { k_update_tet_v4<false, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      if (c->x_host_chunked && c->nE >= (1 << 18)) {
+        // host positions: upload x in pieces on the copy stream and start each element chunk when its vertices are there
+        const double* xh = c->x_host_chunked;
+        MFB_CUDA(cudaEventRecord(c->ev_in, st));                       // everything queued so far (earlier readers of xdev)
+        MFB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_in, 0));
+        int vdone = 0;
+        for (int k = 0; k < mfb_ctx::kChunks; ++k) {
+          const int vhi = k + 1 == mfb_ctx::kChunks ? c->nV : c->chunk_vhi[k];
+          if (vhi > vdone) {
+            MFB_CUDA(cudaMemcpyAsync(c->xdev.p + (size_t)3 * vdone, xh + (size_t)3 * vdone, (size_t)(vhi - vdone) * 24, cudaMemcpyHostToDevice, c->copy_stream));
+            vdone = vhi;
+            if (k + 1 == mfb_ctx::kChunks) MFB_CUDA(cudaEventRecord(c->ev_in, c->copy_stream));     // the caller's buffer is free after this
+            MFB_CUDA(cudaEventRecord(c->ev_chunk[k], c->copy_stream));
+            MFB_CUDA(cudaStreamWaitEvent(st, c->ev_chunk[k], 0));
+          } else if (k + 1 == mfb_ctx::kChunks) {
+            MFB_CUDA(cudaEventRecord(c->ev_in, c->copy_stream));
+          }
+          const int e0 = c->chunk_e0[k], ne = c->chunk_e0[k + 1] - e0;
+          if (ne <= 0) continue;
+          const unsigned g = (unsigned)((ne + kV4Threads - 1) / kV4Threads);
+          if (c->fuse_rhs) k_update_tet_v4<true, 1><<<g, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, e0);
+          else k_update_tet_v4<false, 1><<<g, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, e0);
+        }
+        LAUNCHED(c, mfb_ctx::kChunks - 1);
+        c->x_host_chunked = nullptr;                                   // consumed
+      } else if (c->fuse_rhs) k_update_tet_v4<true, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
+      else k_update_tet_v4<false, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
+      if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
+      else k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
       // vertex vectors first: grad_x_ / rhs_ are final after this launch (a host reader copies them out while the
       // CSR values are still being written, see mfb_rhs)
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
@@ -157,8 +184,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       if (c->nb > 0) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, c->nF, c->Ablk.p, c->Avals.p);
       LAUNCHED(c, 3);
     } else {
-      if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
-      else { k_update_tet_v4<false, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      else { k_update_tet_v4<false, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
       LAUNCHED(c, 1);
     }
   } else if (c->kind == MFB_SHELL) {
@@ -216,10 +243,17 @@ extern "C" int mfb_update(mfb_ctx* c, const double* x, double dt) {
     MFB_CUDA(cudaEventCreateWithFlags(&c->ev_in, cudaEventDisableTiming));
     MFB_CUDA(cudaEventCreateWithFlags(&c->ev_vec, cudaEventDisableTiming));
   }
-  int rc = upload_x(c, x);
-  if (rc) return rc;
-  MFB_CUDA(cudaEventRecord(c->ev_in, c->stream));
+  int rc;
+  const bool chunked = c->kind == MFB_TET && c->smem_b == 3 && c->asm_mode == 1 && c->nE >= (1 << 18);
+  if (chunked) {                     // mfb_update_dev uploads x piecewise, interleaved with the element chunks
+    if (!c->ev_chunk[0]) for (int k = 0; k < mfb_ctx::kChunks; ++k) MFB_CUDA(cudaEventCreateWithFlags(&c->ev_chunk[k], cudaEventDisableTiming));
+    c->x_host_chunked = x;
+  } else {
+    if ((rc = upload_x(c, x))) return rc;
+    MFB_CUDA(cudaEventRecord(c->ev_in, c->stream));
+  }
   rc = mfb_update_dev(c, c->xdev.p, dt);
+  c->x_host_chunked = nullptr;
   if (rc) return rc;
   // The caller's buffer is free once the upload has finished.  The kernels are stream-ordered: every entry point that
   // hands results to the host synchronises on what it reads, so update() does not wait for the device here.

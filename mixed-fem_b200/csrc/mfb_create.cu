@@ -8,6 +8,7 @@
 // 64-bit keys row*nF+col (cub via thrust), which yields the identical pattern because the pattern only depends on the
 // SET of pairs and on ascending (row, col) order.
 #include "mfb_ctx.cuh"
+#include <algorithm>
 #include <thrust/device_ptr.h>
 #include <thrust/sort.h>
 #include <thrust/scan.h>
@@ -333,6 +334,18 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   cudaStream_t st = c->stream;
 #define TRY(x) do { rc = (x); if (rc) { delete c; return rc; } } while (0)
   { std::vector<double> hv(d->Vref, d->Vref + (size_t)dim * d->nV); TRY(upload(c->vref, hv, st)); MFB_CUDA(cudaStreamSynchronize(st)); }
+  {   // element chunks (multiples of the 128-thread CTA) and the vertices each one needs
+    const int ctas = (nE + 127) / 128;
+    int vmax = -1;
+    for (int k = 0; k < mfb_ctx::kChunks; ++k) {
+      c->chunk_e0[k] = (int)((int64_t)ctas * k / mfb_ctx::kChunks) * 128;
+      const int e1 = k + 1 == mfb_ctx::kChunks ? nE : (int)((int64_t)ctas * (k + 1) / mfb_ctx::kChunks) * 128;
+      for (int e = c->chunk_e0[k]; e < e1 && e < nE; ++e)
+        for (int j = 0; j < npe; ++j) vmax = std::max(vmax, (int)d->T[(size_t)e * npe + j]);
+      c->chunk_vhi[k] = vmax + 1;
+    }
+    c->chunk_e0[mfb_ctx::kChunks] = nE;
+  }
   TRY(upload(c->T, hT, st)); TRY(upload(c->fidx, hf, st)); TRY(upload(c->dphi, hdphi, st)); TRY(upload(c->vol, hvol, st));
   if (d->elem_kind == MFB_SHELL) { TRY(upload(c->nrest, hnrm, st)); TRY(c->xupd.alloc((size_t)3 * d->nV)); MFB_CUDA(cudaMemcpyAsync(c->xupd.p, c->vref.p, (size_t)3 * d->nV * 8, cudaMemcpyDeviceToDevice, st)); }
   if (d->mat_id) {
@@ -379,7 +392,10 @@ extern "C" void mfb_destroy(mfb_ctx* c) {
   cudaSetDevice(c->device);
   mfb_newton_free(c);
   mfb::comm_free(c);
-  if (c->copy_stream) { cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->ev_in); cudaEventDestroy(c->ev_vec); }
+  if (c->copy_stream) {
+    cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->ev_in); cudaEventDestroy(c->ev_vec);
+    for (int k = 0; k < mfb_ctx::kChunks; ++k) if (c->ev_chunk[k]) cudaEventDestroy(c->ev_chunk[k]);
+  }
   if (c->h_scal) cudaFreeHost(c->h_scal);
   delete c;
 }

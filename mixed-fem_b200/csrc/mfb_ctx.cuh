@@ -100,6 +100,13 @@ struct mfb_ctx {
   cudaStream_t copy_stream = 0;
   cudaEvent_t ev_in = 0, ev_vec = 0;
   bool ev_vec_valid = false;
+  // chunked upload of x in mfb_update: element chunk k needs the vertices below chunk_vhi[k] (prefix maximum over the
+  // chunk's elements, from mfb_create), so its kernel starts as soon as that part of x has arrived
+  static constexpr int kChunks = 8;
+  int chunk_e0[kChunks + 1] = {0};
+  int chunk_vhi[kChunks] = {0};
+  cudaEvent_t ev_chunk[kChunks] = {0};
+  const double* x_host_chunked = nullptr;   // set by mfb_update around its call of mfb_update_dev
   // multi-GPU (mfb_dist.cu): NCCL communicator, this rank's interface vertices (local free id, slot in the packed
   // buffer over all shared vertices), dot-product weights (1 interior / owned interface vertex, 0 copy owned elsewhere)
   void* comm = nullptr;

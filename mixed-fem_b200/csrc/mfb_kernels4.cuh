@@ -418,9 +418,10 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 }
 
 template <bool FUSE_RHS, int ASM>
-__global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
+__global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
+                                                                 int e_begin) {
   extern __shared__ __align__(128) double smem4[];
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int e = e_begin + blockIdx.x * blockDim.x + threadIdx.x;      // e_begin: a multiple of the CTA size (chunked launches)
   const int w = threadIdx.x >> 5;
   double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;
   int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;

@@ -275,3 +275,36 @@ def test_update_parity_shell(built, model):
     for which, xin, out0, tr in (("jacobian_x", xe, xv, True), ("jacobian_x", xv, xe, False)):
         assert vec_rel(gpu.product(which, xin, out0, tr), cpu.product(which, xin, out0, tr)) <= TOL, which
     gpu.close()
+
+
+def test_host_update_with_chunked_upload_equals_device_update(built):
+    """mfb_update(x_host) on >= 2^18 tets uploads x in pieces on a copy stream and launches the element chunks as their
+    vertices arrive, and mfb_rhs(out_host) copies rhs_ out beside the CSR finalisation: same results as the plain
+    device-pointer path (mfb_update_dev on the whole mesh), up to the summation order of the reductions."""
+    import torch
+    import mixed_fem_b200 as mf
+    from mixed_fem_b200 import meshgen
+    V, T = meshgen.kuhn_grid(36, 36, 36, h=1.0 / 36)
+    assert T.shape[0] >= (1 << 18)
+    fm = meshgen.pinned_free_map(V)
+    xa = meshgen.deformed_positions(V, 1.0 / 36, scale=1.0)
+    xb = meshgen.deformed_positions(V, 1.0 / 36, scale=0.5)
+    res = []
+    for host in (True, False):
+        ms = mf.MixedStretch(V, T, fm, [("Stable-Neohookean", MU, LA)])
+        ms.reset(xb)
+        for it in range(3):                                   # repeated host updates reuse the staging buffers
+            x = xa if it % 2 == 0 else xb
+            if host:
+                ms.update(x, DT)
+                r = ms.rhs()
+            else:
+                xd = torch.as_tensor(x, device="cuda")
+                ms.update_dev(xd.data_ptr(), DT)
+                torch.cuda.synchronize()
+                r = ms.rhs()
+        res.append((r.copy(), ms.lhs()[2].copy(), ms.get("grad_x").copy(), ms.get("R").copy(), ms.get("Hinv").copy()))
+        assert ms.status()["nonfinite"] == 0
+        ms.close()
+    for a, b in zip(res[0], res[1]):
+        assert vec_rel(a, b) <= 1e-12
