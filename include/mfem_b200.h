@@ -124,6 +124,12 @@ int mfb_lhs_values_dev(mfb_ctx* ctx, const double** values_dev);
 /* matrix-free operators, out += ... / out -= ... exactly as mixed_stretch.cpp:406-468.  which: 0 product_hessian,
  * 1 product_hessian_inv, 2 product_jacobian_mixed, 3 product_jacobian_x (transposed selects the branch). host buffers. */
 int mfb_product(mfb_ctx* ctx, int which, const double* x, double* out, int transposed);
+/* jacobian_x() = -PJW_ * blockdiag(dSdF_) (mixed_stretch.cpp:385-390) as COO triplets for the indefinite / dual-condensed
+ * systems (linear_system.h:64-239): mfb_jacobian_x_nnz() = nE*N*(verts per element)*d entries; row = d*free_id + r or -1
+ * for a pinned vertex (value 0: drop it), col = N*e + n.  The block-diagonal hessian() / hessian_inv() /
+ * jacobian_mixed() are mfb_get(MFB_F_HLOC), vol * MFB_F_HINV and vol * Sym per element. */
+int64_t mfb_jacobian_x_nnz(mfb_ctx* ctx);
+int mfb_jacobian_x_coo(mfb_ctx* ctx, int32_t* rows, int32_t* cols, double* vals);
 
 /* ---- state access ---- */
 int64_t mfb_field_size(const mfb_ctx* ctx, int field);

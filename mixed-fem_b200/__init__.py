@@ -29,6 +29,7 @@ EXPORTS = [
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
     "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
     "mfb_newton_init", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
+    "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo",
     "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_interface_sum_dev", "mfb_allreduce_dev",
 ]
 
@@ -107,6 +108,9 @@ def lib():
     L.mfb_scatter_map.argtypes = [vp, C.POINTER(ip), C.POINTER(ip)]
     L.mfb_reset.argtypes = [vp, dp]
     L.mfb_update.argtypes = [vp, dp, C.c_double]
+    L.mfb_jacobian_x_nnz.argtypes = [vp]
+    L.mfb_jacobian_x_nnz.restype = C.c_int64
+    L.mfb_jacobian_x_coo.argtypes = [vp, ip, ip, dp]
     L.mfb_comm_unique_id.argtypes = [C.c_char_p]
     L.mfb_comm_init.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     L.mfb_comm_set_interface.argtypes = [vp, ip, ip, C.c_int32, C.c_int32, dp]
@@ -409,6 +413,15 @@ class MixedStretch:
         n = C.c_int64()
         self._check(self.L.mfb_num_kernel_launches(self.h, C.byref(n), int(reset)))
         return n.value
+
+    def jacobian_x(self):
+        """explicit -PJW_ * blockdiag(dSdF_) (mixed_stretch.cpp:385-390): (rows, cols, vals) triplets with the pinned rows
+        dropped; shape (d*nF, N*nE)."""
+        n = int(self.L.mfb_jacobian_x_nnz(self.h))
+        r = np.empty(n, dtype=np.int32); c = np.empty(n, dtype=np.int32); v = np.empty(n)
+        self._check(self.L.mfb_jacobian_x_coo(self.h, _ip(r), _ip(c), _dp(v)))
+        keep = r >= 0
+        return r[keep], c[keep], v[keep]
 
     # ---- multi-GPU (one process per GPU; `local` is this rank's partition.LocalProblem) ----
     def comm_init(self, local):

@@ -448,6 +448,31 @@ extern "C" int mfb_product(mfb_ctx* c, int which, const double* x, double* out, 
   return MFB_OK;
 }
 
+extern "C" int64_t mfb_jacobian_x_nnz(mfb_ctx* c) {
+  if (!c) return 0;
+  return (int64_t)c->nE * c->N * c->npe * c->dim;
+}
+
+extern "C" int mfb_jacobian_x_coo(mfb_ctx* c, int32_t* rows, int32_t* cols, double* vals) {
+  CHECK_CTX(c);
+  if (!rows || !cols || !vals) return MFB_ERR_INVALID;
+  const int64_t n = mfb_jacobian_x_nnz(c);
+  mfb::DBuf<int> dr, dc;
+  mfb::DBuf<double> dv;
+  int rc;
+  if ((rc = dr.alloc((size_t)n + 1)) || (rc = dc.alloc((size_t)n + 1)) || (rc = dv.alloc((size_t)n + 1))) return rc;
+  if (c->kind == MFB_SHELL) k_jacobian_x_coo<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dr.p, dc.p, dv.p);
+  else if (c->dim == 3) k_jacobian_x_coo<3><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dr.p, dc.p, dv.p);
+  else k_jacobian_x_coo<2><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), dr.p, dc.p, dv.p);
+  LAUNCHED(c, 1);
+  MFB_CUDA(cudaMemcpyAsync(rows, dr.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaMemcpyAsync(cols, dc.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaMemcpyAsync(vals, dv.p, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
+
 extern "C" int mfb_last_status(mfb_ctx* c, mfb_status* st) {
   CHECK_CTX(c);
   if (!st) return MFB_ERR_INVALID;

@@ -476,6 +476,62 @@ __global__ void __launch_bounds__(128) k_product(DevMesh m, DevState st, int whi
   }
 }
 
+// jacobian_x() = -PJW_ * blockdiag(dSdF_)  (mixed_stretch.cpp:385-390) as COO triplets, one (element, stretch dof n,
+// local vertex j, component r) entry each: row = d*free(v_j) + r (-1 when v_j is pinned), col = N*e + n,
+// value = -vol * sum_c Jloc(j; r, c-th column of F) dSdF(., n).  Entry index = ((e*N + n)*NPE + j)*SD + r.
+template <int DIM>
+__global__ void __launch_bounds__(128) k_jacobian_x_coo(DevMesh m, DevState st, int* __restrict__ rows, int* __restrict__ cols,
+                                                        double* __restrict__ vals) {
+  using D = Dims<DIM>;
+  constexpr int SD = D::SD, NPE = D::NPE;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  const double vol = m.vol[e];
+  int f[NPE];
+#pragma unroll
+  for (int j = 0; j < NPE; ++j) f[j] = m.fidx[j * ld + e];
+  [[maybe_unused]] ShellGeo geo;
+  [[maybe_unused]] double dphi[D::M];
+  if constexpr (DIM == K_SHELL) shell_geo(m, e, m.xlast, geo);
+  else {
+#pragma unroll
+    for (int q = 0; q < D::M; ++q) dphi[q] = m.dphi[q * ld + e];
+  }
+#pragma unroll
+  for (int n = 0; n < D::N; ++n) {
+    double t[D::M], a[NPE][SD];
+#pragma unroll
+    for (int q = 0; q < D::M; ++q) t[q] = st.dSdF[(n * D::M + q) * ld + e];
+    if constexpr (DIM == K_SHELL) {
+      shell_JT(geo, t, a[1], a[2]);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) a[0][r] = -(a[1][r] + a[2][r]);
+    } else {
+#pragma unroll
+      for (int r = 0; r < SD; ++r) a[0][r] = 0.0;
+#pragma unroll
+      for (int k = 0; k < SD; ++k)
+#pragma unroll
+        for (int r = 0; r < SD; ++r) {
+          double v = 0.0;
+#pragma unroll
+          for (int c = 0; c < SD; ++c) v += dphi[SD * k + c] * t[SD * c + r];
+          a[k + 1][r] = v; a[0][r] -= v;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NPE; ++j)
+#pragma unroll
+      for (int r = 0; r < SD; ++r) {
+        const int64_t i = (((int64_t)e * D::N + n) * NPE + j) * SD + r;
+        rows[i] = f[j] >= 0 ? SD * f[j] + r : -1;
+        cols[i] = D::N * e + n;
+        vals[i] = f[j] >= 0 ? -vol * a[j][r] : 0.0;
+      }
+  }
+}
+
 // -----------------------------------------------------------------------------------------------------------------
 // k_update_tri2d : MixedStretch<2>::update() for Tri2DMesh elements, same fusion as k_update_tet (N=3, M=4, 6x6 blocks).
 // The reference's 2D "volume" is the SIGNED double area (tri2d_mesh.cpp:32-34), so vol multiplies at the end and no

@@ -475,7 +475,7 @@ static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restr
 #pragma unroll
         for (int r = 0; r < 3; ++r) {
           const double v = src[tr ? 3 * c + r : 3 * r + c];
-          A[D0 + (int64_t)r * rowlen + q] = v;
+          __stcs(&A[D0 + (int64_t)r * rowlen + q], v);      // streamed out: the block-CSR lines are the ones worth caching
           acc[r] += v;
         }
       }
@@ -487,7 +487,7 @@ static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restr
     t += __shfl_down_sync(0xffffffffu, t, 6, 16);
     t += __shfl_down_sync(0xffffffffu, acc[r], 12, 16);
     const double tot = __shfl_sync(0xffffffffu, t, c, 16);       // lanes 0..2 hold the totals of columns c = 0..2
-    if (qd >= 0) A[D0 + (int64_t)r * rowlen + qd] = -(dval[r] + tot);
+    if (qd >= 0) __stcs(&A[D0 + (int64_t)r * rowlen + qd], -(dval[r] + tot));
   }
 }
 

@@ -122,6 +122,16 @@ class MixedStretch {
     return h;
   }
   std::vector<double> dSdF_blocks() { return get(MFB_F_DSDF); }
+  // jacobian_x(): -mesh_->jacobian() * blockdiag(dSdF_) (mixed_stretch.cpp:385-390) as triplets (pinned rows: row -1)
+  struct Triplets { std::vector<int32_t> rows, cols; std::vector<double> vals; int32_t nrows, ncols; };
+  Triplets jacobian_x() {
+    Triplets t;
+    const size_t n = (size_t)mfb_jacobian_x_nnz(ctx_);
+    t.rows.resize(n); t.cols.resize(n); t.vals.resize(n);
+    check(mfb_jacobian_x_coo(ctx_, t.rows.data(), t.cols.data(), t.vals.data()));
+    t.nrows = DIM * nfree_; t.ncols = N() * nelem_;
+    return t;
+  }
 
   mfb_ctx* ctx() { return ctx_; }
   mfb_status status() { mfb_status st{}; check(mfb_last_status(ctx_, &st)); return st; }

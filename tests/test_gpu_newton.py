@@ -13,7 +13,11 @@ from tests.common import LA, MU, compare_histories, vec_rel
 pytestmark = pytest.mark.gpu
 
 
-def _run(dim, model, n, h, steps=2, outer=6, pin=0.01):
+def _run(dim, model, n, h, steps=2, outer=3, pin=0.01):
+    """`outer` = 3 Newton iterations per time step for the multi-step runs: both sides then do the same number of
+    iterations.  Letting the loop run into its termination test (decrement ~ newton_tol, energy change ~ 1e-12) makes the
+    iteration count of a step a coin flip on rounding noise, and the next step's history inherits the difference at the
+    1e-7 level (measured: 1 run in 40).  The convergence tail is covered by the single-step runs with outer = 6."""
     if dim == 3:
         V, T = meshgen.kuhn_grid(*n)
     else:
@@ -39,6 +43,7 @@ def _run(dim, model, n, h, steps=2, outer=6, pin=0.01):
 @pytest.mark.parametrize("model", ["Stable-Neohookean", "ARAP", "Corot"])
 def test_newton_history_matches_oracle_tets(built, model):
     _run(3, model, (8, 3, 3), 0.02)
+    _run(3, model, (8, 3, 3), 0.02, steps=1, outer=6)
 
 
 def test_newton_history_matches_oracle_triangles(built):
@@ -47,6 +52,7 @@ def test_newton_history_matches_oracle_triangles(built):
     # h = 0.01: with the default 0.0333 the condensed system of this thin sheet has kappa ~ 1e5 and the CG solution (tol
     # 1e-13) differs from the oracle's direct solve by more than the 1e-8 bar - a linear-solver effect
     _run(2, "Stable-Neohookean", (16, 10, 0), 0.01)
+    _run(2, "Stable-Neohookean", (16, 10, 0), 0.01, steps=1, outer=6)
 
 
 def test_newton_with_reference_default_solver_settings(built):
@@ -75,9 +81,9 @@ def test_newton_history_matches_oracle_shell(built):
     gpu = mf.MixedStretch(V, T, fm, mats, normals=N, thickness=1e-3); gpu.reset()
     ont = onewton.OracleNewton(cpu, V, T, fm, density=100.0, h=0.01)
     gpu.newton_init(density=100.0, h=0.01)
-    for _ in range(2):
-        lo = ont.step(outer_steps=6, newton_tol=1e-10)
-        lg = gpu.newton_step(outer_steps=6, newton_tol=1e-10, precond=2, cg_tol=1e-13, cg_max_iters=5000)
+    for outer in (3, 6):                 # see _run: only the last step runs into the termination test
+        lo = ont.step(outer_steps=outer, newton_tol=1e-10)
+        lg = gpu.newton_step(outer_steps=outer, newton_tol=1e-10, precond=2, cg_tol=1e-13, cg_max_iters=5000)
         compare_histories(lg, lo)
         assert vec_rel(gpu.newton_positions(), ont.x) <= 1e-9
         assert vec_rel(gpu.get("s"), cpu.get("s")) <= 1e-9
