@@ -163,8 +163,8 @@ def gpu_arm(args):
     fm = meshgen.pinned_free_map(V)
     mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
     nE_total, nV_total = T.shape[0], V.shape[0]
-    xa = meshgen.deformed_positions(V, h, scale=1.0)
-    xb = meshgen.deformed_positions(V, h, scale=0.5)
+    xa = meshgen.deformed_positions(V, h, scale=args.jitter)
+    xb = meshgen.deformed_positions(V, h, scale=0.5 * args.jitter)
     rng = np.random.default_rng(meshgen.SEED)
     lam = rng.uniform(-1, 1, size=6 * nE_total) * mu * 1e-3
     if world > 1:
@@ -399,6 +399,7 @@ def main():
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--exp", type=int, default=0, help="what-if experiment bits of the update kernel (results are WRONG; profiling aid only)")
+    ap.add_argument("--jitter", type=float, default=1.0, help="multiplies the vertex jitter of the synthetic state (SURVEY 8d: 1.0); large values make Hessians indefinite -> Jacobi tail")
     ap.add_argument("--material", default="Stable-Neohookean", help="material of the timed update (the headline metric is quoted on the default)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-newton", action="store_true", help="skip the ms-per-Newton-iteration leg (config C3)")
