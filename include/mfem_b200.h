@@ -196,7 +196,8 @@ int mfb_allreduce_dev(mfb_ctx* ctx, double* v_dev, int n, int op);   /* op 0 sum
 
 /* ---- instrumentation ---- */
 int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
-int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0) */
+int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0), "cg_zero_guess" (0:
+                                                                       mfb_newton_step starts CG from the reference's guess) */
 /* device time of the update kernel alone, CUDA events on the ctx stream, accumulated while option "profile" is 1 */
 int mfb_kernel_time_ms(mfb_ctx* ctx, double* total_ms, int* count);
 

@@ -92,6 +92,7 @@ struct mfb_ctx {
   int64_t launches = 0;
   // optional CUDA-event timing of the update kernel alone (bench.py roofline): ring of event pairs on the stream
   int profile = 0;
+  int cg_zero_guess = 0;   // mfb_newton_step: start CG from 0 instead of the reference's guess (parity runs, see mfb_newton.cu)
   std::vector<cudaEvent_t> ev0, ev1;
   int ev_count = 0;
   void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)

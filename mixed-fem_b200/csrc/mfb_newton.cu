@@ -288,6 +288,13 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
       k_guess<2><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
     }
     c->launches += 3;
+    // The reference starts CG from -P(x - x_tilde - h^2 f), a guess of the size of the FIRST Newton step.  Near
+    // convergence the solution is many orders smaller than the guess and the recursive CG residual reaches
+    // tol*|b| with an ABSOLUTE error of order eps*kappa*|guess| (observed 1e-9 on a 2D sheet, against a true
+    // step of 4e-12, in some runs and not in others: it depends on the summation order of the assembly).  That is
+    // the reference's behaviour and the default; option "cg_zero_guess" starts from 0 so that parity runs can be
+    // held against an exact solve.
+    if (c->cg_zero_guess) MFB_CUDA(cudaMemsetAsync(s->dx.p, 0, (size_t)nf * 8, st));
     // multi-GPU: both parts of b are element sums of this rank's slab: one interface sum makes b consistent
     if ((rc = interface_sum(c, s->b.p, dim, nullptr, 0, nullptr, 0))) return rc;
     int cg_it = 0; double cg_res = 0;

@@ -28,6 +28,7 @@ def _run(dim, model, n, h, steps=2, outer=3, pin=0.01):
     gpu = mf.MixedStretch(V, T, fm, mats); gpu.reset()
     ont = onewton.OracleNewton(cpu, V, T, fm, density=1000.0, h=h)
     gpu.newton_init(density=1000.0, h=h)
+    gpu.set_option("cg_zero_guess", 1)        # the oracle solves exactly; see the note on the guess in mfb_newton.cu
     for _ in range(steps):
         lo = ont.step(outer_steps=outer, newton_tol=1e-10)
         lg = gpu.newton_step(outer_steps=outer, newton_tol=1e-10, precond=2, cg_tol=1e-13, cg_max_iters=5000)
@@ -81,6 +82,7 @@ def test_newton_history_matches_oracle_shell(built):
     gpu = mf.MixedStretch(V, T, fm, mats, normals=N, thickness=1e-3); gpu.reset()
     ont = onewton.OracleNewton(cpu, V, T, fm, density=100.0, h=0.01)
     gpu.newton_init(density=100.0, h=0.01)
+    gpu.set_option("cg_zero_guess", 1)
     for outer in (3, 6):                 # see _run: only the last step runs into the termination test
         lo = ont.step(outer_steps=outer, newton_tol=1e-10)
         lg = gpu.newton_step(outer_steps=outer, newton_tol=1e-10, precond=2, cg_tol=1e-13, cg_max_iters=5000)
