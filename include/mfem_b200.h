@@ -120,6 +120,10 @@ int mfb_constraint_value_dev(mfb_ctx* ctx, const double* x_dev, const double* s_
 int mfb_evaluate_constraint(mfb_ctx* ctx, const double* x, double* c);                /* mixed_stretch.cpp:345-366 */
 int mfb_lhs_values(mfb_ctx* ctx, double* values);              /* lhs().valuePtr() mixed_stretch.h:37-39 ; host, nnz */
 int mfb_lhs_values_dev(mfb_ctx* ctx, const double** values_dev);
+/* the operator (A, or A + M for device M values on the same pattern, else NULL) as block-CSR with d x d ROW-MAJOR blocks:
+ * ptr[nF+1], col[nb], val[nb*d*d] (host) - the layout of amgcl's crs<static_matrix<double,d,d>> that the reference's
+ * AMGCL solver consumes (src/linear_solvers/amgcl_solver.h:40-75); nb = nnz / d^2 */
+int mfb_lhs_bsr(mfb_ctx* ctx, const double* M_vals_dev, int32_t* ptr, int32_t* col, double* val);
 
 /* matrix-free operators, out += ... / out -= ... exactly as mixed_stretch.cpp:406-468.  which: 0 product_hessian,
  * 1 product_hessian_inv, 2 product_jacobian_mixed, 3 product_jacobian_x (transposed selects the branch). host buffers. */

@@ -29,7 +29,7 @@ EXPORTS = [
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
     "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
     "mfb_newton_init", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
-    "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo",
+    "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo", "mfb_lhs_bsr",
     "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_interface_sum_dev", "mfb_allreduce_dev",
 ]
 
@@ -108,6 +108,7 @@ def lib():
     L.mfb_scatter_map.argtypes = [vp, C.POINTER(ip), C.POINTER(ip)]
     L.mfb_reset.argtypes = [vp, dp]
     L.mfb_update.argtypes = [vp, dp, C.c_double]
+    L.mfb_lhs_bsr.argtypes = [vp, vp, ip, ip, dp]
     L.mfb_jacobian_x_nnz.argtypes = [vp]
     L.mfb_jacobian_x_nnz.restype = C.c_int64
     L.mfb_jacobian_x_coo.argtypes = [vp, ip, ip, dp]
@@ -346,6 +347,14 @@ class MixedStretch:
         vals = np.empty(self.nnz)
         self._check(self.L.mfb_lhs_values(self.h, _dp(vals)))
         return outer, inner, vals
+
+    def lhs_bsr(self, M_ptr=None):
+        """(ptr, col, val[nb, d, d]) block-CSR of A (+ M): the amgcl static_matrix layout (amgcl_solver.h:40-75)."""
+        d = self.dim
+        nb = self.nnz // (d * d)
+        ptr = np.empty(self.nfree + 1, dtype=np.int32); col = np.empty(max(nb, 1), dtype=np.int32); val = np.empty(max(nb, 1) * d * d)
+        self._check(self.L.mfb_lhs_bsr(self.h, C.c_void_p(M_ptr) if M_ptr else None, _ip(ptr), _ip(col), _dp(val)))
+        return ptr, col[:nb], val[:nb * d * d].reshape(nb, d, d)
 
     def lhs_values_dev(self):
         p = C.c_void_p()

@@ -585,3 +585,44 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
   if (relres_out) *relres_out = sqrt(resNorm2 / rhsNorm2);
   return MFB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Hand-off to block solvers: the operator (A, or A + M when M values on the same pattern are
+// given) as block-CSR with d x d row-major blocks - the layout of amgcl::backend::crs<amgcl::static_matrix<double,d,d>>
+// that the reference's AMGCL solver builds from Eigen blocks (src/linear_solvers/amgcl_solver.h:40-75).
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+template <int DIM>
+__global__ void k_to_bsr(const int* __restrict__ blockptr, const int* __restrict__ brow, int nb, const double* __restrict__ A,
+                         const double* __restrict__ Mv, double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)nb * DIM * DIM) return;
+  const int b = (int)(i / (DIM * DIM)), rc = (int)(i % (DIM * DIM)), r = rc / DIM, cc = rc % DIM;
+  const int row = brow[b], b0 = blockptr[row], nbr = blockptr[row + 1] - b0;
+  const int64_t src = (int64_t)DIM * DIM * b0 + (int64_t)r * DIM * nbr + DIM * (b - b0) + cc;
+  out[i] = A[src] + (Mv ? Mv[src] : 0.0);
+}
+}  // namespace
+
+extern "C" int mfb_lhs_bsr(mfb_ctx* c, const double* M_vals_dev, int32_t* ptr, int32_t* col, double* val) {
+  CHECK_CTX(c);
+  if (!ptr || !col || !val) return MFB_ERR_INVALID;
+  const int dd = c->dim * c->dim;
+  mfb::DBuf<double> tmp;
+  int rc = tmp.alloc((size_t)c->nb * dd + 1);
+  if (rc) return rc;
+  cudaStream_t st = c->stream;
+  if (c->nb > 0) {
+    if (c->dim == 3) k_to_bsr<3><<<nblk((int64_t)c->nb * dd), 256, 0, st>>>(c->blockptr.p, c->brow.p, c->nb, c->Avals.p, M_vals_dev, tmp.p);
+    else k_to_bsr<2><<<nblk((int64_t)c->nb * dd), 256, 0, st>>>(c->blockptr.p, c->brow.p, c->nb, c->Avals.p, M_vals_dev, tmp.p);
+    c->launches += 1;
+  }
+  MFB_CUDA(cudaMemcpyAsync(ptr, c->blockptr.p, ((size_t)c->nF + 1) * 4, cudaMemcpyDeviceToHost, st));
+  if (c->nb > 0) {
+    MFB_CUDA(cudaMemcpyAsync(col, c->bcol.p, (size_t)c->nb * 4, cudaMemcpyDeviceToHost, st));
+    MFB_CUDA(cudaMemcpyAsync(val, tmp.p, (size_t)c->nb * dd * 8, cudaMemcpyDeviceToHost, st));
+  }
+  MFB_CUDA(cudaStreamSynchronize(st));
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}

@@ -120,3 +120,30 @@ def test_full_size_properties_C3_1M(built):
     assert st2["polar_iters"] == 0
     assert vec_rel(gpu.get("S"), S1) <= 1e-14 and vec_rel(gpu.rhs(), rhs1) <= 1e-12 and vec_rel(gpu.lhs()[2], A1) <= 1e-12
     gpu.close()
+
+
+@pytest.mark.parametrize("dim", [3, 2])
+def test_block_csr_export_equals_the_scalar_csr(built, dim):
+    """mfb_lhs_bsr: the amgcl hand-off layout (row-major d x d blocks) against the reference-layout scalar CSR."""
+    import scipy.sparse as sp
+    import mixed_fem_b200 as mf
+    from mixed_fem_b200 import meshgen
+    from tests.common import LA, MU
+    V, T = meshgen.kuhn_grid(5, 3, 2) if dim == 3 else meshgen.tri_grid(7, 5)
+    fm = meshgen.pinned_free_map(V, ratio=0.05)
+    ms = mf.MixedStretch(V, T, fm, [("Stable-Neohookean", MU, LA)])
+    ms.reset()
+    ms.update((V * 1.03).reshape(-1), 0.0333)
+    outer, inner, vals = ms.lhs()
+    n = outer.size - 1
+    A = sp.csr_matrix((vals, inner, outer), shape=(n, n))
+    ptr, col, blk = ms.lhs_bsr()
+    B = sp.bsr_matrix((blk, col, ptr), shape=(n, n))
+    assert abs(A - B).max() == 0.0
+    ms.newton_init(h=0.0333)
+    _, Mptr = ms.newton_positions_dev()
+    ptr, col, blk = ms.lhs_bsr(Mptr)
+    L = sp.bsr_matrix((blk, col, ptr), shape=(n, n)).tocsr()
+    assert abs(L - L.T).max() <= 1e-12 * abs(L).max()
+    assert (L - A).diagonal().min() > 0                 # the mass matrix sits on the diagonal blocks (and beyond)
+    ms.close()
