@@ -101,8 +101,14 @@ def cpu_arm(nx, ny, nz, seconds, threads=None, native=True):
                 _NATIVE_LIB = ""
         libpath = _NATIVE_LIB or None
     L = orc.lib(libpath)
-    if threads:
-        L.orc_set_num_threads(int(threads))
+    if not threads:
+        # all host cores this process may use: torchrun exports OMP_NUM_THREADS=1 to every rank, which would make the
+        # CPU arm 10x slower than the machine allows
+        try:
+            threads = len(os.sched_getaffinity(0))
+        except Exception:
+            threads = os.cpu_count() or 1
+    L.orc_set_num_threads(int(threads))
     cores = L.orc_num_threads()
     V, T = meshgen.kuhn_grid(nx, ny, nz, h=1.0 / 119)
     fm = meshgen.pinned_free_map(V)
