@@ -182,6 +182,36 @@ int mfb_newton_positions(mfb_ctx* ctx, double* x_full);                         
 int mfb_newton_positions_dev(mfb_ctx* ctx, double** x_full_dev, const double** mass_values_dev);
 void mfb_newton_free(mfb_ctx* ctx);
 
+/* ---- the two saddle-point formulations of the same Newton system, matrix-free on the device.
+ * They need the Displacement / BDF1 state of mfb_newton_init and an mfb_update at the current positions.
+ * Host vectors use the reference's ordering: KKT vector = [dx (d*nF) ; ds (N*nE, entry N*e+n) ; la (N*nE)].
+ *
+ * SystemMatrixIndefinite (src/linear_solvers/linear_system.h:64-118) with the BlockMatrix product
+ * (src/linear_solvers/block_matrix.h:74-125):  out = [PMP^T dx + B la ; Hloc ds + C la ; B^T dx + C ds],
+ * B = jacobian_x(), C = jacobian_mixed();  b = [-x.gradient() ; -gradient_mixed() ; -gradient_dual()]. */
+int64_t mfb_kkt_size(mfb_ctx* ctx);                                        /* d*nF + 2*N*nE */
+int mfb_kkt_product(mfb_ctx* ctx, const double* v, double* out);          /* out = A v (host, reference ordering) */
+int mfb_kkt_rhs(mfb_ctx* ctx, double* out);                               /* SystemMatrixIndefinite::pre_solve, linear_system.h:71-87 */
+/* device vectors: [x part | ds component-major N x ld | la component-major N x ld] at the offsets given here; the
+ * padding (ld > nE, and between the parts) must be zero in the input and is zero in the output */
+int mfb_kkt_layout_dev(mfb_ctx* ctx, int64_t* off_x, int64_t* off_s, int64_t* off_la, int64_t* total);
+int mfb_kkt_product_dev(mfb_ctx* ctx, const double* v_dev, double* out_dev);
+/* pre_solve + MINRES (identity preconditioner; Eigen MINRES recurrence and stop test |r| < tol |b|) from the guess in
+ * sol + post_solve (linear_system.h:89-100: x.delta() = dx, delta() = ds, lambda() = la).  sol: host, in/out. */
+int mfb_kkt_solve_minres(mfb_ctx* ctx, double* sol, double tol, int max_iters, int* iters_out, double* relres_out);
+
+/* DualCondensedSystem (src/linear_solvers/linear_system.h:120-239):  lhs = G^T G + C*C*H with G = Ml^-1/2 B,
+ * Ml = lumped PMP^T, H = hessian_inv();  rhs = B^T Ml^-1 (-x.gradient()) - C H gradient_mixed() + gradient_dual().
+ * The reference builds lhs as an explicit sparse matrix; here it is applied matrix-free (two element passes). */
+int mfb_dual_product(mfb_ctx* ctx, const double* la, double* out);        /* out = lhs * la (host, N*nE) */
+int mfb_dual_product_dev(mfb_ctx* ctx, const double* la_dev_soa, double* out_dev_soa);   /* component-major N x ld */
+int mfb_dual_rhs(mfb_ctx* ctx, double* out);                              /* linear_system.h:158-165 */
+/* pre_solve + CG (Eigen ConjugateGradient recurrence, identity preconditioner) from the guess in la + post_solve
+ * (linear_system.h:178-209: lambda() = la, x.delta() = Ml^-1(-gx - B la), delta() = H(-gradient_mixed() - C la)).
+ * la: host in/out; dx_out (d*nF), ds_out (N*nE): host or NULL. */
+int mfb_dual_solve_cg(mfb_ctx* ctx, double* la, double tol, int max_iters, int* iters_out, double* relres_out, double* dx_out,
+                      double* ds_out);
+
 /* ---- multi-GPU (the reference has no counterpart: it is a single-address-space OpenMP code).
  * One process per GPU, each with a context on ITS slab of elements (locally renumbered vertices).  The assembled
  * matrix stays sub-assembled; vectors are summed at the free vertices shared between slabs with one ncclAllReduce over

@@ -14,7 +14,8 @@ import numpy as np
 from . import meshgen  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmfem_b200.so")
+# MFB_LIB: a differently configured build of the same library (kernel experiments, tools/build_variant.sh)
+LIB_PATH = os.environ.get("MFB_LIB") or os.path.join(_HERE, "libmfem_b200.so")
 
 MODELS = {"Stable-Neohookean": 0, "Neohookean": 1, "Corot": 2, "FixedCorot": 3, "ARAP": 4, "Fung": 5}
 FIELDS = {n: i for i, n in enumerate(
@@ -30,6 +31,8 @@ EXPORTS = [
     "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
     "mfb_newton_init", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
     "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo", "mfb_lhs_bsr",
+    "mfb_kkt_size", "mfb_kkt_product", "mfb_kkt_rhs", "mfb_kkt_layout_dev", "mfb_kkt_product_dev", "mfb_kkt_solve_minres",
+    "mfb_dual_product", "mfb_dual_product_dev", "mfb_dual_rhs", "mfb_dual_solve_cg",
     "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_interface_sum_dev", "mfb_allreduce_dev",
 ]
 
@@ -148,6 +151,18 @@ def lib():
     L.mfb_newton_positions_dev.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     L.mfb_newton_free.argtypes = [vp]
     L.mfb_newton_free.restype = None
+    i64p = C.POINTER(C.c_int64)
+    L.mfb_kkt_size.argtypes = [vp]
+    L.mfb_kkt_size.restype = C.c_int64
+    L.mfb_kkt_product.argtypes = [vp, dp, dp]
+    L.mfb_kkt_rhs.argtypes = [vp, dp]
+    L.mfb_kkt_layout_dev.argtypes = [vp, i64p, i64p, i64p, i64p]
+    L.mfb_kkt_product_dev.argtypes = [vp, vp, vp]
+    L.mfb_kkt_solve_minres.argtypes = [vp, dp, C.c_double, C.c_int, ip, dp]
+    L.mfb_dual_product.argtypes = [vp, dp, dp]
+    L.mfb_dual_product_dev.argtypes = [vp, vp, vp]
+    L.mfb_dual_rhs.argtypes = [vp, dp]
+    L.mfb_dual_solve_cg.argtypes = [vp, dp, C.c_double, C.c_int, ip, dp, dp, dp]
     _lib = L
     return L
 
@@ -431,6 +446,48 @@ class MixedStretch:
         self._check(self.L.mfb_jacobian_x_coo(self.h, _ip(r), _ip(c), _dp(v)))
         keep = r >= 0
         return r[keep], c[keep], v[keep]
+
+    # ---- saddle-point systems (SystemMatrixIndefinite / DualCondensedSystem, linear_system.h:64-239); need newton_init ----
+    def kkt_size(self):
+        return int(self.L.mfb_kkt_size(self.h))
+
+    def kkt_product(self, v):
+        """BlockMatrix product (block_matrix.h:84-124) on [dx ; ds ; la] in the reference's ordering."""
+        v = _f64(v)
+        out = np.empty(self.kkt_size())
+        self._check(self.L.mfb_kkt_product(self.h, _dp(v), _dp(out)))
+        return out
+
+    def kkt_rhs(self):
+        out = np.empty(self.kkt_size())
+        self._check(self.L.mfb_kkt_rhs(self.h, _dp(out)))
+        return out
+
+    def kkt_solve_minres(self, guess=None, tol=1e-10, max_iters=10000):
+        """pre_solve + MINRES + post_solve; returns (solution [dx ; ds ; la], iterations, relative residual)."""
+        sol = np.zeros(self.kkt_size()) if guess is None else _f64(guess).copy()
+        it = C.c_int32(0); err = C.c_double(0)
+        self._check(self.L.mfb_kkt_solve_minres(self.h, _dp(sol), tol, max_iters, C.byref(it), C.byref(err)))
+        return sol, it.value, err.value
+
+    def dual_product(self, la):
+        la = _f64(la)
+        out = np.empty(self.N * self.nE)
+        self._check(self.L.mfb_dual_product(self.h, _dp(la), _dp(out)))
+        return out
+
+    def dual_rhs(self):
+        out = np.empty(self.N * self.nE)
+        self._check(self.L.mfb_dual_rhs(self.h, _dp(out)))
+        return out
+
+    def dual_solve_cg(self, guess=None, tol=1e-10, max_iters=10000):
+        """DualCondensedSystem pre_solve + CG + post_solve; returns (la, dx, ds, iterations, relative residual)."""
+        la = np.zeros(self.N * self.nE) if guess is None else _f64(guess).copy()
+        dx = np.empty(self.dim * self.nfree); ds = np.empty(self.N * self.nE)
+        it = C.c_int32(0); err = C.c_double(0)
+        self._check(self.L.mfb_dual_solve_cg(self.h, _dp(la), tol, max_iters, C.byref(it), C.byref(err), _dp(dx), _dp(ds)))
+        return la, dx, ds, it.value, err.value
 
     # ---- multi-GPU (one process per GPU; `local` is this rank's partition.LocalProblem) ----
     def comm_init(self, local):

@@ -147,7 +147,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       attr4_done = true;
     }
-    const int tail_grid = c->grid() < 148 * 3 ? c->grid() : 148 * 3;
+    const int grid4 = (c->nE + kV4Threads - 1) / kV4Threads;
+    const int tail_grid = grid4 < 148 * MFB_V4_MINB ? grid4 : 148 * MFB_V4_MINB;
     if (bulk) {
       if (c->x_host_chunked && c->nE >= (1 << 18)) {
         // host positions: upload x in pieces on the copy stream and start each element chunk when its vertices are there
@@ -174,8 +175,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
         }
         LAUNCHED(c, mfb_ctx::kChunks - 1);
         c->x_host_chunked = nullptr;                                   // consumed
-      } else if (c->fuse_rhs) k_update_tet_v4<true, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
-      else k_update_tet_v4<false, 1><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
+      } else if (c->fuse_rhs) k_update_tet_v4<true, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
+      else k_update_tet_v4<false, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
       if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
       else k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
       // vertex vectors first: grad_x_ / rhs_ are final after this launch (a host reader copies them out while the
@@ -185,8 +186,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       if (c->nb > 0) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, c->nF, c->Ablk.p, c->Avals.p);
       LAUNCHED(c, 3);
     } else {
-      if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
-      else { k_update_tet_v4<false, 0><<<c->grid(), kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      else { k_update_tet_v4<false, 0><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
       LAUNCHED(c, 1);
     }
   } else if (c->kind == MFB_SHELL) {

@@ -390,6 +390,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
 extern "C" void mfb_destroy(mfb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  mfb::saddle_free(c);
   mfb_newton_free(c);
   mfb::comm_free(c);
   if (c->copy_stream) {

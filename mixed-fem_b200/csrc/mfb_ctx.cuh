@@ -46,6 +46,15 @@ namespace mfb {
 int interface_sum(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns);
 int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop);
 void comm_free(mfb_ctx* c);
+// mfb_newton.cu: what the saddle-point systems (mfb_saddle.cu) read from the Displacement / BDF1 state
+struct NewtonView {
+  double density, h, f[3];
+  double *Mvals, *x, *xt, *diff, *dx;
+  int* vfree;
+};
+void saddle_free(mfb_ctx* c);                                     // mfb_saddle.cu
+int newton_view(mfb_ctx* c, NewtonView* v);                       // MFB_ERR_INVALID before mfb_newton_init
+int newton_disp_gradient(mfb_ctx* c, double* out_free_dev);       // Displacement::gradient() = PM (x - x_tilde - h^2 f), d*nF
 }  // namespace mfb
 
 struct mfb_ctx {
@@ -96,6 +105,7 @@ struct mfb_ctx {
   std::vector<cudaEvent_t> ev0, ev1;
   int ev_count = 0;
   void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)
+  void* saddle = nullptr;     // scratch of the saddle-point systems (mfb_saddle.cu)
   // host-buffer entry points (mfb_update / mfb_rhs): the device->host copy of rhs_ runs on its own stream as soon as
   // the vertex vectors are final, beside the kernel that writes the CSR values
   cudaStream_t copy_stream = 0;

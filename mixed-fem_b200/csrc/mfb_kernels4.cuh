@@ -29,7 +29,16 @@
 
 namespace mfb {
 
-constexpr int kV4Threads = 128;
+#ifndef MFB_V4_THREADS
+#define MFB_V4_THREADS 128
+#endif
+#ifndef MFB_V4_MINB
+#define MFB_V4_MINB 3      // CTAs per SM: 168 registers and the 54-double shared-memory column per thread both allow 3 x 128 threads
+#endif
+#ifndef MFB_V4_ROLL
+#define MFB_V4_ROLL 1      // step-3 loops over vertices / block pairs stay rolled: 6984 -> 5944 SASS instructions, 5.31 -> 5.21 ms
+#endif                      // per 10M tets (straight-line code of this size pays in instruction-cache misses)
+constexpr int kV4Threads = MFB_V4_THREADS;
 constexpr int kV4Warps = kV4Threads / 32;
 constexpr int kV4StageDoubles = 32 * 9;                 // per warp: one 3x3 block per lane
 constexpr int kV4SmemB = 54 * kV4Threads * (int)sizeof(double);
@@ -49,6 +58,18 @@ __device__ __forceinline__ void cp_async4(void* sdst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory");
 }
 
+// base[idx] += val when guard >= 0, as ONE predicated RED with a 32-bit index (9 * #blocks < 2^31 is implied by the
+// int32 CSR of the reference).  Written in PTX because the C++ form `if (t >= 0) atomicAdd(...)` compiles to a
+// branch with a BSSY/BSYNC pair and a 64-bit carry chain per reduction: 13 instructions instead of 5, 88 times per tet.
+__device__ __forceinline__ void red_add_if(double* base, int idx, double val, int guard) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .u64 a;\n\t"
+      "setp.ge.s32 p, %3, 0;\n\t"
+      "mad.wide.s32 a, %2, 8, %0;\n\t"
+      "@p red.global.add.f64 [a], %1;\n\t}"
+      ::"l"(base), "d"(val), "r"(idx), "r"(guard));
+}
+
 // Every lane holds NV values for NV contiguous doubles at base[target .. target+NV) (target < 0: nothing to add).
 // The warp re-distributes them through its shared-memory buffer so that each RED instruction covers runs of NV
 // contiguous doubles with NV adjacent lanes.  All 32 lanes must call this.
@@ -65,7 +86,7 @@ __device__ __forceinline__ void coop_red(double* __restrict__ base, const double
     const int b = q / NV, i = q - b * NV;
     const int t = sC[b];
     const double val = sW[q];
-    if (t >= 0) red_add(base + (int64_t)t + i, val);
+    red_add_if(base, t + i, val, t);
   }
 }
 
@@ -292,8 +313,13 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     for (int n = 0; n < 6; ++n) B0[r][n] = 0.0;
   {
     double v0[6] = {0, 0, 0, 0, 0, 0};
+#if MFB_V4_ROLL
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
     for (int k = 0; k < 3; ++k) {
+      const int fk = (k == 0) ? f[1] : (k == 1) ? f[2] : f[3];
       double vv[6];
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
@@ -317,15 +343,15 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
         }
       }
       if (ASM == 0) {
-        if (f[k + 1] >= 0) {
+        if (fk >= 0) {
 #pragma unroll
           for (int r = 0; r < 3; ++r) {
-            red_add(&st.grad_x[3 * (int64_t)f[k + 1] + r], vv[r]);
-            if (FUSE_RHS) red_add(&st.rhs[3 * (int64_t)f[k + 1] + r], vv[3 + r]);
+            red_add(&st.grad_x[3 * (int64_t)fk + r], vv[r]);
+            if (FUSE_RHS) red_add(&st.rhs[3 * (int64_t)fk + r], vv[3 + r]);
           }
         }
       } else {
-        coop_red<6>(as.gxrh, vv, (f[k + 1] >= 0 && !(m.exp & 2)) ? 6 * f[k + 1] : -1, sW, sC, lane);
+        coop_red<6>(as.gxrh, vv, (fk >= 0 && !(m.exp & 2)) ? 6 * fk : -1, sW, sC, lane);
       }
     }
     if (ASM == 0) {
@@ -387,9 +413,13 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       for (int r = 0; r < 3; ++r)
 #pragma unroll
         for (int n = 0; n < 6; ++n) bj[r][n] = (j == 0) ? B0[r][n] : myB[(6 * (3 * (j - 1) + r) + n) * kV4Threads];
+#if MFB_V4_ROLL
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
       for (int k = j + 1; k < 4; ++k) {
-        const int cd = code[pair6(j, k)];
+        const int cd = (j == 0) ? ((k == 1) ? code[0] : (k == 2) ? code[1] : code[2]) : (j == 1) ? ((k == 2) ? code[3] : code[4]) : code[5];
         double a[3][3];      // a[r][c] = (B_j B_k^T)(r,c)
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -418,7 +448,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 }
 
 template <bool FUSE_RHS, int ASM>
-__global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
+__global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
                                                                  int e_begin) {
   extern __shared__ __align__(128) double smem4[];
   const int e = e_begin + blockIdx.x * blockDim.x + threadIdx.x;      // e_begin: a multiple of the CTA size (chunked launches)
@@ -431,7 +461,7 @@ __global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4(DevMesh m, DevS
 
 // elements the fast PSD path refused: grid-stride over the list the main kernel built (count in counters[5])
 template <bool FUSE_RHS, int ASM>
-__global__ void __launch_bounds__(kV4Threads, 3) k_update_tet_v4_tail(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
+__global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_tail(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
   extern __shared__ __align__(128) double smem4[];
   const int w = threadIdx.x >> 5;
   double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;

@@ -198,6 +198,35 @@ struct mfb_newton_state {
 
 static mfb_newton_state* nstate(mfb_ctx* c) { return (mfb_newton_state*)c->newton; }
 
+int mfb::newton_view(mfb_ctx* c, NewtonView* v) {
+  mfb_newton_state* s = nstate(c);
+  if (!s || !s->ready) { g_last_error = "call mfb_newton_init first"; return MFB_ERR_INVALID; }
+  v->density = s->density; v->h = s->h;
+  for (int l = 0; l < 3; ++l) v->f[l] = s->f[l];
+  v->Mvals = s->Mvals.p; v->x = s->x.p; v->xt = s->xt.p; v->diff = s->diff.p; v->dx = s->dx.p; v->vfree = s->vfree.p;
+  return MFB_OK;
+}
+
+// Displacement<DIM>::gradient (displacement.cpp:59-70): PM (P^T x + b - x_tilde - h^2 f), inertia_blend_factor = 1
+int mfb::newton_disp_gradient(mfb_ctx* c, double* out) {
+  mfb_newton_state* s = nstate(c);
+  if (!s || !s->ready) { g_last_error = "call mfb_newton_init first"; return MFB_ERR_INVALID; }
+  cudaStream_t st = c->stream;
+  const int64_t nx = (int64_t)c->dim * c->nV;
+  const double h2 = s->h * s->h;
+  MFB_CUDA(cudaMemsetAsync(out, 0, (size_t)c->dim * c->nF * 8, st));
+  if (c->dim == 3) {
+    k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], c->nV, s->diff.p);
+    if (c->kind == MFB_SHELL) k_mass_rows_apply<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, 1.0, out);
+    else k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, 1.0, out);
+  } else {
+    k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, c->nV, s->diff.p);
+    k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, 1.0, out);
+  }
+  c->launches += 2;
+  return MFB_OK;
+}
+
 extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0) {
   CHECK_CTX(c);
   if (!free_map || !(h > 0) || !(density > 0)) { g_last_error = "mfb_newton_init: bad arguments"; return MFB_ERR_INVALID; }

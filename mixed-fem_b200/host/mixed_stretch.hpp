@@ -196,4 +196,43 @@ class NewtonStep {
   size_t nx_;
 };
 
+// The two saddle-point systems of src/linear_solvers/linear_system.h on the device (include/mfem_b200.h, mfb_kkt_* /
+// mfb_dual_*).  Same member names as the reference's system classes; vectors in the reference's ordering.  They read
+// the Displacement / BDF1 state, so a NewtonStep on the same variable must exist.
+template <int DIM>
+class SystemMatrixIndefinite {          // linear_system.h:64-118 + BlockMatrix product, block_matrix.h:74-125
+ public:
+  explicit SystemMatrixIndefinite(MixedStretch<DIM>& var) : var_(var) {}
+  size_t rows() const { return (size_t)mfb_kkt_size(var_.ctx()); }
+  std::vector<double> b() { std::vector<double> r(rows()); check(mfb_kkt_rhs(var_.ctx(), r.data())); return r; }
+  std::vector<double> product(const std::vector<double>& v) { std::vector<double> o(rows()); check(mfb_kkt_product(var_.ctx(), v.data(), o.data())); return o; }
+  // "minres-indefinite-*" without the factorisation-based preconditioners: pre_solve + MINRES + post_solve
+  std::vector<double> solve(double tol, int max_iters, int* iters = nullptr, double* error = nullptr) {
+    std::vector<double> x(rows(), 0.0);
+    check(mfb_kkt_solve_minres(var_.ctx(), x.data(), tol, max_iters, iters, error));
+    return x;
+  }
+ private:
+  void check(int rc) const { if (rc != MFB_OK) throw std::runtime_error(std::string("mfem_b200: ") + mfb_last_error_string()); }
+  MixedStretch<DIM>& var_;
+};
+
+template <int DIM>
+class DualCondensedSystem {             // linear_system.h:120-239, lhs applied matrix-free
+ public:
+  explicit DualCondensedSystem(MixedStretch<DIM>& var, size_t n_stretch) : var_(var), n_(n_stretch) {}
+  std::vector<double> b() { std::vector<double> r(n_); check(mfb_dual_rhs(var_.ctx(), r.data())); return r; }
+  std::vector<double> product(const std::vector<double>& la) { std::vector<double> o(n_); check(mfb_dual_product(var_.ctx(), la.data(), o.data())); return o; }
+  // "subspace-CG" without the Gauss-Seidel preconditioner: pre_solve + CG + post_solve; returns lambda()
+  std::vector<double> solve(double tol, int max_iters, int* iters = nullptr, double* error = nullptr) {
+    std::vector<double> la(n_, 0.0);
+    check(mfb_dual_solve_cg(var_.ctx(), la.data(), tol, max_iters, iters, error, nullptr, nullptr));
+    return la;
+  }
+ private:
+  void check(int rc) const { if (rc != MFB_OK) throw std::runtime_error(std::string("mfem_b200: ") + mfb_last_error_string()); }
+  MixedStretch<DIM>& var_;
+  size_t n_;
+};
+
 }  // namespace mfb

@@ -212,7 +212,9 @@ def test_host_cpp_shim_compiles_and_links(built, tmp_path):
                    'std::vector<double> x; v.update(x, 0.1); auto r = v.rhs(); v.solve(r); '
                    'mfb::MeshView sh; sh.shell = true; mfb::MixedStretch<3> w(sh); '
                    'mfb::NewtonStep<3> nt(v, m, 1000.0, 0.0333); auto lg = nt.step(mfb::PcgSolver::by_name("eigen-pcg-block_jacobi")); '
-                   'return (int)v.lhs().nnz + lg.n_iters + (int)nt.positions().size(); } return 0; }\n')
+                   'mfb::SystemMatrixIndefinite<3> kkt(v); auto kb = kkt.b(); auto kx = kkt.solve(1e-8, 100); auto kp = kkt.product(kx); '
+                   'mfb::DualCondensedSystem<3> dc(v, 6); auto db = dc.b(); auto dl = dc.solve(1e-8, 100); auto dp = dc.product(dl); '
+                   'return (int)v.lhs().nnz + lg.n_iters + (int)nt.positions().size() + (int)(kb.size() + kp.size() + db.size() + dp.size()); } return 0; }\n')
     exe = tmp_path / "shim"
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     libdir = os.path.join(ROOT, "mixed-fem_b200")
