@@ -189,6 +189,9 @@ def gpu_arm(args):
         ms.set_option("asm_mode", args.asm)
     if args.exp:
         ms.set_option("exp", args.exp)
+    for kv in args.opt:
+        name, val = kv.split("=")
+        ms.set_option(name, int(val))
     # state: R, s from the 'previous' positions (polar from identity on the device), lambda seeded
     ms.reset(xb)
     ms.set("la", lam)
@@ -404,6 +407,7 @@ def main():
     ap.add_argument("--grid", type=int, nargs=3, default=[119, 119, 119])
     ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value (mfb_set_option), e.g. no_overlap=1")
     ap.add_argument("--exp", type=int, default=0, help="what-if experiment bits of the update kernel (results are WRONG; profiling aid only)")
     ap.add_argument("--jitter", type=float, default=1.0, help="multiplies the vertex jitter of the synthetic state (SURVEY 8d: 1.0); large values make Hessians indefinite -> Jacobi tail")
     ap.add_argument("--material", default="Stable-Neohookean", help="material of the timed update (the headline metric is quoted on the default)")
