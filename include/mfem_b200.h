@@ -212,6 +212,17 @@ int mfb_dual_rhs(mfb_ctx* ctx, double* out);                              /* lin
 int mfb_dual_solve_cg(mfb_ctx* ctx, double* la, double tol, int max_iters, int* iters_out, double* relres_out, double* dx_out,
                       double* ds_out);
 
+/* ---- the non-mixed Stretch<DIM> variable (src/variables/stretch.cpp:16-91) on the same mesh, Assembler
+ * pattern and scatter map: F-form material (material_model.h:43-62), H_e = Jloc^T d2psi/dF2 Jloc vol h^2 with
+ * sim::simple_psd_fix(H, 0), g_e = Jloc^T dpsi/dF vol h^2.  Tetrahedra with one Stable-Neohookean material only
+ * (MFB_ERR_UNSUPPORTED otherwise).  x: d*nV. ---- */
+int mfb_stretch_update(mfb_ctx* ctx, const double* x, double h);             /* Stretch::update, stretch.cpp:33-60 (x host) */
+int mfb_stretch_update_dev(mfb_ctx* ctx, const double* x_dev, double h);
+int mfb_stretch_lhs_values(mfb_ctx* ctx, double* values);                    /* lhs().valuePtr(), nnz values on mfb_csr_pattern */
+int mfb_stretch_gradient(mfb_ctx* ctx, double* out);                         /* gradient(), d*nF ; rhs() = -gradient() (stretch.cpp:62-70) */
+int mfb_stretch_dev(mfb_ctx* ctx, const double** lhs_values_dev, const double** gradient_dev);
+int mfb_stretch_energy(mfb_ctx* ctx, const double* x, double* e);            /* Stretch::energy, stretch.cpp:16-28 */
+
 /* ---- multi-GPU (the reference has no counterpart: it is a single-address-space OpenMP code).
  * One process per GPU, each with a context on ITS slab of elements (locally renumbered vertices).  The assembled
  * matrix stays sub-assembled; vectors are summed at the free vertices shared between slabs with one ncclAllReduce over

@@ -33,6 +33,7 @@ EXPORTS = [
     "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo", "mfb_lhs_bsr",
     "mfb_kkt_size", "mfb_kkt_product", "mfb_kkt_rhs", "mfb_kkt_layout_dev", "mfb_kkt_product_dev", "mfb_kkt_solve_minres",
     "mfb_dual_product", "mfb_dual_product_dev", "mfb_dual_rhs", "mfb_dual_solve_cg",
+    "mfb_stretch_update", "mfb_stretch_update_dev", "mfb_stretch_lhs_values", "mfb_stretch_gradient", "mfb_stretch_dev", "mfb_stretch_energy",
     "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_interface_sum_dev", "mfb_allreduce_dev",
 ]
 
@@ -163,6 +164,12 @@ def lib():
     L.mfb_dual_product_dev.argtypes = [vp, vp, vp]
     L.mfb_dual_rhs.argtypes = [vp, dp]
     L.mfb_dual_solve_cg.argtypes = [vp, dp, C.c_double, C.c_int, ip, dp, dp, dp]
+    L.mfb_stretch_update.argtypes = [vp, dp, C.c_double]
+    L.mfb_stretch_update_dev.argtypes = [vp, vp, C.c_double]
+    L.mfb_stretch_lhs_values.argtypes = [vp, dp]
+    L.mfb_stretch_gradient.argtypes = [vp, dp]
+    L.mfb_stretch_dev.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    L.mfb_stretch_energy.argtypes = [vp, dp, dp]
     _lib = L
     return L
 
@@ -446,6 +453,29 @@ class MixedStretch:
         self._check(self.L.mfb_jacobian_x_coo(self.h, _ip(r), _ip(c), _dp(v)))
         keep = r >= 0
         return r[keep], c[keep], v[keep]
+
+    # ---- the non-mixed Stretch variable (src/variables/stretch.cpp) on the same mesh and pattern ----
+    def stretch_update(self, x, h):
+        x = _f64(x)
+        self._check(self.L.mfb_stretch_update(self.h, _dp(x), h))
+
+    def stretch_lhs(self):
+        """(outer, inner, values) of Stretch::lhs() on the Assembler pattern"""
+        outer, inner = self.csr_pattern()
+        vals = np.empty(self.nnz)
+        self._check(self.L.mfb_stretch_lhs_values(self.h, _dp(vals)))
+        return outer, inner, vals
+
+    def stretch_gradient(self):
+        out = np.empty(self.dim * self.nfree)
+        self._check(self.L.mfb_stretch_gradient(self.h, _dp(out)))
+        return out
+
+    def stretch_energy(self, x):
+        x = _f64(x)
+        e = C.c_double(0)
+        self._check(self.L.mfb_stretch_energy(self.h, _dp(x), C.byref(e)))
+        return e.value
 
     # ---- saddle-point systems (SystemMatrixIndefinite / DualCondensedSystem, linear_system.h:64-239); need newton_init ----
     def kkt_size(self):

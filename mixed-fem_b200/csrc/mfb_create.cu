@@ -391,6 +391,7 @@ extern "C" void mfb_destroy(mfb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   mfb::saddle_free(c);
+  mfb::stretch_free(c);
   mfb_newton_free(c);
   mfb::comm_free(c);
   if (c->copy_stream) {

@@ -53,6 +53,7 @@ struct NewtonView {
   int* vfree;
 };
 void saddle_free(mfb_ctx* c);                                     // mfb_saddle.cu
+void stretch_free(mfb_ctx* c);                                    // mfb_stretch.cu
 int newton_view(mfb_ctx* c, NewtonView* v);                       // MFB_ERR_INVALID before mfb_newton_init
 int newton_disp_gradient(mfb_ctx* c, double* out_free_dev);       // Displacement::gradient() = PM (x - x_tilde - h^2 f), d*nF
 }  // namespace mfb
@@ -106,6 +107,7 @@ struct mfb_ctx {
   int ev_count = 0;
   void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)
   void* saddle = nullptr;     // scratch of the saddle-point systems (mfb_saddle.cu)
+  void* stretch = nullptr;    // the non-mixed Stretch variable's lhs values / gradient (mfb_stretch.cu)
   // host-buffer entry points (mfb_update / mfb_rhs): the device->host copy of rhs_ runs on its own stream as soon as
   // the vertex vectors are final, beside the kernel that writes the CSR values
   cudaStream_t copy_stream = 0;

@@ -1,0 +1,238 @@
+// The NON-mixed variable of the reference, for the FEM-vs-MFEM comparisons of apps/convergence.cpp:
+//
+//   Stretch<DIM>::energy / update / rhs / gradient ... src/variables/stretch.cpp:16-68
+//   F-form material virtuals ......................... src/energies/material_model.h:43-62
+//   StableNeohookean energy/gradient/hessian(Vector9d)  src/energies/stable_neohookean.cpp:93-232
+//   sim::simple_psd_fix(H, 0.0) ....................... deps/Bartels/src/simple_psd_fix.cpp:5-22
+//   Assembler / VecAssembler .......................... src/utils/sparse_utils.h:11-64, 66-120 (same pattern and scatter map as
+//                                                       the mixed variable: both are built from T_ and free_map_)
+//
+// Per tet (one thread):  F = Ds Dm^-1;  g = dpsi/dF (9);  H = d2psi/dF2 (9x9), eigenvalues below 0 clamped to 0;
+//   g_e = Jloc^T g vol h^2 (12);  H_e = Jloc^T H Jloc vol h^2 (12x12), Jloc = dphi^T (x) I_3;  both reduced into the
+//   global vector / the reference-layout CSR through the element -> nonzero map.
+//
+// The reference's F-form code for Stable Neo-Hookean is symbolic-toolbox output (81 expanded polynomials); it is the
+// expansion of   psi = mu/2 (|F|^2 - 3) - mu (J - 1) + la/2 (J - 1)^2,
+//   g = mu F + (la (J - 1) - mu) cof F,   H = mu I + la vec(cof F) vec(cof F)^T + (la (J - 1) - mu) d(cof F)/dF,
+// which is what is evaluated here (tests/test_oracle_stretch.py checks the closed form against finite differences of
+// the energy expression of stable_neohookean.cpp:93-107).  Only Stable Neo-Hookean tets are implemented (config C2's
+// material); other models return MFB_ERR_UNSUPPORTED.  This is a coverage path, not a tuned one: full 12x12 scattered
+// FP64 reductions, the 9x9 Jacobi eigen-solve in local memory.
+#include "mfb_ctx.cuh"
+#include <cmath>
+
+using namespace mfb;
+
+#define CHECK_CTX(c) do { if (!(c)) { g_last_error = "null context"; return MFB_ERR_INVALID; } cudaSetDevice((c)->device); } while (0)
+
+namespace {
+
+inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
+
+// cof F = dJ/dF, column-major [3c + r]
+__device__ __forceinline__ void cofactor3(const double* F, double* C) {
+  C[0] = F[4] * F[8] - F[7] * F[5]; C[1] = F[5] * F[6] - F[8] * F[3]; C[2] = F[3] * F[7] - F[6] * F[4];
+  C[3] = F[7] * F[2] - F[1] * F[8]; C[4] = F[8] * F[0] - F[2] * F[6]; C[5] = F[6] * F[1] - F[0] * F[7];
+  C[6] = F[1] * F[5] - F[4] * F[2]; C[7] = F[2] * F[3] - F[5] * F[0]; C[8] = F[0] * F[4] - F[3] * F[1];
+}
+
+// d2J / dF(r,c) dF(s,c2) = sum_{m,n} eps(r,s,m) eps(c,c2,n) F(m,n): non-zero only for r != s and c != c2
+__device__ __forceinline__ double d2J(const double* F, int r, int c, int s, int c2) {
+  if (r == s || c == c2) return 0.0;
+  const int m = 3 - r - s, n = 3 - c - c2;
+  const double sr = ((s - r + 3) % 3 == 1) ? 1.0 : -1.0;       // eps(r,s,m)
+  const double sc = ((c2 - c + 3) % 3 == 1) ? 1.0 : -1.0;      // eps(c,c2,n)
+  return sr * sc * F[3 * n + m];
+}
+
+__global__ void __launch_bounds__(128) k_stretch_update_tet(DevMesh m, const double* __restrict__ x, double h2, double* __restrict__ Avals,
+                                                            double* __restrict__ grad) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m.nE) return;
+  const int64_t ld = m.ld;
+  double dphi[9], F[9], C[9];
+  tet_F(m, e, x, dphi, F);
+  cofactor3(F, C);
+  const MaterialDev mat = m.matid ? m.mats[m.matid[e]] : m.mat0;
+  const double mu = mat.mu, la = mat.la;
+  const double J = F[0] * C[0] + F[1] * C[1] + F[2] * C[2];
+  const double k1 = la * (J - 1.0) - mu;
+  const double scale = m.vol[e] * h2;
+  // gradient: Jloc^T g
+  double g9[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) g9[i] = mu * F[i] + k1 * C[i];
+  scatter_vertex<3>(m, e, dphi, g9, scale, grad);
+  // Hessian, packed lower, then simple_psd_fix(H, 0)
+  double H[45], V[81];
+#pragma unroll
+  for (int i = 0; i < 9; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j)
+      H[symidx(i, j)] = (i == j ? mu : 0.0) + la * C[i] * C[j] + k1 * d2J(F, i % 3, i / 3, j % 3, j / 3);
+  jacobi_eig<9>(H, V);
+  double ev[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
+  // HJ[i][3(k-1)+s] = sum_c2 dphi(k,c2) Hfix[i, 3 c2 + s]  for the vertices k = 1..3 ; vertex 0 = -(sum)
+  // K(j,r ; k,s) = sum_c dphi(j,c) HJ[3c + r][k,s]
+  int sidx[16], stride[4];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) sidx[q] = m.smap[q * ld + e];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) stride[k] = m.sstride[k * ld + e];
+  double d4[4][3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    d4[0][c] = -(dphi[c] + dphi[3 + c] + dphi[6 + c]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) d4[k + 1][c] = dphi[3 * k + c];
+  }
+  for (int k = 0; k < 4; ++k) {
+    for (int s = 0; s < 3; ++s) {
+      // column (k,s) of Hfix Jloc
+      double col[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        double a = 0.0;
+#pragma unroll
+        for (int c2 = 0; c2 < 3; ++c2) {
+          const int jj = 3 * c2 + s;
+          double hij = 0.0;
+#pragma unroll
+          for (int q = 0; q < 9; ++q) hij += V[q * 9 + i] * V[q * 9 + jj] * ev[q];
+          a += d4[k][c2] * hij;
+        }
+        col[i] = a;
+      }
+      for (int j = 0; j < 4; ++j) {
+        const int base = sidx[j * 4 + k];
+        if (base < 0) continue;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          const double v = d4[j][0] * col[r] + d4[j][1] * col[3 + r] + d4[j][2] * col[6 + r];
+          red_add(&Avals[(int64_t)base + (int64_t)r * stride[j] + s], scale * v);
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) k_stretch_energy_tet(DevMesh m, const double* __restrict__ x, double* __restrict__ partials) {
+  __shared__ double sh[4];
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  double val = 0.0;
+  if (e < m.nE) {
+    double dphi[9], F[9], C[9];
+    tet_F(m, e, x, dphi, F);
+    cofactor3(F, C);
+    const MaterialDev mat = m.matid ? m.mats[m.matid[e]] : m.mat0;
+    const double J = F[0] * C[0] + F[1] * C[1] + F[2] * C[2];
+    double i1 = 0.0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) i1 += F[i] * F[i];
+    // stable_neohookean.cpp:93-107: mu (1 - J) + la/2 (1 - J)^2 + mu/2 (|F|^2 - 3)
+    val = (mat.mu * (1.0 - J) + 0.5 * mat.la * (1.0 - J) * (1.0 - J) + 0.5 * mat.mu * (i1 - 3.0)) * m.vol[e];
+  }
+  const double r = block_sum_128(val, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = r;
+}
+
+struct StretchState {
+  DBuf<double> Avals, grad;
+  bool updated = false;
+};
+
+int stretch_get(mfb_ctx* c, StretchState** out) {
+  if (c->kind != MFB_TET) { g_last_error = "Stretch variable: tetrahedral meshes only"; return MFB_ERR_UNSUPPORTED; }
+  if (c->matid.p) {
+    g_last_error = "Stretch variable: one material per mesh"; return MFB_ERR_UNSUPPORTED;
+  }
+  if (c->mat0_host.model != 0) { g_last_error = "Stretch variable: only Stable-Neohookean has an F-form on the device"; return MFB_ERR_UNSUPPORTED; }
+  if (!c->stretch) {
+    StretchState* s = new StretchState();
+    c->stretch = s;
+    int rc;
+    if ((rc = s->Avals.alloc(c->nnz > 0 ? (size_t)c->nnz : 1)) || (rc = s->grad.alloc((size_t)c->dim * c->nF + 1))) return rc;
+  }
+  *out = (StretchState*)c->stretch;
+  return MFB_OK;
+}
+
+}  // namespace
+
+namespace mfb {
+void stretch_free(mfb_ctx* c) {
+  if (c && c->stretch) { delete (StretchState*)c->stretch; c->stretch = nullptr; }
+}
+}  // namespace mfb
+
+extern "C" int mfb_stretch_update_dev(mfb_ctx* c, const double* x_dev, double h) {
+  CHECK_CTX(c);
+  StretchState* s; int rc;
+  if (!x_dev) return MFB_ERR_INVALID;
+  if ((rc = stretch_get(c, &s))) return rc;
+  cudaStream_t st = c->stream;
+  MFB_CUDA(cudaMemsetAsync(s->Avals.p, 0, (size_t)(c->nnz > 0 ? c->nnz : 1) * 8, st));
+  MFB_CUDA(cudaMemsetAsync(s->grad.p, 0, (size_t)c->dim * c->nF * 8, st));
+  k_stretch_update_tet<<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p);
+  c->launches += 1;
+  MFB_CUDA(cudaGetLastError());
+  s->updated = true;
+  return MFB_OK;
+}
+
+extern "C" int mfb_stretch_update(mfb_ctx* c, const double* x, double h) {
+  CHECK_CTX(c);
+  if (!x) return MFB_ERR_INVALID;
+  MFB_CUDA(cudaMemcpyAsync(c->xdev.p, x, (size_t)c->dim * c->nV * 8, cudaMemcpyHostToDevice, c->stream));
+  return mfb_stretch_update_dev(c, c->xdev.p, h);
+}
+
+extern "C" int mfb_stretch_lhs_values(mfb_ctx* c, double* values) {
+  CHECK_CTX(c);
+  StretchState* s; int rc;
+  if (!values) return MFB_ERR_INVALID;
+  if ((rc = stretch_get(c, &s))) return rc;
+  if (!s->updated) { g_last_error = "mfb_stretch_lhs_values: call mfb_stretch_update first"; return MFB_ERR_STATE; }
+  MFB_CUDA(cudaMemcpyAsync(values, s->Avals.p, (size_t)c->nnz * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_stretch_dev(mfb_ctx* c, const double** lhs_values_dev, const double** gradient_dev) {
+  CHECK_CTX(c);
+  StretchState* s; int rc;
+  if ((rc = stretch_get(c, &s))) return rc;
+  if (!s->updated) { g_last_error = "mfb_stretch_dev: call mfb_stretch_update first"; return MFB_ERR_STATE; }
+  if (lhs_values_dev) *lhs_values_dev = s->Avals.p;
+  if (gradient_dev) *gradient_dev = s->grad.p;
+  return MFB_OK;
+}
+
+extern "C" int mfb_stretch_gradient(mfb_ctx* c, double* out) {
+  CHECK_CTX(c);
+  StretchState* s; int rc;
+  if (!out) return MFB_ERR_INVALID;
+  if ((rc = stretch_get(c, &s))) return rc;
+  if (!s->updated) { g_last_error = "mfb_stretch_gradient: call mfb_stretch_update first"; return MFB_ERR_STATE; }
+  MFB_CUDA(cudaMemcpyAsync(out, s->grad.p, (size_t)c->dim * c->nF * 8, cudaMemcpyDeviceToHost, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
+}
+
+extern "C" int mfb_stretch_energy(mfb_ctx* c, const double* x, double* e) {
+  CHECK_CTX(c);
+  StretchState* s; int rc;
+  if (!x || !e) return MFB_ERR_INVALID;
+  if ((rc = stretch_get(c, &s))) return rc;
+  cudaStream_t st = c->stream;
+  MFB_CUDA(cudaMemcpyAsync(c->xdev.p, x, (size_t)c->dim * c->nV * 8, cudaMemcpyHostToDevice, st));
+  k_stretch_energy_tet<<<c->grid(), 128, 0, st>>>(c->mesh(), c->xdev.p, c->partials.p);
+  k_sum_partials<<<1, 256, 0, st>>>(c->partials.p, c->grid(), c->scal.p);
+  c->launches += 2;
+  MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8, cudaMemcpyDeviceToHost, st));
+  MFB_CUDA(cudaStreamSynchronize(st));
+  *e = c->h_scal[0];
+  return MFB_OK;
+}

@@ -1,0 +1,44 @@
+"""GPU: the non-mixed Stretch variable (mfb_stretch_*, mixed-fem_b200/csrc/mfb_stretch.cu) against oracle/stretch.py:
+energy, assembled gradient and assembled matrix on the Assembler pattern, 1e-10 relative (north_star)."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+import mixed_fem_b200 as mf
+from mixed_fem_b200 import meshgen
+from oracle import stretch as ostretch
+from tests.common import LA, MU, vec_rel
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,scale", [((6, 3, 3), 1.0), ((5, 4, 3), 6.0)])
+def test_stretch_update_matches_oracle(built, n, scale):
+    """scale 6: strongly deformed state, a good part of the element Hessians is indefinite and goes through the clamp"""
+    V, T = meshgen.kuhn_grid(*n)
+    fm = meshgen.pinned_free_map(V)
+    x = meshgen.deformed_positions(V, 1.0 / n[0], scale=scale)
+    h = 0.0333
+    gpu = mf.MixedStretch(V, T, fm, [("Stable-Neohookean", MU, LA)])
+    cpu = ostretch.OracleStretch(V, T, fm, MU, LA)
+    cpu.update(x, h)
+    gpu.stretch_update(x, h)
+    outer, inner, vals = gpu.stretch_lhs()
+    A = sp.csr_matrix((vals, inner, outer), shape=cpu.lhs.shape)
+    assert abs(A - cpu.lhs).max() <= 1e-10 * abs(cpu.lhs).max()
+    assert vec_rel(gpu.stretch_gradient(), cpu.grad) <= 1e-10
+    assert abs(gpu.stretch_energy(x) - cpu.energy(x)) <= 1e-11 * abs(cpu.energy(x))
+    if scale > 1.0:     # the clamp was exercised
+        F = meshgen.deformation_gradients(V, T, x)
+        _, H = ostretch.gradient_hessian(F, MU, LA)
+        assert (np.linalg.eigvalsh(H)[:, 0] < -1e-6 * MU).mean() > 0.05
+    gpu.close()
+
+
+def test_stretch_rejects_what_it_does_not_implement(built):
+    V, T = meshgen.kuhn_grid(2, 2, 2)
+    fm = meshgen.pinned_free_map(V)
+    gpu = mf.MixedStretch(V, T, fm, [("ARAP", MU, LA)])
+    with pytest.raises(mf.MfbError):
+        gpu.stretch_update(V.reshape(-1), 0.1)
+    gpu.close()

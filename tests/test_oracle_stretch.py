@@ -1,0 +1,49 @@
+"""CPU: the oracle's Stretch variable (oracle/stretch.py).  The closed-form Stable Neo-Hookean F-form gradient / Hessian
+are checked against central differences of the reference's expanded energy expression (stable_neohookean.cpp:107), the
+assembled vector / matrix against differences of the assembled energy."""
+import numpy as np
+
+from mixed_fem_b200 import meshgen
+from oracle import stretch as ostretch
+from tests.common import LA, MU
+
+
+def test_snh_f_form_closed_forms_match_the_expanded_energy():
+    rng = np.random.default_rng(1)
+    F = np.eye(3)[None] + 0.3 * rng.standard_normal((20, 3, 3))
+    g, H = ostretch.gradient_hessian(F, MU, LA)
+    F9 = np.transpose(F, (0, 2, 1)).reshape(-1, 9)
+    eps = 1e-6
+    for i in range(9):
+        d = np.zeros(9); d[i] = eps
+        fd = (ostretch.energy_expanded(F9 + d, MU, LA) - ostretch.energy_expanded(F9 - d, MU, LA)) / (2 * eps)
+        assert np.allclose(fd, g[:, i], rtol=1e-6, atol=1e-6 * np.abs(g).max())
+        gp, _ = ostretch.gradient_hessian(np.transpose((F9 + d).reshape(-1, 3, 3), (0, 2, 1)), MU, LA)
+        gm, _ = ostretch.gradient_hessian(np.transpose((F9 - d).reshape(-1, 3, 3), (0, 2, 1)), MU, LA)
+        assert np.allclose((gp - gm) / (2 * eps), H[:, :, i], rtol=1e-5, atol=1e-6 * np.abs(H).max())
+    assert np.abs(H - np.transpose(H, (0, 2, 1))).max() <= 1e-9 * np.abs(H).max()
+
+
+def test_simple_psd_fix_clamps_at_zero():
+    rng = np.random.default_rng(2)
+    A = rng.standard_normal((5, 9, 9)); A = A + np.transpose(A, (0, 2, 1))
+    B = ostretch.simple_psd_fix(A, 0.0)
+    w = np.linalg.eigvalsh(B)
+    assert w.min() >= -1e-12 and np.allclose(np.linalg.eigvalsh(A).clip(min=0), w, atol=1e-10)
+
+
+def test_assembled_gradient_is_the_derivative_of_the_energy():
+    V, T = meshgen.kuhn_grid(3, 2, 2)
+    fm = meshgen.pinned_free_map(V)
+    st = ostretch.OracleStretch(V, T, fm, MU, LA)
+    x = meshgen.deformed_positions(V, 1.0 / 3)
+    h = 0.1
+    st.update(x, h)
+    free = np.nonzero(fm >= 0)[0]
+    rng = np.random.default_rng(0)
+    for v in rng.choice(free, 6, replace=False):
+        for l in range(3):
+            d = np.zeros_like(x); d[3 * v + l] = 1e-6
+            fd = (st.energy(x + d) - st.energy(x - d)) / 2e-6 * h * h
+            assert abs(fd - st.grad[3 * fm[v] + l]) <= 1e-5 * np.abs(st.grad).max()
+    assert abs(st.lhs - st.lhs.T).max() <= 1e-10 * abs(st.lhs).max()
