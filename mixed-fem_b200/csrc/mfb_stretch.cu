@@ -15,9 +15,10 @@
 // expansion of   psi = mu/2 (|F|^2 - 3) - mu (J - 1) + la/2 (J - 1)^2,
 //   g = mu F + (la (J - 1) - mu) cof F,   H = mu I + la vec(cof F) vec(cof F)^T + (la (J - 1) - mu) d(cof F)/dF,
 // which is what is evaluated here (tests/test_oracle_stretch.py checks the closed form against finite differences of
-// the energy expression of stable_neohookean.cpp:93-107).  Only Stable Neo-Hookean tets are implemented (config C2's
-// material); other models return MFB_ERR_UNSUPPORTED.  This is a coverage path, not a tuned one: full 12x12 scattered
-// FP64 reductions, the 9x9 Jacobi eigen-solve in local memory.
+// the energy expression of stable_neohookean.cpp:93-107).  Only Stable Neo-Hookean is implemented, for tets (config C2)
+// and 2D triangles (config C1's material; stable_neohookean.cpp:274-324 is the same closed form with a 2x2 cofactor);
+// other models return MFB_ERR_UNSUPPORTED.  This is a coverage path, not a tuned one: full (d(d+1))^2 scattered FP64
+// reductions, the d^2 x d^2 Jacobi eigen-solve in local memory.
 #include "mfb_ctx.cuh"
 #include <cmath>
 
@@ -45,72 +46,93 @@ __device__ __forceinline__ double d2J(const double* F, int r, int c, int s, int 
   return sr * sc * F[3 * n + m];
 }
 
-__global__ void __launch_bounds__(128) k_stretch_update_tet(DevMesh m, const double* __restrict__ x, double h2, double* __restrict__ Avals,
-                                                            double* __restrict__ grad) {
+// 2D twins: cof F = [F11 -F10; -F01 F00] (column-major [2c + r]), d2J = eps(r,s) eps(c,c2)
+__device__ __forceinline__ void cofactor2(const double* F, double* C) { C[0] = F[3]; C[1] = -F[2]; C[2] = -F[1]; C[3] = F[0]; }
+__device__ __forceinline__ double d2J2(int r, int c, int s, int c2) {
+  if (r == s || c == c2) return 0.0;
+  return ((s > r) ? 1.0 : -1.0) * ((c2 > c) ? 1.0 : -1.0);
+}
+
+// psi, J-dependent coefficient and cofactor of the Stable Neo-Hookean F-form for DIM = 2, 3
+// (stable_neohookean.cpp:93-107 / :274-282: mu (1 - J) + la/2 (1 - J)^2 + mu/2 (|F|^2 - DIM))
+template <int DIM>
+__device__ __forceinline__ double snh_J_cof(const double* F, double* C) {
+  if constexpr (DIM == 3) { cofactor3(F, C); return F[0] * C[0] + F[1] * C[1] + F[2] * C[2]; }
+  else { cofactor2(F, C); return F[0] * F[3] - F[2] * F[1]; }
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double* __restrict__ x, double h2, double* __restrict__ Avals,
+                                                        double* __restrict__ grad) {
+  constexpr int M = DIM * DIM, NPE = DIM + 1;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
-  double dphi[9], F[9], C[9];
-  tet_F(m, e, x, dphi, F);
-  cofactor3(F, C);
+  double dphi[M], F[M], C[M];
+  elem_F<DIM>(m, e, x, dphi, F);
+  const double J = snh_J_cof<DIM>(F, C);
   const MaterialDev mat = m.matid ? m.mats[m.matid[e]] : m.mat0;
   const double mu = mat.mu, la = mat.la;
-  const double J = F[0] * C[0] + F[1] * C[1] + F[2] * C[2];
   const double k1 = la * (J - 1.0) - mu;
   const double scale = m.vol[e] * h2;
   // gradient: Jloc^T g
-  double g9[9];
+  double g9[M];
 #pragma unroll
-  for (int i = 0; i < 9; ++i) g9[i] = mu * F[i] + k1 * C[i];
-  scatter_vertex<3>(m, e, dphi, g9, scale, grad);
+  for (int i = 0; i < M; ++i) g9[i] = mu * F[i] + k1 * C[i];
+  scatter_vertex<DIM>(m, e, dphi, g9, scale, grad);
   // Hessian, packed lower, then simple_psd_fix(H, 0)
-  double H[45], V[81];
+  double H[M * (M + 1) / 2], V[M * M];
 #pragma unroll
-  for (int i = 0; i < 9; ++i)
+  for (int i = 0; i < M; ++i)
 #pragma unroll
-    for (int j = 0; j <= i; ++j)
-      H[symidx(i, j)] = (i == j ? mu : 0.0) + la * C[i] * C[j] + k1 * d2J(F, i % 3, i / 3, j % 3, j / 3);
-  jacobi_eig<9>(H, V);
-  double ev[9];
+    for (int j = 0; j <= i; ++j) {
+      double dd;
+      if constexpr (DIM == 3) dd = d2J(F, i % 3, i / 3, j % 3, j / 3);
+      else dd = d2J2(i % 2, i / 2, j % 2, j / 2);
+      H[symidx(i, j)] = (i == j ? mu : 0.0) + la * C[i] * C[j] + k1 * dd;
+    }
+  jacobi_eig<M>(H, V);
+  double ev[M];
 #pragma unroll
-  for (int k = 0; k < 9; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
-  // HJ[i][3(k-1)+s] = sum_c2 dphi(k,c2) Hfix[i, 3 c2 + s]  for the vertices k = 1..3 ; vertex 0 = -(sum)
-  // K(j,r ; k,s) = sum_c dphi(j,c) HJ[3c + r][k,s]
-  int sidx[16], stride[4];
+  for (int k = 0; k < M; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
+  // column (k,s) of Hfix Jloc:  col[i] = sum_c2 dphi(k,c2) Hfix[i, DIM c2 + s] ;  K(j,r ; k,s) = sum_c dphi(j,c) col[DIM c + r]
+  int sidx[NPE * NPE], stride[NPE];
 #pragma unroll
-  for (int q = 0; q < 16; ++q) sidx[q] = m.smap[q * ld + e];
+  for (int q = 0; q < NPE * NPE; ++q) sidx[q] = m.smap[q * ld + e];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) stride[k] = m.sstride[k * ld + e];
-  double d4[4][3];
+  for (int k = 0; k < NPE; ++k) stride[k] = m.sstride[k * ld + e];
+  double d4[NPE][DIM];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    d4[0][c] = -(dphi[c] + dphi[3 + c] + dphi[6 + c]);
+  for (int c = 0; c < DIM; ++c) {
+    double sum = 0.0;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) d4[k + 1][c] = dphi[3 * k + c];
+    for (int k = 0; k < DIM; ++k) { d4[k + 1][c] = dphi[DIM * k + c]; sum += dphi[DIM * k + c]; }
+    d4[0][c] = -sum;
   }
-  for (int k = 0; k < 4; ++k) {
-    for (int s = 0; s < 3; ++s) {
-      // column (k,s) of Hfix Jloc
-      double col[9];
+  for (int k = 0; k < NPE; ++k) {
+    for (int s = 0; s < DIM; ++s) {
+      double col[M];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) {
+      for (int i = 0; i < M; ++i) {
         double a = 0.0;
 #pragma unroll
-        for (int c2 = 0; c2 < 3; ++c2) {
-          const int jj = 3 * c2 + s;
+        for (int c2 = 0; c2 < DIM; ++c2) {
+          const int jj = DIM * c2 + s;
           double hij = 0.0;
 #pragma unroll
-          for (int q = 0; q < 9; ++q) hij += V[q * 9 + i] * V[q * 9 + jj] * ev[q];
+          for (int q = 0; q < M; ++q) hij += V[q * M + i] * V[q * M + jj] * ev[q];
           a += d4[k][c2] * hij;
         }
         col[i] = a;
       }
-      for (int j = 0; j < 4; ++j) {
-        const int base = sidx[j * 4 + k];
+      for (int j = 0; j < NPE; ++j) {
+        const int base = sidx[j * NPE + k];
         if (base < 0) continue;
 #pragma unroll
-        for (int r = 0; r < 3; ++r) {
-          const double v = d4[j][0] * col[r] + d4[j][1] * col[3 + r] + d4[j][2] * col[6 + r];
+        for (int r = 0; r < DIM; ++r) {
+          double v = 0.0;
+#pragma unroll
+          for (int c = 0; c < DIM; ++c) v += d4[j][c] * col[DIM * c + r];
           red_add(&Avals[(int64_t)base + (int64_t)r * stride[j] + s], scale * v);
         }
       }
@@ -118,21 +140,21 @@ __global__ void __launch_bounds__(128) k_stretch_update_tet(DevMesh m, const dou
   }
 }
 
-__global__ void __launch_bounds__(128) k_stretch_energy_tet(DevMesh m, const double* __restrict__ x, double* __restrict__ partials) {
+template <int DIM>
+__global__ void __launch_bounds__(128) k_stretch_energy(DevMesh m, const double* __restrict__ x, double* __restrict__ partials) {
+  constexpr int M = DIM * DIM;
   __shared__ double sh[4];
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   double val = 0.0;
   if (e < m.nE) {
-    double dphi[9], F[9], C[9];
-    tet_F(m, e, x, dphi, F);
-    cofactor3(F, C);
+    double dphi[M], F[M], C[M];
+    elem_F<DIM>(m, e, x, dphi, F);
+    const double J = snh_J_cof<DIM>(F, C);
     const MaterialDev mat = m.matid ? m.mats[m.matid[e]] : m.mat0;
-    const double J = F[0] * C[0] + F[1] * C[1] + F[2] * C[2];
     double i1 = 0.0;
 #pragma unroll
-    for (int i = 0; i < 9; ++i) i1 += F[i] * F[i];
-    // stable_neohookean.cpp:93-107: mu (1 - J) + la/2 (1 - J)^2 + mu/2 (|F|^2 - 3)
-    val = (mat.mu * (1.0 - J) + 0.5 * mat.la * (1.0 - J) * (1.0 - J) + 0.5 * mat.mu * (i1 - 3.0)) * m.vol[e];
+    for (int i = 0; i < M; ++i) i1 += F[i] * F[i];
+    val = (mat.mu * (1.0 - J) + 0.5 * mat.la * (1.0 - J) * (1.0 - J) + 0.5 * mat.mu * (i1 - (double)DIM)) * m.vol[e];
   }
   const double r = block_sum_128(val, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = r;
@@ -144,7 +166,7 @@ struct StretchState {
 };
 
 int stretch_get(mfb_ctx* c, StretchState** out) {
-  if (c->kind != MFB_TET) { g_last_error = "Stretch variable: tetrahedral meshes only"; return MFB_ERR_UNSUPPORTED; }
+  if (c->kind == MFB_SHELL) { g_last_error = "Stretch variable: tetrahedra and 2D triangles only"; return MFB_ERR_UNSUPPORTED; }
   if (c->matid.p) {
     g_last_error = "Stretch variable: one material per mesh"; return MFB_ERR_UNSUPPORTED;
   }
@@ -175,7 +197,8 @@ extern "C" int mfb_stretch_update_dev(mfb_ctx* c, const double* x_dev, double h)
   cudaStream_t st = c->stream;
   MFB_CUDA(cudaMemsetAsync(s->Avals.p, 0, (size_t)(c->nnz > 0 ? c->nnz : 1) * 8, st));
   MFB_CUDA(cudaMemsetAsync(s->grad.p, 0, (size_t)c->dim * c->nF * 8, st));
-  k_stretch_update_tet<<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p);
+  if (c->dim == 3) k_stretch_update<3><<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p);
+  else k_stretch_update<2><<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p);
   c->launches += 1;
   MFB_CUDA(cudaGetLastError());
   s->updated = true;
@@ -228,7 +251,8 @@ extern "C" int mfb_stretch_energy(mfb_ctx* c, const double* x, double* e) {
   if ((rc = stretch_get(c, &s))) return rc;
   cudaStream_t st = c->stream;
   MFB_CUDA(cudaMemcpyAsync(c->xdev.p, x, (size_t)c->dim * c->nV * 8, cudaMemcpyHostToDevice, st));
-  k_stretch_energy_tet<<<c->grid(), 128, 0, st>>>(c->mesh(), c->xdev.p, c->partials.p);
+  if (c->dim == 3) k_stretch_energy<3><<<c->grid(), 128, 0, st>>>(c->mesh(), c->xdev.p, c->partials.p);
+  else k_stretch_energy<2><<<c->grid(), 128, 0, st>>>(c->mesh(), c->xdev.p, c->partials.p);
   k_sum_partials<<<1, 256, 0, st>>>(c->partials.p, c->grid(), c->scal.p);
   c->launches += 2;
   MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8, cudaMemcpyDeviceToHost, st));

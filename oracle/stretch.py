@@ -1,9 +1,10 @@
 """ORACLE — TEST INFRASTRUCTURE ONLY (imported by tests/ only; never by the product).
 
-numpy restatement of the reference's NON-mixed variable for tetrahedra with the Stable Neo-Hookean F-form:
+numpy restatement of the reference's NON-mixed variable for tetrahedra and 2D triangles with the Stable Neo-Hookean
+F-form:
 
   Stretch<DIM>::energy / update / rhs / gradient ..... src/variables/stretch.cpp:16-68
-  StableNeohookean::energy/gradient/hessian(Vector9d)  src/energies/stable_neohookean.cpp:93-232
+  StableNeohookean::energy/gradient/hessian(Vector9d)  src/energies/stable_neohookean.cpp:93-232 (Vector4d: :274-324)
   sim::simple_psd_fix(H, 0.0) ........................ deps/Bartels/src/simple_psd_fix.cpp:5-22
   local Jacobian Jloc = dphi^T (x) I_3 ............... src/mesh/tet_mesh.cpp:43-75
   Assembler / VecAssembler ........................... src/utils/sparse_utils.h:11-120 (sums of element blocks at free dofs)
@@ -31,17 +32,30 @@ for _i, _j, _k in ((0, 1, 2), (1, 2, 0), (2, 0, 1)):
     _EPS[_j, _i, _k] = -1.0
 
 
+_EPS2 = np.array([[0.0, 1.0], [-1.0, 0.0]])
+
+
+def energy_expanded_2d(F4, mu, la):
+    """stable_neohookean.cpp:274-282 verbatim (F4 column-major: F11, F21, F12, F22)"""
+    F1_1, F2_1, F1_2, F2_2 = [F4[..., i] for i in range(4)]
+    t = -F1_1 * F2_2 + F1_2 * F2_1 + 1.0
+    return mu * t + (la * t ** 2) / 2.0 + (mu * (F1_1 * F1_1 + F1_2 * F1_2 + F2_1 * F2_1 + F2_2 * F2_2 - 2.0)) / 2.0
+
+
 def gradient_hessian(F, mu, la):
-    """F (nE,3,3) -> g (nE,9), H (nE,9,9), index 3c + r (column-major vec F), BEFORE the psd fix"""
-    nE = F.shape[0]
+    """F (nE,d,d) -> g (nE,d*d), H (nE,d*d,d*d), index d*c + r (column-major vec F), BEFORE the psd fix"""
+    nE, d = F.shape[0], F.shape[1]
+    M = d * d
     J = np.linalg.det(F)
     cof = J[:, None, None] * np.transpose(np.linalg.inv(F), (0, 2, 1))        # dJ/dF
-    vec = lambda A: np.transpose(A, (0, 2, 1)).reshape(nE, 9)
+    vec = lambda A: np.transpose(A, (0, 2, 1)).reshape(nE, M)
     k1 = la * (J - 1.0) - mu
     g = mu * vec(F) + k1[:, None] * vec(cof)
-    # d2J/dF(r,c)dF(s,c2) = eps(r,s,m) eps(c,c2,n) F(m,n)
-    d2 = np.einsum("rsm,cdn,emn->ecrds", _EPS, _EPS, F).reshape(nE, 9, 9)       # [3c+r, 3d+s]
-    H = mu * np.eye(9)[None] + la * np.einsum("ei,ej->eij", vec(cof), vec(cof)) + k1[:, None, None] * d2
+    if d == 3:      # d2J/dF(r,c)dF(s,c2) = eps(r,s,m) eps(c,c2,n) F(m,n)
+        d2 = np.einsum("rsm,cdn,emn->ecrds", _EPS, _EPS, F).reshape(nE, M, M)      # [3c+r, 3c2+s]
+    else:           # J = F00 F11 - F01 F10
+        d2 = np.broadcast_to(np.einsum("rs,cd->crds", _EPS2, _EPS2).reshape(1, M, M), (nE, M, M))
+    H = mu * np.eye(M)[None] + la * np.einsum("ei,ej->eij", vec(cof), vec(cof)) + k1[:, None, None] * d2
     return g, H
 
 
@@ -55,32 +69,40 @@ class OracleStretch:
     def __init__(self, V, T, free_map, mu, la):
         self.V, self.T, self.fm = np.asarray(V, float), np.asarray(T), np.asarray(free_map)
         self.mu, self.la = mu, la
-        self.dphi = meshgen.tet_dphi(self.V, self.T)                              # (nE,4,3)
+        self.d = d = self.V.shape[1]
         X = self.V[self.T]
-        self.vol = np.abs(np.linalg.det(X[:, 1:, :] - X[:, :1, :])) / 6.0          # |igl::volume| (tet_mesh.cpp:31-34)
+        Dm = np.transpose(X[:, 1:, :] - X[:, :1, :], (0, 2, 1))
+        inv = np.linalg.inv(Dm)
+        self.dphi = np.concatenate([-inv.sum(axis=1, keepdims=True), inv], axis=1)      # (nE,d+1,d), linear_*_dphi_dX.cpp
+        # |igl::volume| for tets (tet_mesh.cpp:31-34), igl::doublearea for 2D triangles (tri2d_mesh.cpp:32-34)
+        self.vol = np.abs(np.linalg.det(Dm)) / 6.0 if d == 3 else np.linalg.det(Dm)
         self.nF = int(self.fm.max()) + 1
-        # Jloc (nE, 9, 12): dF(3c+r) / dx(3k+r2) = dphi(k,c) delta(r,r2)
+        # Jloc (nE, d*d, d*(d+1)): dF(d c + r) / dx(d k + r2) = dphi(k,c) delta(r,r2)
         nE = self.T.shape[0]
-        self.Jloc = np.einsum("ekc,rs->ecrks", self.dphi, np.eye(3)).reshape(nE, 9, 12)
+        self.Jloc = np.einsum("ekc,rs->ecrks", self.dphi, np.eye(d)).reshape(nE, d * d, d * (d + 1))
 
     def energy(self, x):
+        d = self.d
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
-        F9 = np.transpose(F, (0, 2, 1)).reshape(-1, 9)
-        return float(np.sum(energy_expanded(F9, self.mu, self.la) * self.vol))
+        Fv = np.transpose(F, (0, 2, 1)).reshape(-1, d * d)
+        psi = energy_expanded(Fv, self.mu, self.la) if d == 3 else energy_expanded_2d(Fv, self.mu, self.la)
+        return float(np.sum(psi * self.vol))
 
     def update(self, x, h):
+        d = self.d
+        nd = d * (d + 1)
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
         g, H = gradient_hessian(F, self.mu, self.la)
         H = simple_psd_fix(H, 0.0)
         w = self.vol * h * h
-        He = np.einsum("eia,eij,ejb->eab", self.Jloc, H, self.Jloc) * w[:, None, None]      # (nE,12,12)
-        ge = np.einsum("eia,ei->ea", self.Jloc, g) * w[:, None]                              # (nE,12)
-        dofs = (3 * self.fm[self.T][:, :, None] + np.arange(3)[None, None, :]).reshape(-1, 12)
-        free = (self.fm[self.T] >= 0)[:, :, None].repeat(3, axis=2).reshape(-1, 12)
+        He = np.einsum("eia,eij,ejb->eab", self.Jloc, H, self.Jloc) * w[:, None, None]      # (nE,nd,nd)
+        ge = np.einsum("eia,ei->ea", self.Jloc, g) * w[:, None]                              # (nE,nd)
+        dofs = (d * self.fm[self.T][:, :, None] + np.arange(d)[None, None, :]).reshape(-1, nd)
+        free = (self.fm[self.T] >= 0)[:, :, None].repeat(d, axis=2).reshape(-1, nd)
         rows = np.broadcast_to(dofs[:, :, None], He.shape)
         cols = np.broadcast_to(dofs[:, None, :], He.shape)
         keep = free[:, :, None] & free[:, None, :]
-        n = 3 * self.nF
+        n = d * self.nF
         self.lhs = sp.coo_matrix((He[keep], (rows[keep], cols[keep])), shape=(n, n)).tocsr()
         self.grad = np.bincount(dofs[free], weights=ge[free], minlength=n)
 

@@ -12,10 +12,11 @@ from tests.common import LA, MU, vec_rel
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("n,scale", [((6, 3, 3), 1.0), ((5, 4, 3), 6.0)])
+@pytest.mark.parametrize("n,scale", [((6, 3, 3), 1.0), ((5, 4, 3), 6.0), ((9, 7, 0), 1.0), ((8, 6, 0), 6.0)])
 def test_stretch_update_matches_oracle(built, n, scale):
-    """scale 6: strongly deformed state, a good part of the element Hessians is indefinite and goes through the clamp"""
-    V, T = meshgen.kuhn_grid(*n)
+    """scale 6: strongly deformed state, a good part of the element Hessians is indefinite and goes through the clamp;
+    n[2] == 0: 2D triangles (config C1's element type and material)"""
+    V, T = meshgen.kuhn_grid(*n) if n[2] else meshgen.tri_grid(n[0], n[1])
     fm = meshgen.pinned_free_map(V)
     x = meshgen.deformed_positions(V, 1.0 / n[0], scale=scale)
     h = 0.0333

@@ -47,3 +47,37 @@ def test_assembled_gradient_is_the_derivative_of_the_energy():
             fd = (st.energy(x + d) - st.energy(x - d)) / 2e-6 * h * h
             assert abs(fd - st.grad[3 * fm[v] + l]) <= 1e-5 * np.abs(st.grad).max()
     assert abs(st.lhs - st.lhs.T).max() <= 1e-10 * abs(st.lhs).max()
+
+
+def test_snh_f_form_2d_matches_the_reference_expressions():
+    """2D: closed forms against the reference's OWN expanded gradient / Hessian entries (stable_neohookean.cpp:283-321,
+    short enough to transcribe a few of) and against differences of its energy"""
+    rng = np.random.default_rng(4)
+    F = np.eye(2)[None] + 0.3 * rng.standard_normal((10, 2, 2))
+    g, H = ostretch.gradient_hessian(F, MU, LA)
+    F4 = np.transpose(F, (0, 2, 1)).reshape(-1, 4)
+    F1_1, F2_1, F1_2, F2_2 = F4.T
+    t = -F1_1 * F2_2 + F1_2 * F2_1 + 1.0
+    assert np.allclose(g[:, 0], F1_1 * MU - F2_2 * MU - F2_2 * LA * t, rtol=1e-13)
+    assert np.allclose(g[:, 1], F1_2 * MU + F2_1 * MU + F1_2 * LA * t, rtol=1e-13)
+    assert np.allclose(H[:, 0, 3], -LA - MU + F1_1 * F2_2 * LA * 2.0 - F1_2 * F2_1 * LA, rtol=1e-13)
+    assert np.allclose(H[:, 1, 2], LA + MU - F1_1 * F2_2 * LA + F1_2 * F2_1 * LA * 2.0, rtol=1e-13)
+    assert np.allclose(H[:, 2, 3], -F1_1 * F2_1 * LA, rtol=1e-13) and np.allclose(H[:, 1, 1], MU + F1_2 ** 2 * LA, rtol=1e-13)
+    eps = 1e-6
+    for i in range(4):
+        d = np.zeros(4); d[i] = eps
+        fd = (ostretch.energy_expanded_2d(F4 + d, MU, LA) - ostretch.energy_expanded_2d(F4 - d, MU, LA)) / (2 * eps)
+        assert np.allclose(fd, g[:, i], rtol=1e-6, atol=1e-6 * np.abs(g).max())
+
+
+def test_assembled_gradient_2d():
+    V, T = meshgen.tri_grid(4, 3)
+    fm = meshgen.pinned_free_map(V)
+    st = ostretch.OracleStretch(V, T, fm, MU, LA)
+    x = meshgen.deformed_positions(V, 0.25)
+    st.update(x, 0.1)
+    for v in np.nonzero(fm >= 0)[0][:5]:
+        for l in range(2):
+            d = np.zeros_like(x); d[2 * v + l] = 1e-6
+            fd = (st.energy(x + d) - st.energy(x - d)) / 2e-6 * 0.01
+            assert abs(fd - st.grad[2 * fm[v] + l]) <= 1e-5 * np.abs(st.grad).max()
