@@ -38,6 +38,9 @@ namespace mfb {
 #ifndef MFB_V4_ROLL
 #define MFB_V4_ROLL 1      // step-3 loops over vertices / block pairs stay rolled: 6984 -> 5944 SASS instructions, 5.31 -> 5.21 ms
 #endif                      // per 10M tets (straight-line code of this size pays in instruction-cache misses)
+#ifndef MFB_V4_ROLL_DSDF
+#define MFB_V4_ROLL_DSDF 0
+#endif
 constexpr int kV4Threads = MFB_V4_THREADS;
 constexpr int kV4Warps = kV4Threads / 32;
 constexpr int kV4StageDoubles = 32 * 9;                 // per warp: one 3x3 block per lane
@@ -185,10 +188,18 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   {
     double Hinv3[6];
     if (!procrustes_hinv(Y, Hinv3)) status |= ST_POLAR_HFAIL;
+#if MFB_V4_ROLL_DSDF
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
     for (int n = 0; n < 6; ++n) {
       double col[9];
+#if MFB_V4_ROLL_DSDF
+      dsdf3_column_rt(n, R, F, Hinv3, col);
+#else
       dsdf3_column(n, R, F, Hinv3, col);
+#endif
       if (!TAIL && inrange && !(m.exp & 1)) {
         const double sy = (n < 3) ? 1.0 : 2.0;
 #pragma unroll

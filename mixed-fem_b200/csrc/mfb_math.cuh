@@ -699,6 +699,34 @@ MFB_HD void dsdf3_column(int n, const double* R, const double* F, const double* 
   }
 }
 
+// Same column for a RUN-TIME n (the caller keeps its loop over n rolled: one body instead of six in the instruction
+// stream).  Columns of R and F are picked with selects; for n < 3 (i == j) the symmetrised expressions reduce to the
+// unsymmetrised ones exactly (0.5 (c + c) = c, 0.5 r + 0.5 r = r), so the result is bit-identical to dsdf3_column.
+MFB_HD void dsdf3_column_rt(int n, const double* R, const double* F, const double* Hinv3, double* col) {
+  const int i = (n < 3) ? n : (n == 5 ? 1 : 0);
+  const int j = (n < 3) ? n : (n == 3 ? 1 : 2);
+  double ri[3], rj[3], fi[3], fj[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    ri[a] = (i == 0) ? R[a] : (i == 1) ? R[3 + a] : R[6 + a];
+    rj[a] = (j == 0) ? R[a] : (j == 1) ? R[3 + a] : R[6 + a];
+    fi[a] = (i == 0) ? F[a] : (i == 1) ? F[3 + a] : F[6 + a];
+    fj[a] = (j == 0) ? F[a] : (j == 1) ? F[3 + a] : F[6 + a];
+  }
+  double c1[3], c2[3], c[3], d[3];
+  cross3(fj, ri, c1);
+  cross3(fi, rj, c2);
+  c[0] = 0.5 * (c1[0] + c2[0]); c[1] = 0.5 * (c1[1] + c2[1]); c[2] = 0.5 * (c1[2] + c2[2]);
+  symmul3(Hinv3, c, d);
+#pragma unroll
+  for (int b = 0; b < 3; ++b) {
+    double v[3];
+    cross3(&R[3 * b], d, v);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) col[3 * b + a] = (0.5 * ((b == j) ? ri[a] : 0.0) + 0.5 * ((b == i) ? rj[a] : 0.0)) + v[a];
+  }
+}
+
 // Hp^-1 from the final Y; returns false on the reference's "H FAILURE" condition (|H|_F < 1e-6)
 MFB_HD bool procrustes_hinv(const double* Y, double* Hinv3) {
   const double h00 = Y[4] + Y[8], h11 = Y[0] + Y[8], h22 = Y[0] + Y[4];
