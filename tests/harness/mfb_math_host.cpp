@@ -48,6 +48,17 @@ int hh_polar3(double* R, const double* F, double* s6, double* Js_6x9, int* statu
   for (int n = 0; n < 6; ++n) { double col[9]; dsdf3_column(n, R, F, Hinv3, col); for (int k = 0; k < 9; ++k) Js_6x9[k * 6 + n] = col[k]; }
   return it;
 }
+// number of entries where the run-time-index variant of the ds/dF column differs from the unrolled one (must be 0)
+int hh_dsdf_rt_mismatches(const double* R, const double* F, const double* Hinv3) {
+  int bad = 0;
+  for (int n = 0; n < 6; ++n) {
+    double a[9], b[9];
+    dsdf3_column(n, R, F, Hinv3, a);
+    dsdf3_column_rt(n, R, F, Hinv3, b);
+    for (int k = 0; k < 9; ++k) bad += !(a[k] == b[k]);
+  }
+  return bad;
+}
 void hh_polar2(const double* F, double* R, double* s3, double* Js_3x4) {
   double Js[3][4];
   polar2(F, R, s3, Js);

@@ -184,6 +184,15 @@ def test_device_polar3_contracted_dsdf_matches_explicit_9x9(harness):
         assert np.linalg.norm(Js.reshape(9, 6).T - Jo) <= 1e-12 * np.linalg.norm(Jo)
 
 
+def test_rolled_dsdf_column_is_bit_identical(harness):
+    """dsdf3_column_rt (run-time column index, kernel option MFB_V4_ROLL_DSDF) against the unrolled dsdf3_column"""
+    rng = np.random.default_rng(7)
+    for _ in range(200):
+        R = np.ascontiguousarray(sl.expm(np.cross(np.eye(3), rng.standard_normal(3))).T).reshape(-1)
+        F = rng.standard_normal(9); Hi = rng.standard_normal(6)
+        assert harness.hh_dsdf_rt_mismatches(P(R), P(F), P(Hi)) == 0
+
+
 def test_device_polar2_matches_dsvd_route(harness):
     rng = np.random.default_rng(3)
     for _ in range(300):
