@@ -95,6 +95,16 @@ __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double*
   double ev[M];
 #pragma unroll
   for (int k = 0; k < M; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
+  // Hfix = V max(L, 0) V^T, packed lower, back into H
+#pragma unroll
+  for (int i = 0; i < M; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) {
+      double a = 0.0;
+#pragma unroll
+      for (int q = 0; q < M; ++q) a += V[q * M + i] * V[q * M + j] * ev[q];
+      H[symidx(i, j)] = a;
+    }
   // column (k,s) of Hfix Jloc:  col[i] = sum_c2 dphi(k,c2) Hfix[i, DIM c2 + s] ;  K(j,r ; k,s) = sum_c dphi(j,c) col[DIM c + r]
   int sidx[NPE * NPE], stride[NPE];
 #pragma unroll
@@ -109,22 +119,19 @@ __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double*
     for (int k = 0; k < DIM; ++k) { d4[k + 1][c] = dphi[DIM * k + c]; sum += dphi[DIM * k + c]; }
     d4[0][c] = -sum;
   }
+#pragma unroll
   for (int k = 0; k < NPE; ++k) {
+#pragma unroll
     for (int s = 0; s < DIM; ++s) {
       double col[M];
 #pragma unroll
       for (int i = 0; i < M; ++i) {
         double a = 0.0;
 #pragma unroll
-        for (int c2 = 0; c2 < DIM; ++c2) {
-          const int jj = DIM * c2 + s;
-          double hij = 0.0;
-#pragma unroll
-          for (int q = 0; q < M; ++q) hij += V[q * M + i] * V[q * M + jj] * ev[q];
-          a += d4[k][c2] * hij;
-        }
+        for (int c2 = 0; c2 < DIM; ++c2) a += d4[k][c2] * H[symidx(i, DIM * c2 + s)];
         col[i] = a;
       }
+#pragma unroll
       for (int j = 0; j < NPE; ++j) {
         const int base = sidx[j * NPE + k];
         if (base < 0) continue;
