@@ -214,7 +214,7 @@ int mfb_dual_solve_cg(mfb_ctx* ctx, double* la, double tol, int max_iters, int* 
 
 /* ---- the non-mixed Stretch<DIM> variable (src/variables/stretch.cpp:16-91) on the same mesh, Assembler
  * pattern and scatter map: F-form material (material_model.h:43-62), H_e = Jloc^T d2psi/dF2 Jloc vol h^2 with
- * sim::simple_psd_fix(H, 0), g_e = Jloc^T dpsi/dF vol h^2.  Tetrahedra or 2D triangles with one Stable-Neohookean material
+ * sim::simple_psd_fix(H, 0), g_e = Jloc^T dpsi/dF vol h^2.  One material per mesh: Stable-Neohookean (tets, 2D triangles) or ARAP (tets; H = mu (I - dR/dF), no psd fix)
  * (MFB_ERR_UNSUPPORTED otherwise).  x: d*nV. ---- */
 int mfb_stretch_update(mfb_ctx* ctx, const double* x, double h);             /* Stretch::update, stretch.cpp:33-60 (x host) */
 int mfb_stretch_update_dev(mfb_ctx* ctx, const double* x_dev, double h);

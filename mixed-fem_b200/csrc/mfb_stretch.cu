@@ -17,7 +17,7 @@
 // which is what is evaluated here (tests/test_oracle_stretch.py checks the closed form against finite differences of
 // the energy expression of stable_neohookean.cpp:93-107).  Only Stable Neo-Hookean is implemented, for tets (config C2)
 // and 2D triangles (config C1's material; stable_neohookean.cpp:274-324 is the same closed form with a 2x2 cofactor);
-// other models return MFB_ERR_UNSUPPORTED.  This is a coverage path, not a tuned one: full (d(d+1))^2 scattered FP64
+// ARAP (tets) is further down; other models return MFB_ERR_UNSUPPORTED.  This is a coverage path, not a tuned one: full (d(d+1))^2 scattered FP64
 // reductions, the d^2 x d^2 Jacobi eigen-solve in local memory.
 #include "mfb_ctx.cuh"
 #include <cmath>
@@ -61,9 +61,75 @@ __device__ __forceinline__ double snh_J_cof(const double* F, double* C) {
   else { cofactor2(F, C); return F[0] * F[3] - F[2] * F[1]; }
 }
 
+// ARAP F-form (src/energies/arap.cpp:134-162): psi = mu/2 (|F|^2 - 2 tr S + 3), g = mu (F - R), H = mu (I - dR/dF), NO psd fix.
+// The reference takes R and dR/dF from iARAP::rotation (closed-form polar, src/svd/iARAP.cpp); the polar factor and its
+// derivative are unique functions of F, here: the Newton polar of the mixed path started from the identity and polished
+// (polar_from_identity), and  dR/dF(:, (r,c)) = [w x r_b]_b  with  w = (tr(Y) I - Y)^-1 (r_c x e_r),  Y = R F^T,  r_b = columns of R
+// (differentiate F = R S, take the skew part of dF R^T).  Returns false if the polar iteration failed.
+// Polar rotation of F from scratch: the mixed path's Newton iteration (reference tolerance 1e-6, with its back-tracking)
+// from the identity, then two undamped Newton steps (quadratic: 1e-6 -> 1e-12 -> rounding).  Running the reference
+// iteration itself to 1e-13 stalls on some elements: its back-tracking compares against -tr(R Y) (sic) and shrinks the
+// step below the tolerance.  Y = R F^T on exit.
+__device__ __forceinline__ int polar_from_identity(const double* F, double* R, double* Y) {
+  int status = 0;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R[i] = (i % 4 == 0) ? 1.0 : 0.0;
+  procrustes3(R, F, Y, 1e-6, 100, &status);
+  for (int k = 0; k < 2; ++k) {
+    const double gv[3] = {Y[5] - Y[7], Y[6] - Y[2], Y[1] - Y[3]};
+    double inv[6], w[3], dR[9], t[9];
+    syminv3(Y[4] + Y[8], -0.5 * (Y[3] + Y[1]), -0.5 * (Y[6] + Y[2]), Y[0] + Y[8], -0.5 * (Y[7] + Y[5]), Y[0] + Y[4], inv);
+    symmul3(inv, gv, w);
+    w[0] = -w[0]; w[1] = -w[1]; w[2] = -w[2];
+    // exp([w]x) to second order (|w| <= 1e-6 here: error 1e-19); rodrigues3 keeps the reference's cut-off and returns
+    // the identity below an angle of 1e-8, which would leave up to 1e-8 of rotation uncorrected
+    dR[0] = 1.0 - 0.5 * (w[1] * w[1] + w[2] * w[2]); dR[4] = 1.0 - 0.5 * (w[0] * w[0] + w[2] * w[2]); dR[8] = 1.0 - 0.5 * (w[0] * w[0] + w[1] * w[1]);
+    dR[1] = w[2] + 0.5 * w[0] * w[1];  dR[3] = -w[2] + 0.5 * w[0] * w[1];
+    dR[2] = -w[1] + 0.5 * w[0] * w[2]; dR[6] = w[1] + 0.5 * w[0] * w[2];
+    dR[5] = w[0] + 0.5 * w[1] * w[2];  dR[7] = -w[0] + 0.5 * w[1] * w[2];
+    mul33(dR, R, t);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = t[i];
+    mul33(dR, Y, t);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) Y[i] = t[i];
+  }
+  return status;
+}
+
+__device__ __forceinline__ bool arap_f_form(const double* F, double mu, double* R, double* g, double* H /* packed lower 45 */) {
+  double Y[9], Hinv3[6];
+  const int status = polar_from_identity(F, R, Y);
+  const bool ok = procrustes_hinv(Y, Hinv3) && !(status & ST_POLAR_MAXITER);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) g[i] = mu * (F[i] - R[i]);
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int jc = 3 * c + r;
+      double er[3] = {0.0, 0.0, 0.0};
+      er[r] = 1.0;
+      double a[3], w[3];
+      cross3(&R[3 * c], er, a);
+      symmul3(Hinv3, a, w);
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        double v[3];
+        cross3(w, &R[3 * b], v);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const int i = 3 * b + q;
+          if (i >= jc) H[symidx(i, jc)] = mu * ((i == jc ? 1.0 : 0.0) - v[q]);
+        }
+      }
+    }
+  return ok;
+}
+
 template <int DIM>
 __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double* __restrict__ x, double h2, double* __restrict__ Avals,
-                                                        double* __restrict__ grad) {
+                                                        double* __restrict__ grad, unsigned long long* __restrict__ counters) {
   constexpr int M = DIM * DIM, NPE = DIM + 1;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
@@ -75,36 +141,44 @@ __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double*
   const double mu = mat.mu, la = mat.la;
   const double k1 = la * (J - 1.0) - mu;
   const double scale = m.vol[e] * h2;
+  double g9[M], H[M * (M + 1) / 2];
+  bool arap = false;
+  if constexpr (DIM == 3) arap = mat.model == 4;
+  if (arap) {
+    if constexpr (DIM == 3) {
+      double R[9];
+      if (!arap_f_form(F, mu, R, g9, H)) atomicAdd(&counters[1], 1ull);     // polar_hfail
+    }
+  } else {
+    // Stable Neo-Hookean: gradient, Hessian (packed lower), then simple_psd_fix(H, 0)
+#pragma unroll
+    for (int i = 0; i < M; ++i) g9[i] = mu * F[i] + k1 * C[i];
+#pragma unroll
+    for (int i = 0; i < M; ++i)
+#pragma unroll
+      for (int j = 0; j <= i; ++j) {
+        double dd;
+        if constexpr (DIM == 3) dd = d2J(F, i % 3, i / 3, j % 3, j / 3);
+        else dd = d2J2(i % 2, i / 2, j % 2, j / 2);
+        H[symidx(i, j)] = (i == j ? mu : 0.0) + la * C[i] * C[j] + k1 * dd;
+      }
+    double V[M * M], ev[M];
+    jacobi_eig<M>(H, V);
+#pragma unroll
+    for (int k = 0; k < M; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
+    // Hfix = V max(L, 0) V^T, packed lower, back into H
+#pragma unroll
+    for (int i = 0; i < M; ++i)
+#pragma unroll
+      for (int j = 0; j <= i; ++j) {
+        double a = 0.0;
+#pragma unroll
+        for (int q = 0; q < M; ++q) a += V[q * M + i] * V[q * M + j] * ev[q];
+        H[symidx(i, j)] = a;
+      }
+  }
   // gradient: Jloc^T g
-  double g9[M];
-#pragma unroll
-  for (int i = 0; i < M; ++i) g9[i] = mu * F[i] + k1 * C[i];
   scatter_vertex<DIM>(m, e, dphi, g9, scale, grad);
-  // Hessian, packed lower, then simple_psd_fix(H, 0)
-  double H[M * (M + 1) / 2], V[M * M];
-#pragma unroll
-  for (int i = 0; i < M; ++i)
-#pragma unroll
-    for (int j = 0; j <= i; ++j) {
-      double dd;
-      if constexpr (DIM == 3) dd = d2J(F, i % 3, i / 3, j % 3, j / 3);
-      else dd = d2J2(i % 2, i / 2, j % 2, j / 2);
-      H[symidx(i, j)] = (i == j ? mu : 0.0) + la * C[i] * C[j] + k1 * dd;
-    }
-  jacobi_eig<M>(H, V);
-  double ev[M];
-#pragma unroll
-  for (int k = 0; k < M; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
-  // Hfix = V max(L, 0) V^T, packed lower, back into H
-#pragma unroll
-  for (int i = 0; i < M; ++i)
-#pragma unroll
-    for (int j = 0; j <= i; ++j) {
-      double a = 0.0;
-#pragma unroll
-      for (int q = 0; q < M; ++q) a += V[q * M + i] * V[q * M + j] * ev[q];
-      H[symidx(i, j)] = a;
-    }
   // column (k,s) of Hfix Jloc:  col[i] = sum_c2 dphi(k,c2) Hfix[i, DIM c2 + s] ;  K(j,r ; k,s) = sum_c dphi(j,c) col[DIM c + r]
   int sidx[NPE * NPE], stride[NPE];
 #pragma unroll
@@ -162,6 +236,16 @@ __global__ void __launch_bounds__(128) k_stretch_energy(DevMesh m, const double*
 #pragma unroll
     for (int i = 0; i < M; ++i) i1 += F[i] * F[i];
     val = (mat.mu * (1.0 - J) + 0.5 * mat.la * (1.0 - J) * (1.0 - J) + 0.5 * mat.mu * (i1 - (double)DIM)) * m.vol[e];
+    if constexpr (DIM == 3) {
+      if (mat.model == 4) {      // ARAP: mu/2 (|F|^2 - 2 tr S + 3), tr S = R : F   (arap.cpp:134-141)
+        double R[9], Y[9];
+        polar_from_identity(F, R, Y);
+        double trS = 0.0;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) trS += R[i] * F[i];
+        val = 0.5 * mat.mu * (i1 - 2.0 * trS + 3.0) * m.vol[e];
+      }
+    }
   }
   const double r = block_sum_128(val, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = r;
@@ -177,7 +261,9 @@ int stretch_get(mfb_ctx* c, StretchState** out) {
   if (c->matid.p) {
     g_last_error = "Stretch variable: one material per mesh"; return MFB_ERR_UNSUPPORTED;
   }
-  if (c->mat0_host.model != 0) { g_last_error = "Stretch variable: only Stable-Neohookean has an F-form on the device"; return MFB_ERR_UNSUPPORTED; }
+  if (!(c->mat0_host.model == 0 || (c->mat0_host.model == 4 && c->dim == 3))) {
+    g_last_error = "Stretch variable: F-forms on the device are Stable-Neohookean (2D, 3D) and ARAP (3D)"; return MFB_ERR_UNSUPPORTED;
+  }
   if (!c->stretch) {
     StretchState* s = new StretchState();
     c->stretch = s;
@@ -204,8 +290,9 @@ extern "C" int mfb_stretch_update_dev(mfb_ctx* c, const double* x_dev, double h)
   cudaStream_t st = c->stream;
   MFB_CUDA(cudaMemsetAsync(s->Avals.p, 0, (size_t)(c->nnz > 0 ? c->nnz : 1) * 8, st));
   MFB_CUDA(cudaMemsetAsync(s->grad.p, 0, (size_t)c->dim * c->nF * 8, st));
-  if (c->dim == 3) k_stretch_update<3><<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p);
-  else k_stretch_update<2><<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p);
+  MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
+  if (c->dim == 3) k_stretch_update<3><<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p, c->counters.p);
+  else k_stretch_update<2><<<c->grid(), 128, 0, st>>>(c->mesh(), x_dev, h * h, s->Avals.p, s->grad.p, c->counters.p);
   c->launches += 1;
   MFB_CUDA(cudaGetLastError());
   s->updated = true;

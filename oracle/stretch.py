@@ -59,6 +59,45 @@ def gradient_hessian(F, mu, la):
     return g, H
 
 
+def polar_rotation(F):
+    """R of F = R S (S symmetric, R in SO(3)): what iARAP::rotation returns (src/svd/iARAP.cpp), via numpy's SVD"""
+    U, sig, Vt = np.linalg.svd(F)
+    flip = np.linalg.det(U @ Vt) < 0
+    U = U.copy()
+    U[flip, :, -1] *= -1.0
+    return U @ Vt
+
+
+def arap_gradient_hessian(F, mu):
+    """src/energies/arap.cpp:143-162: g = mu (F - R), H = mu (I - dR/dF), NO psd fix.  dR/dF in closed form:
+    column (r,c): w = (tr(Y) I - Y)^-1 (r_c x e_r), Y = R F^T, dR(:,b) = w x r_b  (checked against finite differences
+    of polar_rotation in tests/test_oracle_stretch.py)"""
+    nE = F.shape[0]
+    R = polar_rotation(F)
+    Y = R @ np.transpose(F, (0, 2, 1))
+    Hp = np.trace(Y, axis1=1, axis2=2)[:, None, None] * np.eye(3)[None] - 0.5 * (Y + np.transpose(Y, (0, 2, 1)))
+    Hpi = np.linalg.inv(Hp)
+    dRdF = np.zeros((nE, 9, 9))
+    for c in range(3):
+        for r in range(3):
+            er = np.zeros(3); er[r] = 1.0
+            a = np.cross(R[:, :, c], er[None, :])
+            w = np.einsum("eij,ej->ei", Hpi, a)
+            for b in range(3):
+                dRdF[:, 3 * b:3 * b + 3, 3 * c + r] = np.cross(w, R[:, :, b])
+    vec = lambda A: np.transpose(A, (0, 2, 1)).reshape(nE, 9)
+    g = mu * (vec(F) - vec(R))
+    H = mu * (np.eye(9)[None] - dRdF)
+    return g, H, R
+
+
+def arap_energy(F, mu):
+    """arap.cpp:134-141: mu/2 (|F|^2 - 2 tr S + 3)"""
+    R = polar_rotation(F)
+    trS = np.einsum("eij,eij->e", R, F)
+    return 0.5 * mu * (np.einsum("eij,eij->e", F, F) - 2.0 * trS + 3.0)
+
+
 def simple_psd_fix(H, tol=0.0):
     w, V = np.linalg.eigh(H)
     w = np.where(w < tol, tol, w)
@@ -66,9 +105,9 @@ def simple_psd_fix(H, tol=0.0):
 
 
 class OracleStretch:
-    def __init__(self, V, T, free_map, mu, la):
+    def __init__(self, V, T, free_map, mu, la, model="Stable-Neohookean"):
         self.V, self.T, self.fm = np.asarray(V, float), np.asarray(T), np.asarray(free_map)
-        self.mu, self.la = mu, la
+        self.mu, self.la, self.model = mu, la, model
         self.d = d = self.V.shape[1]
         X = self.V[self.T]
         Dm = np.transpose(X[:, 1:, :] - X[:, :1, :], (0, 2, 1))
@@ -85,6 +124,8 @@ class OracleStretch:
         d = self.d
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
         Fv = np.transpose(F, (0, 2, 1)).reshape(-1, d * d)
+        if self.model == "ARAP":
+            return float(np.sum(arap_energy(F, self.mu) * self.vol))
         psi = energy_expanded(Fv, self.mu, self.la) if d == 3 else energy_expanded_2d(Fv, self.mu, self.la)
         return float(np.sum(psi * self.vol))
 
@@ -92,8 +133,11 @@ class OracleStretch:
         d = self.d
         nd = d * (d + 1)
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
-        g, H = gradient_hessian(F, self.mu, self.la)
-        H = simple_psd_fix(H, 0.0)
+        if self.model == "ARAP":
+            g, H, _ = arap_gradient_hessian(F, self.mu)
+        else:
+            g, H = gradient_hessian(F, self.mu, self.la)
+            H = simple_psd_fix(H, 0.0)
         w = self.vol * h * h
         He = np.einsum("eia,eij,ejb->eab", self.Jloc, H, self.Jloc) * w[:, None, None]      # (nE,nd,nd)
         ge = np.einsum("eia,ei->ea", self.Jloc, g) * w[:, None]                              # (nE,nd)

@@ -36,10 +36,29 @@ def test_stretch_update_matches_oracle(built, n, scale):
     gpu.close()
 
 
+def test_stretch_arap_f_form_matches_oracle(built):
+    """ARAP F-form (arap.cpp:134-162): polar rotation and dR/dF, no psd fix"""
+    V, T = meshgen.kuhn_grid(5, 3, 3)
+    fm = meshgen.pinned_free_map(V)
+    x = meshgen.deformed_positions(V, 0.2, scale=3.0)
+    h = 0.0333
+    gpu = mf.MixedStretch(V, T, fm, [("ARAP", MU, LA)])
+    cpu = ostretch.OracleStretch(V, T, fm, MU, LA, model="ARAP")
+    cpu.update(x, h)
+    gpu.stretch_update(x, h)
+    outer, inner, vals = gpu.stretch_lhs()
+    A = sp.csr_matrix((vals, inner, outer), shape=cpu.lhs.shape)
+    assert abs(A - cpu.lhs).max() <= 1e-10 * abs(cpu.lhs).max()
+    assert vec_rel(gpu.stretch_gradient(), cpu.grad) <= 1e-10
+    assert abs(gpu.stretch_energy(x) - cpu.energy(x)) <= 1e-10 * abs(cpu.energy(x))
+    assert gpu.status()["polar_hfail"] == 0
+    gpu.close()
+
+
 def test_stretch_rejects_what_it_does_not_implement(built):
     V, T = meshgen.kuhn_grid(2, 2, 2)
     fm = meshgen.pinned_free_map(V)
-    gpu = mf.MixedStretch(V, T, fm, [("ARAP", MU, LA)])
+    gpu = mf.MixedStretch(V, T, fm, [("Corot", MU, LA)])
     with pytest.raises(mf.MfbError):
         gpu.stretch_update(V.reshape(-1), 0.1)
     gpu.close()

@@ -81,3 +81,22 @@ def test_assembled_gradient_2d():
             d = np.zeros_like(x); d[2 * v + l] = 1e-6
             fd = (st.energy(x + d) - st.energy(x - d)) / 2e-6 * 0.01
             assert abs(fd - st.grad[2 * fm[v] + l]) <= 1e-5 * np.abs(st.grad).max()
+
+
+def test_arap_f_form_closed_dRdF_matches_finite_differences():
+    rng = np.random.default_rng(5)
+    import scipy.linalg as sl
+    F = np.stack([sl.expm(np.cross(np.eye(3), rng.standard_normal(3) * 0.7)) @ (np.diag([1.2, 0.9, 1.05]) + 0.15 * rng.standard_normal((3, 3)))
+                  for _ in range(12)])
+    g, H, R = ostretch.arap_gradient_hessian(F, MU)
+    assert np.abs(R - np.stack([sl.polar(f)[0] for f in F])).max() <= 1e-12
+    assert np.abs(H - np.transpose(H, (0, 2, 1))).max() <= 1e-9 * MU
+    F9 = np.transpose(F, (0, 2, 1)).reshape(-1, 9)
+    eps = 1e-6
+    for i in range(9):
+        d = np.zeros(9); d[i] = eps
+        Fp = np.transpose((F9 + d).reshape(-1, 3, 3), (0, 2, 1)); Fm = np.transpose((F9 - d).reshape(-1, 3, 3), (0, 2, 1))
+        fd_e = (ostretch.arap_energy(Fp, MU) - ostretch.arap_energy(Fm, MU)) / (2 * eps)
+        assert np.allclose(fd_e, g[:, i], rtol=1e-6, atol=1e-7 * MU)
+        gp, _, _ = ostretch.arap_gradient_hessian(Fp, MU); gm, _, _ = ostretch.arap_gradient_hessian(Fm, MU)
+        assert np.allclose((gp - gm) / (2 * eps), H[:, :, i], rtol=1e-5, atol=1e-7 * MU)
