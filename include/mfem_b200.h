@@ -36,6 +36,7 @@ enum mfb_elem { MFB_TET = 0, MFB_TRI2D = 1, MFB_SHELL = 2 };   /* TetrahedralMes
 typedef struct {          /* src/config.h:143-151 MaterialConfig (the fields the path reads) */
   int32_t model;
   double mu, la;
+  double density;         /* MaterialConfig::density (config.h:149); <= 0 means the default 1000.  Read by mfb_newton_init only */
 } mfb_material;
 
 typedef struct {          /* what MixedStretch pulls from Mesh: src/mesh/mesh.h:82-105,151-171 */
@@ -173,10 +174,17 @@ typedef struct mfb_newton_log {   /* the OptimizerData columns of newton_optimiz
   double cg_error[MFB_NEWTON_LOG_MAX];
   int32_t cg_iters[MFB_NEWTON_LOG_MAX], ls_iters[MFB_NEWTON_LOG_MAX];
 } mfb_newton_log;
-/* Displacement::reset + BDF1 state: free_map as given to mfb_create; density = MaterialConfig::density; h = SimConfig::h;
- * force = body force d-vector (NULL: gravity (0,-9.8,0)); x0 / v0 host d*nV or NULL (vec(Vref^T), zero).  Also builds
- * PMP^T on the Assembler pattern. */
+/* Displacement::reset + BDF1 state: free_map as given to mfb_create; h = SimConfig::h; force = body force d-vector
+ * (NULL: gravity (0,-9.8,0)); x0 / v0 host d*nV or NULL (vec(Vref^T), zero).  Also builds PMP^T on the Assembler pattern.
+ * density > 0: one MaterialConfig::density for the whole mesh; density <= 0: every element takes the density of ITS
+ * material (mfb_material::density through mat_id).
+ * mfb_newton_init_density: one density per ELEMENT (host, nE).  This is what reproduces a multi-object scene exactly:
+ * the reference scales each object's mass matrix by the density of the material the OBJECT was created with
+ * (src/mesh/tet_mesh.cpp:36-40, tri2d_mesh.cpp:36-41, tri_mesh.cpp:67-68; block-diagonal over objects, meshes.cpp:100-108),
+ * which for an object with a per-tet material_ids file is materials[0] (mesh.cpp:14-19), not the per-tet material. */
 int mfb_newton_init(mfb_ctx* ctx, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0);
+int mfb_newton_init_density(mfb_ctx* ctx, const int32_t* free_map, const double* density_e, double h, const double* force, const double* x0,
+                            const double* v0);
 int mfb_newton_step(mfb_ctx* ctx, const mfb_newton_opts* opts, mfb_newton_log* log);   /* one time step = NewtonOptimizer::step() */
 int mfb_newton_positions(mfb_ctx* ctx, double* x_full);                                 /* host d*nV */
 int mfb_newton_positions_dev(mfb_ctx* ctx, double** x_full_dev, const double** mass_values_dev);

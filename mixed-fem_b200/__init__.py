@@ -29,7 +29,7 @@ EXPORTS = [
     "mfb_constraint_value_dev", "mfb_evaluate_constraint", "mfb_lhs_values", "mfb_lhs_values_dev", "mfb_product",
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
     "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
-    "mfb_newton_init", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
+    "mfb_newton_init", "mfb_newton_init_density", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
     "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo", "mfb_lhs_bsr",
     "mfb_kkt_size", "mfb_kkt_product", "mfb_kkt_rhs", "mfb_kkt_layout_dev", "mfb_kkt_product_dev", "mfb_kkt_solve_minres",
     "mfb_dual_product", "mfb_dual_product_dev", "mfb_dual_rhs", "mfb_dual_solve_cg",
@@ -43,7 +43,7 @@ class MfbError(RuntimeError):
 
 
 class _Material(C.Structure):
-    _fields_ = [("model", C.c_int32), ("mu", C.c_double), ("la", C.c_double)]
+    _fields_ = [("model", C.c_int32), ("mu", C.c_double), ("la", C.c_double), ("density", C.c_double)]
 
 
 class _MeshDesc(C.Structure):
@@ -147,6 +147,7 @@ def lib():
     L.mfb_set_option.argtypes = [vp, C.c_char_p, C.c_int]
     L.mfb_kernel_time_ms.argtypes = [vp, dp, ip]
     L.mfb_newton_init.argtypes = [vp, ip, C.c_double, C.c_double, dp, dp, dp]
+    L.mfb_newton_init_density.argtypes = [vp, ip, dp, C.c_double, dp, dp, dp]
     L.mfb_newton_step.argtypes = [vp, C.POINTER(_NewtonOpts), C.POINTER(_NewtonLog)]
     L.mfb_newton_positions.argtypes = [vp, dp]
     L.mfb_newton_positions_dev.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
@@ -189,7 +190,7 @@ def _f64(a):
 class MixedStretch:
     """Host-side mirror of mfem::MixedStretch<DIM> over the C ABI (same method names and argument meaning).
 
-    materials: list of (model_name, mu, la); mat_id: per-element index or None.
+    materials: list of (model_name, mu, la[, density]); mat_id: per-element index or None.
     """
 
     name = "mixed-stretch"   # src/variables/mixed_stretch.h:21-23
@@ -205,9 +206,11 @@ class MixedStretch:
         self.N = 6 if self.dim == 3 else 3
         self.M = self.dim * self.dim
         mats = (_Material * len(materials))()
-        for i, (model, mu, la) in enumerate(materials):
+        for i, m in enumerate(materials):           # (model, mu, la) or (model, mu, la, density)
+            model, mu, la = m[0], m[1], m[2]
             mats[i].model = MODELS[model] if isinstance(model, str) else int(model)
             mats[i].mu, mats[i].la = float(mu), float(la)
+            mats[i].density = float(m[3]) if len(m) > 3 else 1000.0
         mid = None if mat_id is None else np.ascontiguousarray(mat_id, dtype=np.int32)
         d = _MeshDesc()
         self.shell = normals is not None
@@ -229,12 +232,20 @@ class MixedStretch:
 
     # ---- device-resident Newton time step (NewtonOptimizer<DIM>::step, newton_optimizer.cpp:14-139) ----
     def newton_init(self, density=1000.0, h=0.0333, force=None, x0=None, v0=None):
-        """Displacement::reset + BDF1 + mass matrix (displacement.cpp:73-93); force = body-force d-vector (default gravity)."""
+        """Displacement::reset + BDF1 + mass matrix (displacement.cpp:73-93); force = body-force d-vector (default gravity).
+        density: a scalar, None (each element takes its material's density) or one value per element (the density of the
+        element's OBJECT in a multi-object scene, sceneio.Scene.density_e)."""
         f = None if force is None else _f64(force)
         x0 = None if x0 is None else _f64(x0)
         v0 = None if v0 is None else _f64(v0)
-        self._check(self.L.mfb_newton_init(self.h, _ip(self._free_map), float(density), float(h), _dp(f) if f is not None else None,
-                                           _dp(x0) if x0 is not None else None, _dp(v0) if v0 is not None else None))
+        tail = (float(h), _dp(f) if f is not None else None, _dp(x0) if x0 is not None else None, _dp(v0) if v0 is not None else None)
+        if density is not None and np.ndim(density) > 0:
+            rho = _f64(density)
+            if rho.size != self.nE:
+                raise MfbError("density: expected one value per element")
+            self._check(self.L.mfb_newton_init_density(self.h, _ip(self._free_map), _dp(rho), *tail))
+        else:
+            self._check(self.L.mfb_newton_init(self.h, _ip(self._free_map), 0.0 if density is None else float(density), *tail))
 
     def newton_step(self, outer_steps=5, ls_iters=20, newton_tol=1e-10, precond=1, cg_tol=1e-4, cg_max_iters=500):
         """One time step; returns the per-iteration columns the reference prints (newton_optimizer.cpp:92-97)."""

@@ -48,7 +48,8 @@ int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop);
 void comm_free(mfb_ctx* c);
 // mfb_newton.cu: what the saddle-point systems (mfb_saddle.cu) read from the Displacement / BDF1 state
 struct NewtonView {
-  double density, h, f[3];
+  double h, f[3];
+  const double* emass;    // per element: density x vol
   double *Mvals, *x, *xt, *diff, *dx;
   int* vfree;
 };
@@ -96,6 +97,8 @@ struct mfb_ctx {
   double* h_scal = nullptr;   // pinned
   // host copies (lazy)
   std::vector<int32_t> h_outer, h_inner, h_smap, h_sstride;
+  std::vector<int32_t> h_matid;          // kept for mfb_newton_init's per-material densities
+  std::vector<double> h_mat_density;
   // flags
   bool rhs_valid = false;     // rhs_/gl_ match the current S_, s_, g_, H_, dSdF_
   bool updated = false;

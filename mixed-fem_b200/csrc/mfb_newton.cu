@@ -28,12 +28,12 @@ template <int K> struct MassCoef { static constexpr double c0 = Dims<K>::NPE == 
 
 // PMP^T on the Assembler pattern: only the d diagonal entries of each d x d block are non-zero
 template <int K>
-__global__ void __launch_bounds__(128) k_mass_values(DevMesh m, double density, double* __restrict__ Mvals) {
+__global__ void __launch_bounds__(128) k_mass_values(DevMesh m, const double* __restrict__ emass, double* __restrict__ Mvals) {
   constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
-  const double mass = density * m.vol[e];
+  const double mass = emass[e];           // density of the element's object x vol (tet_mesh.cpp:36-40, meshes.cpp:100-108)
 #pragma unroll
   for (int j = 0; j < NPE; ++j) {
     const int stride = m.sstride[j * ld + e];
@@ -59,12 +59,12 @@ __global__ void k_inertia_diff(const double* __restrict__ x, const double* __res
 
 // out(free rows) += sign * PM diff : element-wise product with the consistent mass blocks, all columns (pinned included)
 template <int K>
-__global__ void __launch_bounds__(128) k_mass_rows_apply(DevMesh m, double density, const double* __restrict__ diff, double sign, double* __restrict__ out) {
+__global__ void __launch_bounds__(128) k_mass_rows_apply(DevMesh m, const double* __restrict__ emass, const double* __restrict__ diff, double sign, double* __restrict__ out) {
   constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
-  const double mass = sign * density * m.vol[e];
+  const double mass = sign * emass[e];
   double d[NPE][DIM], sum[DIM];
 #pragma unroll
   for (int l = 0; l < DIM; ++l) sum[l] = 0.0;
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(128) k_mass_rows_apply(DevMesh m, double densi
 
 // 0.5 diff^T M diff with the FULL mass matrix (displacement.cpp:21-33), per-block partial sums
 template <int K>
-__global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, double density, const double* __restrict__ diff, double* __restrict__ partials) {
+__global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, const double* __restrict__ emass, const double* __restrict__ diff, double* __restrict__ partials) {
   constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   __shared__ double sh[4];
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, double densit
 #pragma unroll
     for (int l = 0; l < DIM; ++l) ss += sum[l] * sum[l];
     // sum_jk m_jk d_j.d_k = c1 |sum_j d_j|^2 + (c0 - c1) sum_j |d_j|^2
-    val = 0.5 * density * m.vol[e] * (MassCoef<K>::c1 * ss + (MassCoef<K>::c0 - MassCoef<K>::c1) * sq);
+    val = 0.5 * emass[e] * (MassCoef<K>::c1 * ss + (MassCoef<K>::c0 - MassCoef<K>::c1) * sq);
   }
   const double r = block_sum_128(val, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = r;
@@ -190,7 +190,8 @@ int sum_partials(mfb_ctx* c, int n, double* out) {
 }  // namespace
 
 struct mfb_newton_state {
-  double density = 1000.0, h = 0.0333, f[3] = {0, -9.8, 0};
+  double h = 0.0333, f[3] = {0, -9.8, 0};
+  DBuf<double> emass;       // per element: density of its object x vol
   DBuf<double> Mvals, x, xprev, vprev, xt, diff, xtrial, strial, dx, b;
   DBuf<int> vfree;
   bool ready = false;
@@ -201,7 +202,7 @@ static mfb_newton_state* nstate(mfb_ctx* c) { return (mfb_newton_state*)c->newto
 int mfb::newton_view(mfb_ctx* c, NewtonView* v) {
   mfb_newton_state* s = nstate(c);
   if (!s || !s->ready) { g_last_error = "call mfb_newton_init first"; return MFB_ERR_INVALID; }
-  v->density = s->density; v->h = s->h;
+  v->emass = s->emass.p; v->h = s->h;
   for (int l = 0; l < 3; ++l) v->f[l] = s->f[l];
   v->Mvals = s->Mvals.p; v->x = s->x.p; v->xt = s->xt.p; v->diff = s->diff.p; v->dx = s->dx.p; v->vfree = s->vfree.p;
   return MFB_OK;
@@ -217,31 +218,67 @@ int mfb::newton_disp_gradient(mfb_ctx* c, double* out) {
   MFB_CUDA(cudaMemsetAsync(out, 0, (size_t)c->dim * c->nF * 8, st));
   if (c->dim == 3) {
     k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], c->nV, s->diff.p);
-    if (c->kind == MFB_SHELL) k_mass_rows_apply<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, 1.0, out);
-    else k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, 1.0, out);
+    if (c->kind == MFB_SHELL) k_mass_rows_apply<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, 1.0, out);
+    else k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, 1.0, out);
   } else {
     k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, c->nV, s->diff.p);
-    k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, 1.0, out);
+    k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, 1.0, out);
   }
   c->launches += 2;
   return MFB_OK;
 }
 
+// per-element densities -> emass = rho_e * vol_e
+__global__ void k_emass(const double* __restrict__ rho, double rho_uniform, const double* __restrict__ vol, int nE, double* __restrict__ emass) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < nE) emass[e] = (rho ? rho[e] : rho_uniform) * vol[e];
+}
+
+static int newton_init_impl(mfb_ctx* c, const int32_t* free_map, double density, const double* density_e, double h, const double* force,
+                            const double* x0, const double* v0);
+
 extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double density, double h, const double* force, const double* x0, const double* v0) {
   CHECK_CTX(c);
-  if (!free_map || !(h > 0) || !(density > 0)) { g_last_error = "mfb_newton_init: bad arguments"; return MFB_ERR_INVALID; }
+  if (!(density > 0)) {      // the per-material densities given to mfb_create (MaterialConfig::density)
+    std::vector<double> rho((size_t)c->nE);
+    for (int e = 0; e < c->nE; ++e) rho[e] = c->h_mat_density.empty() ? 1000.0 : c->h_mat_density[c->h_matid.empty() ? 0 : c->h_matid[e]];
+    return newton_init_impl(c, free_map, 0.0, rho.data(), h, force, x0, v0);
+  }
+  return newton_init_impl(c, free_map, density, nullptr, h, force, x0, v0);
+}
+extern "C" int mfb_newton_init_density(mfb_ctx* c, const int32_t* free_map, const double* density_e, double h, const double* force, const double* x0,
+                                       const double* v0) {
+  CHECK_CTX(c);
+  if (!density_e) { g_last_error = "mfb_newton_init_density: density_e is NULL"; return MFB_ERR_INVALID; }
+  for (int e = 0; e < c->nE; ++e)
+    if (!(density_e[e] > 0)) { g_last_error = "mfb_newton_init_density: densities must be positive"; return MFB_ERR_INVALID; }
+  return newton_init_impl(c, free_map, 0.0, density_e, h, force, x0, v0);
+}
+
+static int newton_init_impl(mfb_ctx* c, const int32_t* free_map, double density, const double* density_e, double h, const double* force,
+                            const double* x0, const double* v0) {
+  if (!free_map || !(h > 0) || (!density_e && !(density > 0))) { g_last_error = "mfb_newton_init: bad arguments"; return MFB_ERR_INVALID; }
   if (c->newton) { delete nstate(c); c->newton = nullptr; }
   mfb_newton_state* s = new mfb_newton_state();
   c->newton = s;
-  s->density = density; s->h = h;
+  s->h = h;
   for (int l = 0; l < 3; ++l) s->f[l] = force ? (l < c->dim ? force[l] : 0.0) : (l == 1 ? -9.8 : 0.0);
   const size_t nx = (size_t)c->dim * c->nV, nf = (size_t)c->dim * c->nF + 1;
   int rc;
   if ((rc = s->Mvals.alloc(c->nnz > 0 ? c->nnz : 1)) || (rc = s->x.alloc(nx)) || (rc = s->xprev.alloc(nx)) || (rc = s->vprev.alloc(nx)) ||
       (rc = s->xt.alloc(nx)) || (rc = s->diff.alloc(nx)) || (rc = s->xtrial.alloc(nx)) || (rc = s->strial.alloc((size_t)c->N * c->ld)) ||
-      (rc = s->dx.alloc(nf)) || (rc = s->b.alloc(nf)) || (rc = s->vfree.alloc(c->nV)))
+      (rc = s->dx.alloc(nf)) || (rc = s->b.alloc(nf)) || (rc = s->vfree.alloc(c->nV)) || (rc = s->emass.alloc((size_t)c->nE + 1)))
     return rc;
   cudaStream_t st = c->stream;
+  {
+    DBuf<double> rho;
+    if (density_e) {
+      if ((rc = rho.alloc((size_t)c->nE))) return rc;
+      MFB_CUDA(cudaMemcpyAsync(rho.p, density_e, (size_t)c->nE * 8, cudaMemcpyHostToDevice, st));
+    }
+    k_emass<<<nblk(c->nE), 256, 0, st>>>(rho.p, density, c->vol.p, c->nE, s->emass.p);
+    MFB_CUDA(cudaStreamSynchronize(st));
+  }
   MFB_CUDA(cudaMemcpyAsync(s->vfree.p, free_map, (size_t)c->nV * 4, cudaMemcpyHostToDevice, st));
   // Displacement::reset (displacement.cpp:73-93): x = vec(V^T), v0 from the mesh (zero unless given)
   if (x0) MFB_CUDA(cudaMemcpyAsync(s->x.p, x0, nx * 8, cudaMemcpyHostToDevice, st));
@@ -252,9 +289,9 @@ extern "C" int mfb_newton_init(mfb_ctx* c, const int32_t* free_map, double densi
   // x_tilde = x_prev + h v_prev
   k_axpy_out<<<nblk((int64_t)nx), 256, 0, st>>>(s->xprev.p, s->vprev.p, h, (int64_t)nx, s->xt.p);
   MFB_CUDA(cudaMemsetAsync(s->Mvals.p, 0, (size_t)(c->nnz > 0 ? c->nnz : 1) * 8, st));
-  if (c->kind == MFB_SHELL) k_mass_values<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
-  else if (c->dim == 3) k_mass_values<3><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
-  else k_mass_values<2><<<c->grid(), 128, 0, st>>>(c->mesh(), density, s->Mvals.p);
+  if (c->kind == MFB_SHELL) k_mass_values<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->Mvals.p);
+  else if (c->dim == 3) k_mass_values<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->Mvals.p);
+  else k_mass_values<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->Mvals.p);
   c->launches += 2;
   MFB_CUDA(cudaStreamSynchronize(st));
   MFB_CUDA(cudaGetLastError());
@@ -272,9 +309,9 @@ static int trial_energy(mfb_ctx* c, mfb_newton_state* s, double a, double* out) 
   else k_unproject_axpy<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, a, nV, s->xtrial.p);
   if (dim == 3) k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->xtrial.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
   else k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->xtrial.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);
-  if (c->kind == MFB_SHELL) k_inertia_energy<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
-  else if (dim == 3) k_inertia_energy<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
-  else k_inertia_energy<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, c->partials.p);
+  if (c->kind == MFB_SHELL) k_inertia_energy<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, c->partials.p);
+  else if (dim == 3) k_inertia_energy<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, c->partials.p);
+  else k_inertia_energy<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, c->partials.p);
   c->launches += 3;
   double e_x = 0, e_s = 0, e_c = 0;
   int rc = sum_partials(c, c->grid(), &e_x);
@@ -308,12 +345,12 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
     MFB_CUDA(cudaMemcpyAsync(s->b.p, rhs_mixed, (size_t)nf * 8, cudaMemcpyDeviceToDevice, st));
     if (dim == 3) {
       k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
-      if (c->kind == MFB_SHELL) k_mass_rows_apply<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
-      else k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
+      if (c->kind == MFB_SHELL) k_mass_rows_apply<K_SHELL><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, -1.0, s->b.p);
+      else k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, -1.0, s->b.p);
       k_guess<3><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
     } else {
       k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);
-      k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->density, s->diff.p, -1.0, s->b.p);
+      k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, -1.0, s->b.p);
       k_guess<2><<<nblk(nx), 256, 0, st>>>(s->diff.p, s->vfree.p, nV, s->dx.p);
     }
     c->launches += 3;

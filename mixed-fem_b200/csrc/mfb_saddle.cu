@@ -44,12 +44,12 @@ template <int K> struct MassC { static constexpr double c0 = Dims<K>::NPE == 4 ?
 
 // out(free) += PMP^T v(free): element mass blocks mass*(c0 | c1) I_d applied to the free vertices of each element
 template <int K>
-__global__ void __launch_bounds__(128) k_mass_free_apply(DevMesh m, double density, const double* __restrict__ v, double* __restrict__ out) {
+__global__ void __launch_bounds__(128) k_mass_free_apply(DevMesh m, const double* __restrict__ emass, const double* __restrict__ v, double* __restrict__ out) {
   constexpr int DIM = Dims<K>::SD, NPE = Dims<K>::NPE;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m.nE) return;
   const int64_t ld = m.ld;
-  const double mass = density * m.vol[e];
+  const double mass = emass[e];
   double d[NPE][DIM], sum[DIM];
   int f[NPE];
 #pragma unroll
@@ -287,7 +287,7 @@ int ensure_lumped(mfb_ctx* c, Saddle* s, const NewtonView& nv) {
   const int64_t nf = (int64_t)c->dim * c->nF;
   k_fill<<<nblk(nf), 256, 0, c->stream>>>(s->wvec.p, 1.0, nf);
   MFB_CUDA(cudaMemsetAsync(s->Mlinv.p, 0, (size_t)nf * 8, c->stream));
-  KDISPATCH(c, k_mass_free_apply, c->mesh(), nv.density, s->wvec.p, s->Mlinv.p);
+  KDISPATCH(c, k_mass_free_apply, c->mesh(), nv.emass, s->wvec.p, s->Mlinv.p);
   k_vec_inv<<<nblk(nf), 256, 0, c->stream>>>(s->Mlinv.p, nf);
   c->launches += 2;
   s->lumped = true;
@@ -297,7 +297,7 @@ int ensure_lumped(mfb_ctx* c, Saddle* s, const NewtonView& nv) {
 int kkt_apply(mfb_ctx* c, Saddle* s, const NewtonView& nv, const double* v, double* out) {
   const int64_t nf = (int64_t)c->dim * c->nF;
   MFB_CUDA(cudaMemsetAsync(out, 0, (size_t)s->nk * 8, c->stream));     // x part accumulates; the padding of ld must stay 0 (dot products)
-  KDISPATCH(c, k_mass_free_apply, c->mesh(), nv.density, v + s->ox, out + s->ox);
+  KDISPATCH(c, k_mass_free_apply, c->mesh(), nv.emass, v + s->ox, out + s->ox);
   KDISPATCH(c, k_kkt_elem, c->mesh(), c->state(), v + s->ox, v + s->os, v + s->ola, out + s->ox, out + s->os, out + s->ola);
   (void)nf;
   return MFB_OK;

@@ -24,7 +24,10 @@ from oracle import pcg as opcg
 
 
 def mass_matrix(V, T, vols, density):
-    """d*nV square consistent mass matrix: element blocks mass*(c0 on the diagonal, c1 off it) (x) I_d."""
+    """d*nV square consistent mass matrix: element blocks mass*(c0 on the diagonal, c1 off it) (x) I_d.
+    density: scalar or one value per element = the density of the element's OBJECT (each object's matrix is scaled by its own
+    material, tet_mesh.cpp:36-40 / tri2d_mesh.cpp:36-41 / tri_mesh.cpp:67-68, and Meshes stacks them block-diagonally,
+    meshes.cpp:100-108)."""
     nV, d = V.shape
     npe = T.shape[1]
     # tets 1/10, 1/20 ; triangles (2D and shells: TriMesh::mass_matrix, src/mesh/tri_mesh.cpp:43-69) 1/6, 1/12
