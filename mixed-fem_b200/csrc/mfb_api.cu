@@ -1,5 +1,6 @@
 // C ABI entry points of the mixed-stretch path (see include/mfem_b200.h for the reference interface each replaces).
 #include "mfb_ctx.cuh"
+#include <cstdlib>
 #include "mfb_kernels3.cuh"
 #include <cstring>
 
@@ -134,8 +135,12 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   }
   if (v4) {
     const DevAsm a = c->asmdesc();
-    const int smem = kV4SmemB + kV4SmemStage;
-    static bool attr4_done = false;
+    static const int extra_smem = getenv("MFB_V4_EXTRA_SMEM") ? atoi(getenv("MFB_V4_EXTRA_SMEM")) : 0;   // occupancy experiments
+    const int smem = kV4SmemB + kV4SmemStage + extra_smem;
+    // cudaFuncSetAttribute applies to the CURRENT device: one flag per device ordinal (a second context on another GPU
+    // of the same process needs its own opt-in)
+    static bool attr4_done_dev[64] = {false};
+    bool& attr4_done = attr4_done_dev[c->device & 63];
     if (!attr4_done) {
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -195,7 +200,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     else k_update_shell<false><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   } else if (c->dim == 3) {
     if (c->smem_b == 2) {
-      static bool attr2_done = false;
+      static bool attr2_done_dev[64] = {false};
+      bool& attr2_done = attr2_done_dev[c->device & 63];
       if (!attr2_done) {
         MFB_CUDA(cudaFuncSetAttribute(k_update_tet_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
         MFB_CUDA(cudaFuncSetAttribute(k_update_tet_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
@@ -206,7 +212,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     } else if (c->smem_b) {
       k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
       LAUNCHED(c, 1);
-      static bool attr_done = false;
+      static bool attr_done_dev[64] = {false};
+      bool& attr_done = attr_done_dev[c->device & 63];
       if (!attr_done) {
         MFB_CUDA(cudaFuncSetAttribute(k_update_tet_sm<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
         MFB_CUDA(cudaFuncSetAttribute(k_update_tet_sm<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));

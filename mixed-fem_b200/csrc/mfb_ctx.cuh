@@ -149,6 +149,7 @@ struct mfb_ctx {
   mfb::DevAsm asmdesc() const {
     mfb::DevAsm a;
     a.Ablk = Ablk.p; a.gxrh = gxrh.p; a.bmap = bmap.p; a.slow_list = slow_list.p;
+    a.sinkA = nbu * 9; a.sinkV = 6 * nF;
     return a;
   }
   int grid() const { return (nE + 127) / 128; }

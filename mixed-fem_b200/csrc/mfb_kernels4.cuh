@@ -33,8 +33,8 @@ namespace mfb {
 #define MFB_V4_THREADS 128
 #endif
 #ifndef MFB_V4_MINB
-#define MFB_V4_MINB 3      // CTAs per SM: 168 registers and the 54-double shared-memory column per thread both allow 3 x 128 threads
-#endif
+#define MFB_V4_MINB 2      // CTAs per SM.  2 x 128 threads at 231 registers, no spills: 4.17 ms per 10M tets; 3 x 128 at 168 registers with
+#endif                     // 96 B of spills: 4.36 ms (round 2, after the late loads moved to cp.async; round 1 measured them equal)
 #ifndef MFB_V4_ROLL
 #define MFB_V4_ROLL 1      // step-3 loops over vertices / block pairs stay rolled: 6984 -> 5944 SASS instructions, 5.31 -> 5.21 ms
 #endif                      // per 10M tets (straight-line code of this size pays in instruction-cache misses)
@@ -43,7 +43,12 @@ namespace mfb {
 #endif
 constexpr int kV4Threads = MFB_V4_THREADS;
 constexpr int kV4Warps = kV4Threads / 32;
-constexpr int kV4StageDoubles = 32 * 9;                 // per warp: one 3x3 block per lane
+// per warp: [0,288) reduction staging (one 3x3 block per lane; la[6][32] parks here until step 3),
+// [288,384) the 6 element->block codes per lane (int[6][32]), [384,448) fidx of the 4 local vertices (int[4][32]).
+// Codes and fidx stay in shared memory for the whole kernel: no registers, no spills, and their global loads are
+// cp.async issued at the top (ncu r1k: the late fidx loads + their spill stores were 10 % of all stall samples).
+constexpr int kV4RedDoubles = 32 * 9;
+constexpr int kV4StageDoubles = kV4RedDoubles + 96 + 64;
 constexpr int kV4SmemB = 54 * kV4Threads * (int)sizeof(double);
 constexpr int kV4SmemStage = kV4Warps * (kV4StageDoubles * (int)sizeof(double) + 32 * (int)sizeof(int));
 
@@ -52,6 +57,7 @@ struct DevAsm {
   double* gxrh;          // [nF][6]   grad_x | rhs interleaved
   const int* bmap;       // [6][ld]   pairs j < k: 2*upper_block + transposed; one vertex pinned: the free vertex's diagonal slot; both: -1
   int* slow_list;        // [nE]
+  int sinkA, sinkV;      // first of 32 scratch doubles behind Ablk / gxrh (reductions without a target land there)
 };
 
 __device__ __forceinline__ void cp_async8(void* sdst, const void* gsrc) {
@@ -73,24 +79,40 @@ __device__ __forceinline__ void red_add_if(double* base, int idx, double val, in
       ::"l"(base), "d"(val), "r"(idx), "r"(guard));
 }
 
+__device__ __forceinline__ void red_add_idx(double* base, int idx, double val) {
+  asm volatile(
+      "{\n\t.reg .u64 a;\n\t"
+      "mad.wide.s32 a, %1, 8, %0;\n\t"
+      "red.global.add.f64 [a], %2;\n\t}"
+      ::"l"(base), "r"(idx), "d"(val));
+}
+
 // Every lane holds NV values for NV contiguous doubles at base[target .. target+NV) (target < 0: nothing to add).
 // The warp re-distributes them through its shared-memory buffer so that each RED instruction covers runs of NV
 // contiguous doubles with NV adjacent lanes.  All 32 lanes must call this.
+// `sink`: index of 32 scratch doubles behind the real targets of `base`; values without a target are added there (one
+// slot per lane), which keeps the reduction unconditional: ncu r1k showed a BSSY/BRA/BSYNC triple and a
+// branch_resolving stall around every predicated RED, and every RED waiting on the shared-memory load issued right
+// before it - here all values are fetched first, then the NV reductions go out back to back.
 template <int NV>
-__device__ __forceinline__ void coop_red(double* __restrict__ base, const double* v, int target, double* sW, int* sC, int lane) {
+__device__ __forceinline__ void coop_red(double* __restrict__ base, const double* v, int target, double* sW, int* sC, int lane, int sink) {
   __syncwarp();
 #pragma unroll
   for (int i = 0; i < NV; ++i) sW[lane * NV + i] = v[i];
   sC[lane] = target;
   __syncwarp();
+  double val[NV];
+  int idx[NV];
 #pragma unroll
   for (int it = 0; it < NV; ++it) {
     const int q = it * 32 + lane;
     const int b = q / NV, i = q - b * NV;
     const int t = sC[b];
-    const double val = sW[q];
-    red_add_if(base, t + i, val, t);
+    val[it] = sW[q];
+    idx[it] = (t >= 0) ? t + i : sink + lane;
   }
+#pragma unroll
+  for (int it = 0; it < NV; ++it) red_add_idx(base, idx[it], val[it]);
 }
 
 // Per-element state is written once per update and not read again by this kernel: streaming (evict-first) stores keep
@@ -126,9 +148,12 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     __syncwarp();     // tail kernel: the previous element's last reduction round has finished reading the buffer
 #pragma unroll
     for (int n = 0; n < 6; ++n) cp_async8(&sW[n * 32 + lane], &st.la[n * ld + e]);
-    int* sI = reinterpret_cast<int*>(sW + 192);
+    int* sI = reinterpret_cast<int*>(sW + kV4RedDoubles);
 #pragma unroll
     for (int q = 0; q < 6; ++q) cp_async4(&sI[q * 32 + lane], &as.bmap[q * ld + e]);
+    int* sF = reinterpret_cast<int*>(sW + kV4RedDoubles + 96);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) cp_async4(&sF[k * 32 + lane], &m.fidx[k * ld + e]);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
   if (!TAIL) {
@@ -150,7 +175,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   // are L2-resident already; prefetching them, a second line per block, or the next CTAs' inputs measured slower.)
   if (ASM == 1) {
     asm volatile("cp.async.wait_all;" ::: "memory");
-    const int* sI = reinterpret_cast<const int*>(sW + 192);
+    const int* sI = reinterpret_cast<const int*>(sW + kV4RedDoubles);
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       const int cd = sI[q * 32 + lane];
@@ -301,18 +326,16 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 
   // ---- 3 : vertex vectors, and B <- sqrt(vol) B L in place (one row at a time through registers)
   int f[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) f[k] = live ? m.fidx[k * ld + e] : -1;
   double tl[6];
-  int code[6];
+  const int* sI = reinterpret_cast<const int*>(sW + kV4RedDoubles);          // codes, fidx: read where they are used
+  const int* sF = reinterpret_cast<const int*>(sW + kV4RedDoubles + 96);
   if (ASM == 1) {
     asm volatile("cp.async.wait_all;" ::: "memory");
-    const int* sI = reinterpret_cast<const int*>(sW + 192);
 #pragma unroll
     for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * sW[n * 32 + lane];
-#pragma unroll
-    for (int q = 0; q < 6; ++q) code[q] = live ? sI[q * 32 + lane] : -1;
   } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) f[k] = live ? m.fidx[k * ld + e] : -1;
 #pragma unroll
     for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * st.la[n * ld + e];
   }
@@ -330,7 +353,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
 #endif
     for (int k = 0; k < 3; ++k) {
-      const int fk = (k == 0) ? f[1] : (k == 1) ? f[2] : f[3];
+      const int fk = (ASM == 1) ? sF[(k + 1) * 32 + lane] : ((k == 0) ? f[1] : (k == 1) ? f[2] : f[3]);
       double vv[6];
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
@@ -362,7 +385,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
           }
         }
       } else {
-        coop_red<6>(as.gxrh, vv, (fk >= 0 && !(m.exp & 2)) ? 6 * fk : -1, sW, sC, lane);
+        if (!(m.exp & 2)) coop_red<6>(as.gxrh, vv, (fk >= 0 && live) ? 6 * fk : -1, sW, sC, lane, as.sinkV);
       }
     }
     if (ASM == 0) {
@@ -374,7 +397,8 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
         }
       }
     } else {
-      coop_red<6>(as.gxrh, v0, (f[0] >= 0 && !(m.exp & 2)) ? 6 * f[0] : -1, sW, sC, lane);
+      const int f0 = sF[lane];
+      if (!(m.exp & 2)) coop_red<6>(as.gxrh, v0, (f0 >= 0 && live) ? 6 * f0 : -1, sW, sC, lane, as.sinkV);
     }
   }
 
@@ -430,7 +454,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
 #endif
       for (int k = j + 1; k < 4; ++k) {
-        const int cd = (j == 0) ? ((k == 1) ? code[0] : (k == 2) ? code[1] : code[2]) : (j == 1) ? ((k == 2) ? code[3] : code[4]) : code[5];
+        const int cd = sI[pair6(j, k) * 32 + lane];
         double a[3][3];      // a[r][c] = (B_j B_k^T)(r,c)
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -451,7 +475,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
         for (int r = 0; r < 3; ++r)
 #pragma unroll
           for (int c = 0; c < 3; ++c) v[3 * r + c] = tr ? a[c][r] : a[r][c];
-        coop_red<9>(as.Ablk, v, (cd >= 0 && !(m.exp & 2)) ? 9 * (cd >> 1) : -1, sW, sC, lane);
+        if (!(m.exp & 2)) coop_red<9>(as.Ablk, v, (cd >= 0 && live) ? 9 * (cd >> 1) : -1, sW, sC, lane, as.sinkA);
       }
     }
   }
