@@ -86,9 +86,9 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_arm(nx, ny, nz, seconds, threads=None, native=True):
-    """Time the oracle (CPU restatement, OpenMP) on a bounded sample of the workload: same generator, same material,
-    same alternating states.  Returns (tets/s, dict)."""
+def cpu_arm(nx, ny, nz, seconds, threads=None, native=True, min_reps=1):
+    """Time the oracle (CPU restatement, OpenMP) on the workload grid (or a bounded sample of it): same generator, same
+    material, same alternating states.  Returns (tets/s, dict)."""
     from mixed_fem_b200 import meshgen
     from oracle import orc
     global _NATIVE_LIB
@@ -129,7 +129,7 @@ def cpu_arm(nx, ny, nz, seconds, threads=None, native=True):
         o.update(xb if reps % 2 == 0 else xa, DT)
         o.rhs()
         reps += 1
-        if time.perf_counter() - t0 >= seconds:
+        if time.perf_counter() - t0 >= seconds and reps >= min_reps:
             break
     el = time.perf_counter() - t0
     tm = o.timers()
@@ -171,6 +171,9 @@ def gpu_arm(args):
     nE_total, nV_total = T.shape[0], V.shape[0]
     xa = meshgen.deformed_positions(V, h, scale=args.jitter)
     xb = meshgen.deformed_positions(V, h, scale=0.5 * args.jitter)
+    tail_states = None
+    if world == 1 and args.tail_jitter > 0 and not args.no_tail:
+        tail_states = (meshgen.deformed_positions(V, h, scale=args.tail_jitter), meshgen.deformed_positions(V, h, scale=0.5 * args.tail_jitter))
     rng = np.random.default_rng(meshgen.SEED)
     lam = rng.uniform(-1, 1, size=6 * nE_total) * mu * 1e-3
     if world > 1:
@@ -195,7 +198,6 @@ def gpu_arm(args):
     # state: R, s from the 'previous' positions (polar from identity on the device), lambda seeded
     ms.reset(xb)
     ms.set("la", lam)
-    del lam
     nb = ms.nnz // 9
     # device-resident inputs + pinned host copies for the e2e leg
     xs_host = [torch.from_numpy(xa).pin_memory(), torch.from_numpy(xb).pin_memory()]
@@ -260,6 +262,10 @@ def gpu_arm(args):
     sync()
     e2e_ms = max(e0.elapsed_time(e1), 0.0)
     e2e_wall = (time.perf_counter() - t0) * 1e3
+    parity = parity_pass(ms, loc, xb, xs_dev[0], lam, iface, world, dev, args)
+    tail = None
+    if tail_states is not None:
+        tail = tail_leg(ms, tail_states, lam, dev, nE_total, Vl.shape[0], nb, jitter=args.tail_jitter)
     t = torch.tensor([ms_total, e2e_ms, kt / max(kn, 1)], dtype=torch.float64, device=dev)
     cnt = torch.tensor([launches, 3 * Vl.shape[0] * 8, 3 * ms.nfree * 8, nb], dtype=torch.float64, device=dev)
     if world > 1:
@@ -308,45 +314,156 @@ def gpu_arm(args):
                          "kernel_share_of_step": k_ms / per_step if per_step > 0 else None},
             "polar_iters_per_tet": st0["polar_iters"] / max(nE_l, 1), "eig_sweeps_per_tet": st0["eig_sweeps"] / max(nE_l, 1),
             "psd_slow_fraction": st0.get("psd_slow", 0) / max(nE_l, 1),
+            "parity": parity,
         }
+        if tail is not None:
+            tail["frac"] = tail["achieved"] / peak
+            out["roofline_tail"] = tail
     if not args.no_newton:
         ms.close()
-        nl = newton_leg(args, rank, world, local_rank)
+        del ms
+        torch.cuda.empty_cache()
+        nl = newton_leg(args, args.newton_grid, "ARAP", "C3", rank, world, local_rank)
         if rank == 0:
+            if world == 1 and not args.no_cpu:
+                nl["cpu_baseline"] = newton_cpu_baseline(args)
             out["newton_iteration"] = nl
+        if not args.no_newton_c4:
+            nl4 = newton_leg(args, args.grid, args.material, "C4", rank, world, local_rank, steps=2)
+            if rank == 0:
+                out["newton_iteration_C4"] = nl4
     if rank == 0:
         if world == 1 and not args.no_cpu:
             cx, cy, cz = args.cpu_grid
             _, info = cpu_arm(cx, cy, cz, args.cpu_seconds)
+            v1, _ = cpu_arm(cx, cy, cz, min(6.0, args.cpu_seconds), threads=1)
+            info["value_1_thread"] = v1            # OMP_NUM_THREADS=1 beside all cores
             out["cpu_baseline"] = info
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
 
-def newton_leg(args, rank=0, world=1, local_rank=0):
-    """Metric m2 of SURVEY.md section 8d: ms per Newton iteration on config C3 (55^3 x 6 = 998 250 tets, ARAP), one time step
-    of the device-resident Newton driver with the reference's default solver settings (eigen-pcg-diag, itr_tol 1e-4,
-    <= 500 CG iterations, outer_steps 3): update + rhs + lhs = M + A + PCG + solve(dx) + line search per iteration.
+def parity_pass(ms, loc, xb, x_dev, lam, iface, world, dev, args):
+    """Cross-rank correctness evidence printed with every run: a fixed pass - reset(xb), seeded
+    lambda, ONE update at the first state, interface sums - and global scalars of its results that must not depend on the
+    number of GPUs: owner-weighted |rhs_|^2 and |grad_x_|^2, v.Av and |Av|^2 for a fixed pseudo-random v (A applied
+    sub-assembled + interface sum), the elastic energy and the constraint value.  Compared with the constants of a 1-GPU
+    run stored in tests/golden/bench_parity.json (written by --write-parity)."""
+    import torch
+    import torch.distributed as dist
+    ms.reset(xb)
+    ms.set("la", lam)
+    ms.update_dev(x_dev.data_ptr(), DT)
+    if iface is not None:
+        iface()
+    torch.cuda.synchronize()
+    nF = ms.nfree
+    if loc is not None:
+        w = np.repeat(loc.dot_weight, 3)
+        gid = loc.free_l2g
+    else:
+        w = np.ones(3 * nF)
+        gid = np.arange(nF, dtype=np.int64)
+    rhs = ms.rhs()
+    gx = ms.get("grad_x")
+    v = np.sin(0.37 * (3.0 * gid[:, None] + np.arange(3)[None, :]) + 0.11).reshape(-1)
+    vd = torch.as_tensor(v, device=dev)
+    yd = torch.zeros_like(vd)
+    ms.spmv_dev(vd.data_ptr(), yd.data_ptr())
+    if world > 1:
+        ms.interface_sum_dev(yd.data_ptr(), 3)
+    torch.cuda.synchronize()
+    y = yd.cpu().numpy()
+    e_psi = ms.energy_dev()
+    e_con = ms.constraint_value_dev(x_dev.data_ptr())
+    vals = torch.tensor([np.dot(w * rhs, rhs), np.dot(w * gx, gx), np.dot(w * v, y), np.dot(w * y, y), e_psi, e_con],
+                        dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(vals)
+    names = ["rhs_norm2", "grad_x_norm2", "vAv", "Av_norm2", "energy", "constraint_value"]
+    got = dict(zip(names, vals.tolist()))
+    key = "%dx%dx%d:%s:j%g" % (tuple(args.grid) + (args.material, args.jitter))
+    path = os.path.join(ROOT, "tests", "golden", "bench_parity.json")
+    try:
+        table = json.load(open(path))
+    except Exception:
+        table = {}
+    if args.write_parity and world == 1:
+        table[key] = got
+        json.dump(table, open(path, "w"), indent=1, sort_keys=True)
+    ref = table.get(key)
+    out = {"values": got, "reference": "1-GPU run, tests/golden/bench_parity.json" if ref else None}
+    if ref:
+        err = {k: abs(got[k] - ref[k]) / max(abs(ref[k]), 1e-300) for k in names}
+        out["rel_err_vs_1gpu"] = err
+        out["ok"] = bool(max(err.values()) <= 1e-10)
+    return out
+
+
+def tail_leg(ms, states, lam, dev, nE_total, nV, nb, steps=8, jitter=None):
+    """The same update on a state where a large part of the Hessians is indefinite (vertex jitter x tail_jitter): those
+    elements leave the Cholesky fast path for the Jacobi tail kernel.  Reported beside the headline so that the cost of
+    the eigen path is driver-recorded."""
+    import torch
+    xa, xb = states
+    xs = [torch.as_tensor(xa, device=dev), torch.as_tensor(xb, device=dev)]
+    ms.reset(xb)
+    ms.set("la", lam)
+    for i in range(3):
+        ms.update_dev(xs[i % 2].data_ptr(), DT)
+    torch.cuda.synchronize()
+    st = ms.status()
+    ms.set_option("profile", 1)
+    ms.kernel_time_ms()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        ms.update_dev(xs[(3 + i) % 2].data_ptr(), DT)
+    e1.record()
+    torch.cuda.synchronize()
+    kt, kn = ms.kernel_time_ms()
+    ms.set_option("profile", 0)
+    per = e0.elapsed_time(e1) / steps
+    k_ms = kt / max(kn, 1)
+    ab = algorithmic_bytes(nE_total, nV, ms.nfree, nb)
+    return {"jitter": jitter, "psd_slow_fraction": st.get("psd_slow", 0) / nE_total, "eig_sweeps_per_tet": st["eig_sweeps"] / nE_total,
+            "value": nE_total / (per * 1e-3), "unit": UNIT, "ms_per_step": per, "kernel_ms": k_ms, "achieved": ab / (k_ms * 1e-3) / 1e9}
+
+
+def cg_bytes_per_iteration(nb, nF):
+    """one PCG iteration: the block-CSR operator once (72 B values + 4 B column index per block) + 7 passes over d*nF vectors"""
+    return 76.0 * nb + 7.0 * 24.0 * nF
+
+
+def newton_leg(args, grid, material, label, rank=0, world=1, local_rank=0, steps=3):
+    """Metric m2 of SURVEY.md section 8d: ms per Newton iteration - `steps` time steps of the device-resident Newton driver
+    with the reference's default solver settings (eigen-pcg-diag, itr_tol 1e-4, <= 500 CG iterations, outer_steps 3):
+    update + rhs + lhs = M + A + PCG + solve(dx) + line search per iteration.  Timed with CUDA events around the time
+    steps (max over ranks) and, per phase, with the library's event spans under the reference's Timer keys.
     N > 1: the same mesh in N element slabs, mfb_newton_step as a collective call (distributed PCG inside the library)."""
     import torch
     import torch.distributed as dist
     import mixed_fem_b200 as mf
     from mixed_fem_b200 import meshgen, partition
-    nx, ny, nz = args.newton_grid
+    nx, ny, nz = grid
     h = 1.0 / nx
     V, T = meshgen.kuhn_grid(nx, ny, nz, h=h)
     fm = meshgen.pinned_free_map(V)
     mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
     nE = T.shape[0]
+    nF_total = int((fm >= 0).sum())
     if world > 1:
         loc, _, _ = partition.make_local(V, T, fm, world, rank)
-        ms = mf.MixedStretch(loc.V, loc.T, loc.free_map, [("ARAP", mu, la)], device=local_rank)
+        ms = mf.MixedStretch(loc.V, loc.T, loc.free_map, [(material, mu, la)], device=local_rank)
+        del V, T
         ms.reset()
         ms.comm_init(loc)
     else:
-        ms = mf.MixedStretch(V, T, fm, [("ARAP", mu, la)], device=local_rank)
+        ms = mf.MixedStretch(V, T, fm, [(material, mu, la)], device=local_rank)
+        del V, T
         ms.reset()
+    ms.set_stream(torch.cuda.current_stream().cuda_stream)
     ms.newton_init(density=1000.0, h=DT)
     ms.newton_step(outer_steps=1)                     # warm-up time step
     torch.cuda.synchronize()
@@ -354,45 +471,118 @@ def newton_leg(args, rank=0, world=1, local_rank=0):
         dist.barrier()
         torch.cuda.synchronize()
     ms.launches(reset=True)
-    t0 = time.perf_counter()
-    lg = ms.newton_step(outer_steps=3, precond=1, cg_tol=1e-4, cg_max_iters=500)
+    ms.set_option("profile", 1)
+    ms.phase_times(reset=True)
+    ms.kernel_time_ms()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    logs = []
+    e0.record()
+    for _ in range(steps):
+        logs.append(ms.newton_step(outer_steps=3, precond=1, cg_tol=1e-4, cg_max_iters=500))
+    e1.record()
     torch.cuda.synchronize()
-    el = (time.perf_counter() - t0) * 1e3
+    el = e0.elapsed_time(e1)
+    ph = ms.phase_times()
+    ms.set_option("profile", 0)
+    nb_l, nF_l = ms.nnz // 9, ms.nfree
+    n = max(sum(int(l["n_iters"]) for l in logs), 1)
+    cg_total = max(sum(int(l["cg_iters_total"]) for l in logs), 1)
+    tt = torch.tensor([el, ph["linsolve"][0]], dtype=torch.float64, device=torch.device("cuda", local_rank))
     if world > 1:
-        t = torch.tensor([el], dtype=torch.float64, device=torch.device("cuda", local_rank))
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        el = float(t[0])
-    n = max(int(lg["n_iters"]), 1)
-    out = {"workload": "C3: %dx%dx%d Kuhn grid = %d tets, ARAP, dt=%.4f, eigen-pcg-diag tol 1e-4" % (nx, ny, nz, nE, DT),
-           "n_gpus": world, "ms_per_newton_iteration": el / n, "newton_iterations": n, "cg_iterations": [int(v) for v in lg["cg_iters"]],
-           "ms_per_cg_iteration_upper_bound": el / max(int(lg["cg_iters_total"]), 1),
-           "energy": [float(v) for v in lg["energy"]], "decrement": [float(v) for v in lg["decrement"]],
-           "alpha": [float(v) for v in lg["alpha"]], "gpu_launches": ms.launches(),
-           "timing": "host wall clock around one time step, max over ranks (the loop branches on device scalars)"}
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    el, lin_ms = tt.tolist()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    cg_ms = lin_ms / cg_total
+    cgb = cg_bytes_per_iteration(nb_l, nF_l)          # this rank's share
+    out = {"workload": "%s: %dx%dx%d Kuhn grid = %d tets, %s, dt=%.4f, eigen-pcg-diag tol 1e-4, %d time steps x 3 Newton iterations" %
+                       (label, nx, ny, nz, nE, material, DT, steps),
+           "n_gpus": world, "ms_per_newton_iteration": el / n, "newton_iterations": n,
+           "cg_iterations": [int(v) for l in logs for v in l["cg_iters"]],
+           "ms_per_cg_iteration": cg_ms,
+           "phase_ms_per_newton_iteration": {k: v[0] / n for k, v in ph.items()},
+           "roofline_cg": {"bound": "hbm", "unit": "GB/s", "peak": peak, "achieved": cgb / (cg_ms * 1e-3) / 1e9,
+                           "frac": cgb / (cg_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_iteration": cgb,
+                           "note": "per rank: 76 B per 3x3 block (values + column index) + 7 vector passes of 24 B per free vertex; "
+                                   "time = CUDA-event span of the PCG (key linsolve) / CG iterations, max over ranks"},
+           "energy": [float(v) for v in logs[-1]["energy"]], "decrement": [float(v) for v in logs[-1]["decrement"]],
+           "alpha": [float(v) for v in logs[-1]["alpha"]], "gpu_launches": ms.launches(),
+           "timing": "CUDA events around %d time steps (the loop itself branches on device scalars read by the host), max over ranks" % steps}
     ms.close()
     return out
 
 
+def newton_cpu_baseline(args):
+    """CPU arm of the SAME leg on a bounded sample: the oracle's restatement of NewtonOptimizer::step (oracle/newton.py)
+    around the C++/OpenMP oracle variable, linear solve = the Eigen ConjugateGradient restatement (diagonal preconditioner,
+    tol 1e-4, <= 500 iterations) on scipy's CSR product (one thread: Eigen's RowMajor SpMV is OpenMP-parallel, so this
+    part is pessimistic for the reference; update / rhs / solve / energy / constraint run on all cores)."""
+    from mixed_fem_b200 import meshgen
+    from oracle import newton as onewton
+    from oracle import orc
+    nx, ny, nz = args.newton_cpu_grid
+    V, T = meshgen.kuhn_grid(nx, ny, nz, h=1.0 / 55)
+    fm = meshgen.pinned_free_map(V)
+    mu, la = meshgen.enu_to_lame(E_YOUNG, NU)
+    L = orc.lib(_NATIVE_LIB or None)
+    try:
+        threads = len(os.sched_getaffinity(0))
+    except Exception:
+        threads = os.cpu_count() or 1
+    L.orc_set_num_threads(int(threads))
+    var = orc.OracleMixedStretch(V, T, fm, [("ARAP", mu, la)], libpath=_NATIVE_LIB or None)
+    var.reset()
+    nt = onewton.OracleNewton(var, V, T, fm, density=1000.0, h=DT)
+    nt.step(outer_steps=1, cg=(1, 1e-4, 500))
+    for k in nt.timers:
+        nt.timers[k] = 0.0
+    var.timers(reset=True)
+    t0 = time.perf_counter()
+    lg = nt.step(outer_steps=3, cg=(1, 1e-4, 500))
+    el = time.perf_counter() - t0
+    n = max(int(lg["n_iters"]), 1)
+    inner = var.timers()
+    ph = {k: v * 1e3 / n for k, v in nt.timers.items()}
+    ph.update({"energy": inner["energy"] / n, "constraint": inner["constraint"] / n, "rotations": inner["rotations"] / n,
+               "derivatives": inner["derivatives"] / n, "Aloc": inner["Aloc"] / n, "assemble": inner["assemble"] / n})
+    nE = T.shape[0]
+    return {"ms_per_newton_iteration": el * 1e3 / n, "ms_per_newton_iteration_per_Mtet": el * 1e3 / n / (nE / 1e6), "cores": int(L.orc_num_threads()),
+            "kind": "port", "cg_iterations": [int(v) for v in lg["cg_iters"]],
+            "sample": "%dx%dx%d x6 = %d tets of the C3 grid (ARAP), one time step of 3 Newton iterations; scale by tets for C3" % (nx, ny, nz, nE),
+            "phase_ms_per_newton_iteration": ph}
+
+
 def reference_arm(args):
+    """bench.py --impl reference: the CPU implementation of the path (the oracle port: the reference itself cannot be
+    compiled here, no Eigen) on the host cores, SAME workload as the CUDA arm (the full --grid, default C4 = 119^3 x 6
+    tets; about 25 GB of host memory and 3-4 s per update()+rhs() call on 16 cores), every step one full call."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cx, cy, cz = args.cpu_grid
-    per = max(2.0, min(20.0, 60.0 / max(1, args.steps + args.warmup)))
-    vals = []
-    info = None
-    for i in range(args.warmup + args.steps):
-        v, info = cpu_arm(cx, cy, cz, per)
-        if i >= args.warmup:
-            vals.append(v)
-    value = float(np.mean(vals))
-    info["value"] = value
+    cx, cy, cz = args.cpu_grid if args.cpu_grid_given else args.grid
     nE = cx * cy * cz * 6
+    # one cpu_arm call builds the oracle once and loops update()+rhs() for the requested number of calls
+    reps = max(1, args.warmup + args.steps)
+    budget = 1.0              # seconds: min_reps decides
+    if nE * reps / 2.5e6 > 420.0:      # keep the run inside a few minutes on a small host: fewer calls, said in `sample`
+        reps = max(2, int(420.0 * 2.5e6 / nE))
+    value, info = cpu_arm(cx, cy, cz, budget, min_reps=reps)
+    v1 = None
+    if nE <= 2_000_000:
+        v1, _ = cpu_arm(cx, cy, cz, 4.0, threads=1)
+    info["value"] = value
+    info["value_1_thread"] = v1
+    same = [cx, cy, cz] == list(args.grid)
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": nE / value * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic",
-           "config": {"workload": "bounded sample of C4: %dx%dx%d Kuhn grid = %d tets, Stable-Neohookean, update()+rhs() on the host cores "
-                                  "(reference cannot be compiled here: no Eigen; oracle port timed instead)" % (cx, cy, cz, nE)},
+           "config": {"workload": ("C4: synthetic %dx%dx%d Kuhn box grid = %d tets, " % (cx, cy, cz, nE)) + "Stable-Neohookean E=1e6 nu=0.45, dt=0.0333, "
+                                  "MixedStretch::update() + rhs() on the host cores (reference cannot be compiled here: no Eigen; oracle port timed instead)",
+                      "same_config_as_cuda_arm": same},
            "cpu_baseline": info,
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out))
@@ -405,7 +595,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--grid", type=int, nargs=3, default=[119, 119, 119])
-    ap.add_argument("--cpu-grid", type=int, nargs=3, default=[64, 32, 32])
+    ap.add_argument("--cpu-grid", type=int, nargs=3, default=None, help="grid of the CPU sample (default: 64 32 32 for the in-run cpu_baseline, the full --grid for --impl reference)")
+    ap.add_argument("--newton-cpu-grid", type=int, nargs=3, default=[32, 16, 16])
+    ap.add_argument("--tail-jitter", type=float, default=8.0, help="vertex jitter multiplier of the roofline_tail line (about 30 %% of the Hessians indefinite)")
+    ap.add_argument("--no-tail", action="store_true")
+    ap.add_argument("--no-newton-c4", action="store_true", help="skip the ms-per-Newton-iteration leg on the C4 grid")
+    ap.add_argument("--write-parity", action="store_true", help="1 GPU: store this run's parity scalars as the reference constants")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (mfb_set_option), e.g. no_overlap=1")
     ap.add_argument("--exp", type=int, default=0, help="what-if experiment bits of the update kernel (results are WRONG; profiling aid only)")
@@ -417,6 +612,9 @@ def main():
     ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): 3 v4 (default), 0 register B, 1 shared-memory B, 2 single fused launch")
     ap.add_argument("--asm", type=int, default=None, help="v4 assembly mode (library option asm_mode): 1 bulk reductions into block-CSR (default), 0 FP64 RED into scalar CSR")
     args = ap.parse_args()
+    args.cpu_grid_given = args.cpu_grid is not None
+    if args.cpu_grid is None:
+        args.cpu_grid = [64, 32, 32]
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":
         reference_arm(args)

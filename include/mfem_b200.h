@@ -253,6 +253,14 @@ int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs
                                                                        mfb_newton_step starts CG from the reference's guess) */
 /* device time of the update kernel alone, CUDA events on the ctx stream, accumulated while option "profile" is 1 */
 int mfb_kernel_time_ms(mfb_ctx* ctx, double* total_ms, int* count);
+/* Phase timers under the reference's own Timer keys (src/optimizers/optimizer_data.cpp:127-256; MixedStretch brackets its
+ * phases at mixed_stretch.cpp:95,112,168,192,207,217,247,279, the optimizer at newton_optimizer.cpp:122,140,162,164,86,88):
+ * CUDA-event spans on the ctx stream, recorded while option "profile" is 1, also emitted as NVTX ranges.  On the device
+ * rotations + derivatives + Aloc + assemble are ONE fused launch sequence, reported under "update" (= the optimizer's key
+ * for the same span).  ms / counts: MFB_PHASE_COUNT entries; reset != 0 clears the accumulators. */
+enum mfb_phase { MFB_PH_UPDATE = 0, MFB_PH_RHS, MFB_PH_LINSOLVE, MFB_PH_SOLVE, MFB_PH_LS, MFB_PH_ENERGY, MFB_PH_CONSTRAINT, MFB_PHASE_COUNT };
+const char* mfb_phase_name(int phase);      /* "update","rhs","linsolve","solve","LS","energy","constraint" */
+int mfb_phase_times(mfb_ctx* ctx, double* ms, int32_t* counts, int reset);
 
 #ifdef __cplusplus
 }

@@ -28,7 +28,7 @@ EXPORTS = [
     "mfb_solve", "mfb_solve_dev", "mfb_post_solve", "mfb_energy", "mfb_constraint_value", "mfb_energy_dev",
     "mfb_constraint_value_dev", "mfb_evaluate_constraint", "mfb_lhs_values", "mfb_lhs_values_dev", "mfb_product",
     "mfb_field_size", "mfb_get", "mfb_set", "mfb_field_dev", "mfb_last_status", "mfb_spmv_dev", "mfb_pcg_dev",
-    "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms",
+    "mfb_num_kernel_launches", "mfb_set_option", "mfb_kernel_time_ms", "mfb_phase_name", "mfb_phase_times",
     "mfb_newton_init", "mfb_newton_init_density", "mfb_newton_step", "mfb_newton_positions", "mfb_newton_positions_dev", "mfb_newton_free",
     "mfb_jacobian_x_nnz", "mfb_jacobian_x_coo", "mfb_lhs_bsr",
     "mfb_kkt_size", "mfb_kkt_product", "mfb_kkt_rhs", "mfb_kkt_layout_dev", "mfb_kkt_product_dev", "mfb_kkt_solve_minres",
@@ -146,6 +146,9 @@ def lib():
     L.mfb_num_kernel_launches.argtypes = [vp, C.POINTER(C.c_int64), C.c_int]
     L.mfb_set_option.argtypes = [vp, C.c_char_p, C.c_int]
     L.mfb_kernel_time_ms.argtypes = [vp, dp, ip]
+    L.mfb_phase_name.argtypes = [C.c_int]
+    L.mfb_phase_name.restype = C.c_char_p
+    L.mfb_phase_times.argtypes = [vp, dp, ip, C.c_int]
     L.mfb_newton_init.argtypes = [vp, ip, C.c_double, C.c_double, dp, dp, dp]
     L.mfb_newton_init_density.argtypes = [vp, ip, dp, C.c_double, dp, dp, dp]
     L.mfb_newton_step.argtypes = [vp, C.POINTER(_NewtonOpts), C.POINTER(_NewtonLog)]
@@ -450,6 +453,13 @@ class MixedStretch:
         t, n = C.c_double(), C.c_int32()
         self._check(self.L.mfb_kernel_time_ms(self.h, C.byref(t), C.byref(n)))
         return t.value, n.value
+
+    def phase_times(self, reset=True):
+        """{key: (total ms, count)} under the reference's Timer keys (recorded while option "profile" is 1)"""
+        n = 7
+        ms = np.zeros(n); cnt = np.zeros(n, dtype=np.int32)
+        self._check(self.L.mfb_phase_times(self.h, _dp(ms), _ip(cnt), int(reset)))
+        return {self.L.mfb_phase_name(k).decode(): (float(ms[k]), int(cnt[k])) for k in range(n)}
 
     def launches(self, reset=False):
         n = C.c_int64()

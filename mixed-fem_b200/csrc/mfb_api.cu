@@ -354,6 +354,7 @@ static int aos_to_soa(mfb_ctx* c, const double* host_aos, mfb::DBuf<double>& soa
 
 extern "C" int mfb_energy_dev(mfb_ctx* c, const double* s_soa, double* e) {
   CHECK_CTX(c);
+  struct Span { mfb_ctx* c; Span(mfb_ctx* c_) : c(c_) { phase_begin(c, MFB_PH_ENERGY); } ~Span() { phase_end(c, MFB_PH_ENERGY); } } span(c);
   if (!e) return MFB_ERR_INVALID;
   const double* sp = s_soa ? s_soa : c->s.p;
   if (c->kind == MFB_SHELL) k_energy<K_SHELL><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), sp, c->partials.p);
@@ -372,6 +373,7 @@ extern "C" int mfb_energy(mfb_ctx* c, const double* /*x*/, const double* s, doub
 }
 extern "C" int mfb_constraint_value_dev(mfb_ctx* c, const double* x_dev, const double* s_soa, double* e) {
   CHECK_CTX(c);
+  struct Span { mfb_ctx* c; Span(mfb_ctx* c_) : c(c_) { phase_begin(c, MFB_PH_CONSTRAINT); } ~Span() { phase_end(c, MFB_PH_CONSTRAINT); } } span(c);
   if (!x_dev || !e) return MFB_ERR_INVALID;
   const double* sp = s_soa ? s_soa : c->s.p;
   if (c->kind == MFB_SHELL) k_constraint<K_SHELL, false><<<c->grid(), 128, 0, c->stream>>>(c->mesh(), c->state(), x_dev, sp, c->partials.p, nullptr);
@@ -494,6 +496,54 @@ extern "C" int mfb_last_status(mfb_ctx* c, mfb_status* st) {
 }
 
 // sum / count of the update-kernel durations recorded since the last call (option "profile" = 1); resets the ring
+#if __has_include(<nvtx3/nvToolsExt.h>)
+#include <nvtx3/nvToolsExt.h>
+#define MFB_NVTX 1
+#endif
+static const char* const kPhaseNames[MFB_PHASE_COUNT] = {"update", "rhs", "linsolve", "solve", "LS", "energy", "constraint"};
+extern "C" const char* mfb_phase_name(int phase) { return (phase >= 0 && phase < MFB_PHASE_COUNT) ? kPhaseNames[phase] : ""; }
+
+void mfb::phase_begin(mfb_ctx* c, int key) {
+  if (!c->profile || key < 0 || key >= MFB_PHASE_COUNT || c->ph_open[key]) return;
+#ifdef MFB_NVTX
+  nvtxRangePushA(kPhaseNames[key]);
+#endif
+  cudaEvent_t e;
+  if (!c->ph_free.empty()) { e = c->ph_free.back(); c->ph_free.pop_back(); }
+  else if (cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, c->stream);
+  c->ph_open[key] = e;
+}
+void mfb::phase_end(mfb_ctx* c, int key) {
+  if (key < 0 || key >= MFB_PHASE_COUNT || !c->ph_open[key]) return;
+#ifdef MFB_NVTX
+  nvtxRangePop();
+#endif
+  cudaEvent_t e;
+  if (!c->ph_free.empty()) { e = c->ph_free.back(); c->ph_free.pop_back(); }
+  else if (cudaEventCreate(&e) != cudaSuccess) { c->ph_free.push_back(c->ph_open[key]); c->ph_open[key] = 0; return; }
+  cudaEventRecord(e, c->stream);
+  c->ph_spans.push_back({key, c->ph_open[key], e});
+  c->ph_open[key] = 0;
+}
+extern "C" int mfb_phase_times(mfb_ctx* c, double* ms, int32_t* counts, int reset) {
+  CHECK_CTX(c);
+  static thread_local double acc[MFB_PHASE_COUNT];
+  static thread_local int32_t cnt[MFB_PHASE_COUNT];
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < MFB_PHASE_COUNT; ++k) { acc[k] = 0; cnt[k] = 0; }
+  for (auto& sp : c->ph_spans) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) { acc[sp.key] += t; cnt[sp.key] += 1; }
+  }
+  for (int k = 0; k < MFB_PHASE_COUNT; ++k) { if (ms) ms[k] = acc[k]; if (counts) counts[k] = cnt[k]; }
+  if (reset) {
+    for (auto& sp : c->ph_spans) { c->ph_free.push_back(sp.a); c->ph_free.push_back(sp.b); }
+    c->ph_spans.clear();
+  }
+  return MFB_OK;
+}
+
 extern "C" int mfb_kernel_time_ms(mfb_ctx* c, double* total_ms, int* count) {
   CHECK_CTX(c);
   MFB_CUDA(cudaStreamSynchronize(c->stream));

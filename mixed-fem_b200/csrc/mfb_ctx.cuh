@@ -53,6 +53,9 @@ struct NewtonView {
   double *Mvals, *x, *xt, *diff, *dx;
   int* vfree;
 };
+// CUDA-event spans under the reference's Timer keys (optimizer_data.cpp:127-256; option "profile" = 1), also NVTX ranges
+void phase_begin(mfb_ctx* c, int key);                            // mfb_api.cu
+void phase_end(mfb_ctx* c, int key);
 void saddle_free(mfb_ctx* c);                                     // mfb_saddle.cu
 void stretch_free(mfb_ctx* c);                                    // mfb_stretch.cu
 int newton_view(mfb_ctx* c, NewtonView* v);                       // MFB_ERR_INVALID before mfb_newton_init
@@ -108,6 +111,10 @@ struct mfb_ctx {
   int cg_zero_guess = 0;   // mfb_newton_step: start CG from 0 instead of the reference's guess (parity runs, see mfb_newton.cu)
   std::vector<cudaEvent_t> ev0, ev1;
   int ev_count = 0;
+  struct PhaseSpan { int key; cudaEvent_t a, b; };
+  std::vector<PhaseSpan> ph_spans;         // closed spans since the last mfb_phase_times
+  std::vector<cudaEvent_t> ph_free;        // event pool
+  cudaEvent_t ph_open[MFB_PHASE_COUNT] = {0};
   void* newton = nullptr;     // mfb_newton_state (mfb_newton.cu)
   void* saddle = nullptr;     // scratch of the saddle-point systems (mfb_saddle.cu)
   void* stretch = nullptr;    // the non-mixed Stretch variable's lhs values / gradient (mfb_stretch.cu)

@@ -338,7 +338,11 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
   log->n_iters = 0; log->cg_iters_total = 0;
   do {
     // update_system(): var->update(unprojected x, dt)
-    if ((rc = mfb_update_dev(c, s->x.p, s->h))) return rc;
+    phase_begin(c, MFB_PH_UPDATE);
+    rc = mfb_update_dev(c, s->x.p, s->h);
+    phase_end(c, MFB_PH_UPDATE);
+    if (rc) return rc;
+    phase_begin(c, MFB_PH_RHS);
     // SystemMatrixPD::pre_solve: rhs = -PM (x - x_tilde - h^2 f) + rhs_mixed ; lhs = PMP^T + A
     const double* rhs_mixed = nullptr;
     if ((rc = mfb_rhs_dev(c, &rhs_mixed))) return rc;
@@ -362,11 +366,19 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
     // held against an exact solve.
     if (c->cg_zero_guess) MFB_CUDA(cudaMemsetAsync(s->dx.p, 0, (size_t)nf * 8, st));
     // multi-GPU: both parts of b are element sums of this rank's slab: one interface sum makes b consistent
-    if ((rc = interface_sum(c, s->b.p, dim, nullptr, 0, nullptr, 0))) return rc;
+    rc = interface_sum(c, s->b.p, dim, nullptr, 0, nullptr, 0);
+    phase_end(c, MFB_PH_RHS);
+    if (rc) return rc;
     int cg_it = 0; double cg_res = 0;
-    if ((rc = mfb_pcg_dev(c, s->Mvals.p, s->b.p, s->dx.p, o->precond, o->cg_tol, o->cg_max_iters, &cg_it, &cg_res))) return rc;
+    phase_begin(c, MFB_PH_LINSOLVE);
+    rc = mfb_pcg_dev(c, s->Mvals.p, s->b.p, s->dx.p, o->precond, o->cg_tol, o->cg_max_iters, &cg_it, &cg_res);
+    phase_end(c, MFB_PH_LINSOLVE);
+    if (rc) return rc;
     // post_solve: x.delta = dx ; var->solve(dx)
-    if ((rc = mfb_solve_dev(c, s->dx.p))) return rc;
+    phase_begin(c, MFB_PH_SOLVE);
+    rc = mfb_solve_dev(c, s->dx.p);
+    phase_end(c, MFB_PH_SOLVE);
+    if (rc) return rc;
     // substep(): decrement = max(|dx|_inf, |ds|_inf)
     double mx = 0, ms = 0;
     k_absmax_soa<<<256, 256, 0, st>>>(s->dx.p, 1, (int)nf, nf, c->partials.p);
@@ -380,7 +392,8 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
     mx = c->h_scal[0]; ms = c->h_scal[1];
     grad_norm = mx > ms ? mx : ms;
     double alpha = 1.0;
-    if ((rc = trial_energy(c, s, 0.0, &E))) return rc;
+    phase_begin(c, MFB_PH_LS);         // the reference's "LS" key spans the line search only; E(0) before it is included here
+    if ((rc = trial_energy(c, s, 0.0, &E))) { phase_end(c, MFB_PH_LS); return rc; }
     res = std::fabs((E - E_prev) / (E + 1e-6));
     E_prev = E;
     // linesearch_backtracking(state, alpha, energy, c = 0, p = 0.5): accept the first alpha with f(alpha) < f(0)
@@ -388,11 +401,12 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
     const double fx0 = E;
     while (iter < o->ls_iters) {
       double fx;
-      if ((rc = trial_energy(c, s, alpha, &fx))) return rc;
+      if ((rc = trial_energy(c, s, alpha, &fx))) { phase_end(c, MFB_PH_LS); return rc; }
       if (fx < fx0) break;
       alpha *= 0.5;
       ++iter;
     }
+    phase_end(c, MFB_PH_LS);
     if (iter < o->ls_iters) {
       if (dim == 3) k_unproject_axpy<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, alpha, nV, s->x.p);
       else k_unproject_axpy<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->vfree.p, s->dx.p, alpha, nV, s->x.p);

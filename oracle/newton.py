@@ -16,6 +16,8 @@ Eigen ConjugateGradient restatement of oracle/pcg.py runs from the reference's i
 (eigen_iterative_solver.h:44-57; the additive-CCD scale is 1 without contact).  PARITY UNPINNED: the reference ships
 no Newton-history fixtures; this follows the control flow line by line.
 """
+import time
+
 import numpy as np
 import scipy.sparse as sp
 import scipy.sparse.linalg as spla
@@ -63,6 +65,9 @@ class OracleNewton:
         self.x = (np.asarray(V, dtype=float).reshape(-1) if x0 is None else np.asarray(x0, dtype=float)).copy()
         self.x_prev = self.x.copy()
         self.v_prev = np.zeros_like(self.x) if v0 is None else np.asarray(v0, dtype=float).copy()
+        # wall-clock seconds under the optimizer's Timer keys (newton_optimizer.cpp:122,140,162,164,86,88); used by
+        # bench.py's CPU baseline of the ms-per-Newton-iteration leg
+        self.timers = {"update": 0.0, "rhs": 0.0, "linsolve": 0.0, "solve": 0.0, "LS": 0.0}
 
     def x_tilde(self):
         return self.x_prev + self.h * self.v_prev
@@ -76,21 +81,27 @@ class OracleNewton:
         h2 = h * h
         log = {k: [] for k in ("energy", "energy_res", "decrement", "alpha", "cg_iters", "ls_iters")}
         i, E_prev = 0, 0.0
+        tm = self.timers
         while True:
+            t0 = time.perf_counter()
             var.update(self.x, h)
+            t1 = time.perf_counter(); tm["update"] += t1 - t0
             outer, inner, vals = var.csr()
             n = outer.size - 1
             A = sp.csr_matrix((vals, inner, outer), shape=(n, n))
             lhs = (self.PMP + A).tocsr()
             diff = self.x - self.x_tilde() - h2 * self.fext
             rhs = -(self.PM @ diff) + var.rhs()
+            t2 = time.perf_counter(); tm["rhs"] += t2 - t1
             if cg is None:
                 dx = spla.spsolve(lhs.tocsc(), rhs)
                 cg_it = 0
             else:
                 guess = -diff[self.free_dofs]
                 dx, cg_it, _ = opcg.conjugate_gradient(lhs, rhs, guess, opcg.make_precond(lhs, cg[0], self.d), cg[1], cg[2])
+            t3 = time.perf_counter(); tm["linsolve"] += t3 - t2
             var.solve(dx)
+            t4 = time.perf_counter(); tm["solve"] += t4 - t3
             ds = var.get("ds")
             decrement = max(np.abs(dx).max(), np.abs(ds).max())
             s0 = var.get("s")
@@ -110,6 +121,7 @@ class OracleNewton:
                     break
                 alpha *= 0.5
                 it += 1
+            tm["LS"] += time.perf_counter() - t4
             if it < ls_iters:
                 self.x[self.free_dofs] += alpha * dx
                 var.set("s", s0 + alpha * ds)
