@@ -206,9 +206,15 @@ def gpu_arm(args):
     iface = None
     if world > 1:
         # the exchange step lives in the library: pack -> ncclAllReduce -> unpack of grad_x_ | rhs_ at the shared vertices
+        # the exchange step lives in the library: interface elements first, point-to-point sum of their grad_x_ | rhs_ with
+        # the neighbouring slabs on a side stream under the interior elements (option update_exchange); --opt
+        # update_exchange=0 falls back to an explicit exchange after the update
         ms.comm_init(loc)
-        gx_ptr, rh_ptr = ms.field_dev("grad_x")[0], ms.rhs_dev()
-        iface = lambda: ms.interface_sum_dev(gx_ptr, 3, rh_ptr, 3)
+        if "update_exchange=0" in args.opt:
+            gx_ptr, rh_ptr = ms.field_dev("grad_x")[0], ms.rhs_dev()
+            iface = lambda: ms.interface_sum_dev(gx_ptr, 3, rh_ptr, 3)
+        else:
+            ms.set_option("update_exchange", 1)
 
     def step(i):
         ms.update_dev(xs_dev[i % 2].data_ptr(), DT)
@@ -299,7 +305,7 @@ def gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": ("C4: synthetic %dx%dx%d Kuhn box grid = %d tets / %d vertices, " % (nx, ny, nz, nE_total, nV_total))
                                    + args.material + " E=1e6 nu=0.45, dt=0.0333, MixedStretch::update() + fused Schur rhs",
-                       "partition": "1 GPU" if world == 1 else "%d element slabs, NCCL all-reduce of interface grad_x_/rhs_" % world,
+                       "partition": "1 GPU" if world == 1 else "%d element slabs (mfb_partition_create), interface elements first, NCCL send/recv of their grad_x_/rhs_ sums with the neighbouring slabs under the interior elements" % world,
                        "l2": "inputs larger than L2 (%.1f GB of per-element state per step), no flush needed" % (1372.0 * nE_total / world / 1e9),
                        "states": "x alternates between two seeded states each step so the warm-started polar iterates"},
             "e2e": {"value": nE_total / (e2e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

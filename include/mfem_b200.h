@@ -236,6 +236,34 @@ int mfb_stretch_energy(mfb_ctx* ctx, const double* x, double* e);            /* 
  * matrix stays sub-assembled; vectors are summed at the free vertices shared between slabs with one ncclAllReduce over
  * a packed buffer laid out over ALL shared vertices.  After mfb_comm_init + mfb_comm_set_interface, mfb_pcg_dev and
  * mfb_newton_step run distributed: every rank calls them collectively with consistent (already summed) vectors. ---- */
+/* Partitioner (host code, no device needed).  Every rank calls it with the GLOBAL mesh and its own rank and gets its part:
+ * method 0 = slabs of equal element count along the longest axis (stable order of the element centroids), method 1 =
+ * recursive coordinate bisection on the centroids.  Local vertices ascend in the global numbering (local free ids keep the
+ * order of the global free_map_); local ELEMENTS are ordered interface-first (those touching a free vertex shared with
+ * another part), so that mfb_update_dev can exchange their vertex sums while the interior elements run. */
+typedef struct mfb_partition mfb_partition;
+enum mfb_part_array {
+  MFB_PART_ELEMS = 0,   /* int32 nE_l : local element -> global element */
+  MFB_PART_VMAP,        /* int32 nV_l : local vertex -> global vertex (ascending) */
+  MFB_PART_T,           /* int32 nE_l x npe : local vertex ids, for mfb_mesh_desc::T */
+  MFB_PART_V,           /* double nV_l x d */
+  MFB_PART_FREE_MAP,    /* int32 nV_l : local free ids */
+  MFB_PART_FREE_L2G,    /* int64 nF_l : local free id -> global free id (ascending) */
+  MFB_PART_IF_LOCAL,    /* int32 : local free ids of this part's shared vertices ... */
+  MFB_PART_IF_POS,      /* int32 : ... and their slots among the n_shared shared vertices of the whole partition */
+  MFB_PART_DOT_WEIGHT,  /* double nF_l : 1 interior / owned (lowest rank touching the vertex), 0 copy owned elsewhere */
+  MFB_PART_NBR_RANK,    /* int32 n_nbr : ranks this part shares vertices with, ascending */
+  MFB_PART_NBR_COUNT,   /* int32 n_nbr : shared vertices per neighbour */
+  MFB_PART_NBR_LOCAL,   /* int32 sum(count) : local free ids per neighbour, ascending GLOBAL id (both sides agree on the order) */
+  MFB_PART_ELEM_PART    /* int32 nE global : part of every element of the global mesh */
+};
+int mfb_partition_create(mfb_partition** out, int32_t dim, int32_t npe, int32_t nV, int32_t nE, const int32_t* T, const double* V,
+                         const int32_t* free_map, int32_t nparts, int32_t rank, int32_t method);
+void mfb_partition_destroy(mfb_partition* p);
+/* sizes[8] = nV_l, nE_l, nF_l, n_if_elems, n_shared, n_if_local, n_nbr, n_nbr_entries */
+int mfb_partition_sizes(const mfb_partition* p, int32_t* sizes);
+int mfb_partition_get(const mfb_partition* p, int what, const void** ptr, int64_t* count);   /* pointers owned by p */
+
 int mfb_comm_unique_id(char* id128);                                  /* rank 0: ncclGetUniqueId; broadcast the 128 bytes */
 int mfb_comm_init(mfb_ctx* ctx, const char* id128, int rank, int world);   /* ncclCommInitRank on the context's device */
 /* if_local[i] = local free vertex id of this rank's i-th interface vertex, if_pos[i] = its slot among the n_shared
@@ -243,6 +271,12 @@ int mfb_comm_init(mfb_ctx* ctx, const char* id128, int rank, int world);   /* nc
  * vertices this rank owns, 0 for copies owned by another rank (so that global dot products count every vertex once) */
 int mfb_comm_set_interface(mfb_ctx* ctx, const int32_t* if_local, const int32_t* if_pos, int32_t n_if_local, int32_t n_shared,
                            const double* dot_weight);
+/* The whole interface description from a partition of THIS context's mesh (mfb_create was given MFB_PART_T / _V / _FREE_MAP):
+ * = mfb_comm_set_interface + the per-neighbour lists + the number of leading interface elements.  With it the exchange is
+ * point-to-point (grouped ncclSend / ncclRecv of each rank's own cuts, summed on arrival) instead of an all-reduce over
+ * every shared vertex of the partition, the CG writes / reads its halo inside its own kernels, and option
+ * "update_exchange" = 1 makes mfb_update_dev sum grad_x_ / rhs_ over ranks itself, overlapped with the interior elements. */
+int mfb_comm_set_partition(mfb_ctx* ctx, const mfb_partition* p);
 /* a (ncomp_a doubles per local free vertex) and optionally b <- sum over ranks at interface vertices, one collective */
 int mfb_interface_sum_dev(mfb_ctx* ctx, double* a_dev, int ncomp_a, double* b_dev, int ncomp_b);
 int mfb_allreduce_dev(mfb_ctx* ctx, double* v_dev, int n, int op);   /* op 0 sum, 1 max; stream-ordered */
@@ -250,7 +284,9 @@ int mfb_allreduce_dev(mfb_ctx* ctx, double* v_dev, int n, int op);   /* op 0 sum
 /* ---- instrumentation ---- */
 int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
 int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0), "cg_zero_guess" (0:
-                                                                       mfb_newton_step starts CG from the reference's guess) */
+                                                                       mfb_newton_step starts CG from the reference's guess),
+                                                                       "update_exchange" (0; multi-GPU, see mfb_comm_set_partition),
+                                                                       "p2p" (1: use the neighbour exchange when a partition is set) */
 /* device time of the update kernel alone, CUDA events on the ctx stream, accumulated while option "profile" is 1 */
 int mfb_kernel_time_ms(mfb_ctx* ctx, double* total_ms, int* count);
 /* Phase timers under the reference's own Timer keys (src/optimizers/optimizer_data.cpp:127-256; MixedStretch brackets its

@@ -34,7 +34,8 @@ EXPORTS = [
     "mfb_kkt_size", "mfb_kkt_product", "mfb_kkt_rhs", "mfb_kkt_layout_dev", "mfb_kkt_product_dev", "mfb_kkt_solve_minres",
     "mfb_dual_product", "mfb_dual_product_dev", "mfb_dual_rhs", "mfb_dual_solve_cg",
     "mfb_stretch_update", "mfb_stretch_update_dev", "mfb_stretch_lhs_values", "mfb_stretch_gradient", "mfb_stretch_dev", "mfb_stretch_energy",
-    "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_interface_sum_dev", "mfb_allreduce_dev",
+    "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_comm_set_partition", "mfb_interface_sum_dev", "mfb_allreduce_dev",
+    "mfb_partition_create", "mfb_partition_destroy", "mfb_partition_sizes", "mfb_partition_get",
 ]
 
 
@@ -556,6 +557,10 @@ class MixedStretch:
         dist.broadcast(t, 0)
         raw = bytes(t.cpu().numpy().tobytes())
         self._check(self.L.mfb_comm_init(self.h, raw, rank, world))
+        if getattr(local, "h", None):          # the library's own partition object: neighbour lists, interface-first elements
+            self.L.mfb_comm_set_partition.argtypes = [C.c_void_p, C.c_void_p]
+            self._check(self.L.mfb_comm_set_partition(self.h, local.h))
+            return
         il = np.ascontiguousarray(local.if_local, dtype=np.int32)
         ipos = np.ascontiguousarray(local.if_pos, dtype=np.int32)
         w = _f64(local.dot_weight)

@@ -1,6 +1,7 @@
 // C ABI entry points of the mixed-stretch path (see include/mfem_b200.h for the reference interface each replaces).
 #include "mfb_ctx.cuh"
 #include <cstdlib>
+#include <algorithm>
 #include "mfb_kernels3.cuh"
 #include <cstring>
 
@@ -22,6 +23,8 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "fuse_rhs")) { c->fuse_rhs = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "assembly")) { c->assembly = value; return MFB_OK; }
   if (!strcmp(name, "profile")) { c->profile = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "update_exchange")) { c->update_exchange = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "p2p")) { c->use_p2p = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch, 3 v4 (default)
   if (!strcmp(name, "exp")) { c->exp = value; return MFB_OK; }
   if (!strcmp(name, "cg_zero_guess")) { c->cg_zero_guess = value ? 1 : 0; return MFB_OK; }
@@ -122,7 +125,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   }
   const DevMesh m = c->mesh();
   const DevState s = c->state();
-  bool vec_recorded = false;
+  bool vec_recorded = false, exchanged = false;
   int slot = -1;
   if (c->profile && c->ev_count < 4096) {
     slot = c->ev_count++;
@@ -180,10 +183,39 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
         }
         LAUNCHED(c, mfb_ctx::kChunks - 1);
         c->x_host_chunked = nullptr;                                   // consumed
+      } else if (c->world > 1 && c->update_exchange && c->use_p2p && c->ent_local.p && c->n_if_elems > 0 && c->n_if_elems < c->nE) {
+        // multi-GPU with a partition: the leading INTERFACE elements first (and their share of the Jacobi tail), then the
+        // point-to-point sum of their vertex vectors (grad_x | rhs, still interleaved) on a side stream while the
+        // interior elements - which touch no shared vertex - run on this one
+        if (!c->xstream) {
+          MFB_CUDA(cudaStreamCreateWithFlags(&c->xstream, cudaStreamNonBlocking));
+          MFB_CUDA(cudaEventCreateWithFlags(&c->ev_x0, cudaEventDisableTiming));
+          MFB_CUDA(cudaEventCreateWithFlags(&c->ev_x1, cudaEventDisableTiming));
+        }
+        const int n1 = std::min(c->nE, ((c->n_if_elems + kV4Threads - 1) / kV4Threads) * kV4Threads);
+        const int g1 = (n1 + kV4Threads - 1) / kV4Threads, g2 = (c->nE - n1 + kV4Threads - 1) / kV4Threads;
+        if (c->fuse_rhs) { k_update_tet_v4<true, 1><<<g1, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 1><<<std::min(g1, tail_grid), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+        else { k_update_tet_v4<false, 1><<<g1, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<false, 1><<<std::min(g1, tail_grid), kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+        k_mark_tail<<<1, 1, 0, st>>>(c->counters.p);
+        MFB_CUDA(cudaEventRecord(c->ev_x0, st));
+        MFB_CUDA(cudaStreamWaitEvent(c->xstream, c->ev_x0, 0));
+        { int rcx = p2p_interface_sum_on(c, c->gxrh.p, 6, nullptr, 0, nullptr, 0, c->xstream); if (rcx) return rcx; }
+        MFB_CUDA(cudaEventRecord(c->ev_x1, c->xstream));
+        if (g2 > 0) {
+          if (c->fuse_rhs) k_update_tet_v4<true, 1><<<g2, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, n1);
+          else k_update_tet_v4<false, 1><<<g2, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, n1);
+        }
+        if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
+        else k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
+        MFB_CUDA(cudaStreamWaitEvent(st, c->ev_x1, 0));
+        LAUNCHED(c, 4);
+        exchanged = true;
       } else if (c->fuse_rhs) k_update_tet_v4<true, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
       else k_update_tet_v4<false, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
-      if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
-      else k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
+      if (!exchanged) {
+        if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
+        else k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
+      }
       // vertex vectors first: grad_x_ / rhs_ are final after this launch (a host reader copies them out while the
       // CSR values are still being written, see mfb_rhs)
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
@@ -234,6 +266,11 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   if (c->kind == MFB_TET && c->nb > 0 && !bulk) {   // RED variants accumulate the upper triangle only
     k_mirror_lower<<<nblk((int64_t)c->n_mirror * 9), 256, 0, st>>>(c->mirror.p, c->n_mirror, 3, c->Avals.p);
     LAUNCHED(c, 1);
+  }
+  if (c->world > 1 && c->update_exchange && !exchanged) {     // same semantics without the overlap (other element kinds, all-reduce path)
+    int rcx = interface_sum(c, c->grad_x.p, c->dim, c->fuse_rhs ? c->rhs.p : nullptr, c->dim, nullptr, 0);
+    if (rcx) return rcx;
+    vec_recorded = false;
   }
   if (slot >= 0) MFB_CUDA(cudaEventRecord(c->ev1[slot], st));
   LAUNCHED(c, 1);

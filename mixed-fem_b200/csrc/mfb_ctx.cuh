@@ -41,11 +41,18 @@ struct DBuf {   // plain device buffer
 }  // namespace mfb
 
 struct mfb_ctx;
+struct mfb_partition;
 namespace mfb {
 // mfb_dist.cu (no-ops when world == 1)
 int interface_sum(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns);
 int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop);
 void comm_free(mfb_ctx* c);
+// mfb_partition.cu -> mfb_dist.cu
+struct PartitionView {
+  int nparts, rank, nF, nE, n_if_elems, n_shared;
+  const std::vector<int32_t>*if_local, *if_pos, *nbr_rank, *nbr_count, *nbr_local;
+  const std::vector<double>* dot_weight;
+};
 // mfb_newton.cu: what the saddle-point systems (mfb_saddle.cu) read from the Displacement / BDF1 state
 struct NewtonView {
   double h, f[3];
@@ -56,6 +63,11 @@ struct NewtonView {
 // CUDA-event spans under the reference's Timer keys (optimizer_data.cpp:127-256; option "profile" = 1), also NVTX ranges
 void phase_begin(mfb_ctx* c, int key);                            // mfb_api.cu
 void phase_end(mfb_ctx* c, int key);
+int partition_view(const mfb_partition* p, PartitionView* v);      // mfb_partition.cu
+// point-to-point halo of the CG (mfb_dist.cu): group{ send/recv of the packed interface rows ; all-reduce of `ns` scalars }
+int halo_exchange(mfb_ctx* c, int ncomp, double* scal, int ns);
+int halo_buffers(mfb_ctx* c, int ncomp, double** send, double** recv);
+int p2p_interface_sum_on(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns, cudaStream_t st);
 void saddle_free(mfb_ctx* c);                                     // mfb_saddle.cu
 void stretch_free(mfb_ctx* c);                                    // mfb_stretch.cu
 int newton_view(mfb_ctx* c, NewtonView* v);                       // MFB_ERR_INVALID before mfb_newton_init
@@ -137,6 +149,16 @@ struct mfb_ctx {
   mfb::DBuf<int> if_local, if_pos, if_inv;   // if_inv[slot] = local free id or -1
   int n_if_local = 0, n_shared = 0;
   mfb::DBuf<double> if_buf, dot_w;
+  // point-to-point exchange (mfb_comm_set_partition): neighbour ranks, entry offsets, local free id per entry, and per
+  // local free row the list of its entries (rowif_ptr / rowif_idx: the CG kernels write / read their halo through it)
+  int use_p2p = 1, update_exchange = 0;
+  int n_if_elems = 0, n_nbr = 0, n_ent = 0;
+  std::vector<int> nbr_rank, nbr_off;        // nbr_off[n_nbr + 1]
+  mfb::DBuf<int> ent_local, rowif_ptr, rowif_idx;
+  mfb::DBuf<double> xsend, xrecv;
+  int xbuf_comp = 0;
+  cudaStream_t xstream = 0;                   // side stream of the overlapped exchange in mfb_update_dev
+  cudaEvent_t ev_x0 = 0, ev_x1 = 0;
 
   mfb::DevMesh mesh() const {
     mfb::DevMesh m;

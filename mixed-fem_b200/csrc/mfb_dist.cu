@@ -8,9 +8,23 @@
 // Everything is enqueued on the context stream: no host synchronisation is added by this file.
 // NCCL is bound at run time (dlopen "libnccl.so.2": the copy the host process already holds - e.g. torch's - else the
 // system one), so the library has no NCCL dependency for single-GPU users.
+//
+// Two exchange paths.  (1) all-reduce path (mfb_comm_set_interface): ONE buffer over all shared vertices of the partition.
+// (2) point-to-point path (mfb_comm_set_partition, default when set): every rank packs only ITS cuts, one grouped
+// ncclSend / ncclRecv per neighbour (<= 2 for slabs), arrivals are added to the local values - a + b on one side, b + a
+// on the other, bit-identical copies for vertices shared by two parts; scalar sums ride in the same NCCL group.
 #include "mfb_ctx.cuh"
 #include <dlfcn.h>
+#if __has_include(<nccl.h>)
 #include <nccl.h>
+#else      // the few NCCL declarations this file needs, so that the single-GPU library builds without NCCL headers
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef enum { ncclSuccess = 0 } ncclResult_t;
+typedef enum { ncclSum = 0, ncclProd = 1, ncclMax = 2, ncclMin = 3 } ncclRedOp_t;
+typedef enum { ncclInt8 = 0, ncclUint8 = 1, ncclInt32 = 2, ncclUint32 = 3, ncclInt64 = 4, ncclUint64 = 5, ncclFloat16 = 6, ncclFloat32 = 7, ncclFloat64 = 8, ncclDouble = 8 } ncclDataType_t;
+#endif
+#include <cstring>
 
 using namespace mfb;
 
@@ -23,6 +37,10 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   bool ok = false;
 };
@@ -40,7 +58,12 @@ NcclApi* nccl() {
       api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
       api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
       api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
-      api.ok = api.GetUniqueId && api.CommInitRank && api.AllReduce && api.CommDestroy && api.GetErrorString;
+      api.Send = (decltype(api.Send))dlsym(h, "ncclSend");
+      api.Recv = (decltype(api.Recv))dlsym(h, "ncclRecv");
+      api.GroupStart = (decltype(api.GroupStart))dlsym(h, "ncclGroupStart");
+      api.GroupEnd = (decltype(api.GroupEnd))dlsym(h, "ncclGroupEnd");
+      api.ok = api.GetUniqueId && api.CommInitRank && api.AllReduce && api.CommDestroy && api.GetErrorString && api.Send && api.Recv &&
+               api.GroupStart && api.GroupEnd;
     }
   }
   return &api;
@@ -81,14 +104,88 @@ __global__ void k_if_invert(const int* __restrict__ if_local, const int* __restr
   if (i < n) inv[if_pos[i]] = if_local[i];
 }
 
+// point-to-point path: entry i (concatenated over the neighbours) <-> local free vertex ent[i]
+__global__ void k_p2p_pack(const int* __restrict__ ent, int n_ent, const double* __restrict__ a, int na, const double* __restrict__ b, int nb,
+                           double* __restrict__ send) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int w = na + nb;
+  if (i >= n_ent * w) return;
+  const int v = i / w, k = i - v * w;
+  const int64_t l = ent[v];
+  send[i] = (k < na) ? a[l * na + k] : b[l * nb + (k - na)];
+}
+// a vertex shared with more than one neighbour has several entries: atomic adds (order-dependent only in that case)
+__global__ void k_p2p_unpack_add(const int* __restrict__ ent, int n_ent, double* __restrict__ a, int na, double* __restrict__ b, int nb,
+                                 const double* __restrict__ recv) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int w = na + nb;
+  if (i >= n_ent * w) return;
+  const int v = i / w, k = i - v * w;
+  const int64_t l = ent[v];
+  if (k < na) atomicAdd(&a[l * na + k], recv[i]); else atomicAdd(&b[l * nb + (k - na)], recv[i]);
+}
+
+int ensure_xbuf(mfb_ctx* c, int ncomp) {
+  if (c->xbuf_comp >= ncomp) return MFB_OK;
+  int rc;
+  const size_t n = (size_t)c->n_ent * ncomp + 1;
+  if ((rc = c->xsend.alloc(n)) || (rc = c->xrecv.alloc(n))) return rc;
+  c->xbuf_comp = ncomp;
+  return MFB_OK;
+}
+
 }  // namespace
 
 namespace mfb {
+
+// group{ send / recv of xsend / xrecv (ncomp doubles per entry) with every neighbour ; all-reduce(sum) of ns scalars }
+// on `st`.  The send buffer must have been filled on `st` (k_p2p_pack, or the CG's SpMV kernel).
+static int halo_exchange_on(mfb_ctx* c, int ncomp, double* scal, int ns, cudaStream_t st) {
+  NcclApi* api = nccl();
+  ncclResult_t r = api->GroupStart();
+  if (r != ncclSuccess) return nccl_fail("ncclGroupStart", r);
+  for (int q = 0; q < c->n_nbr; ++q) {
+    const size_t off = (size_t)c->nbr_off[q] * ncomp, cnt = (size_t)(c->nbr_off[q + 1] - c->nbr_off[q]) * ncomp;
+    if ((r = api->Send(c->xsend.p + off, cnt, ncclDouble, c->nbr_rank[q], (ncclComm_t)c->comm, st)) != ncclSuccess) return nccl_fail("ncclSend", r);
+    if ((r = api->Recv(c->xrecv.p + off, cnt, ncclDouble, c->nbr_rank[q], (ncclComm_t)c->comm, st)) != ncclSuccess) return nccl_fail("ncclRecv", r);
+  }
+  if (ns > 0 && (r = api->AllReduce(scal, scal, (size_t)ns, ncclDouble, ncclSum, (ncclComm_t)c->comm, st)) != ncclSuccess) return nccl_fail("ncclAllReduce", r);
+  if ((r = api->GroupEnd()) != ncclSuccess) return nccl_fail("ncclGroupEnd", r);
+  return MFB_OK;
+}
+int halo_buffers(mfb_ctx* c, int ncomp, double** send, double** recv) {
+  int rc = ensure_xbuf(c, ncomp);
+  if (rc) return rc;
+  *send = c->xsend.p; *recv = c->xrecv.p;
+  return MFB_OK;
+}
+int halo_exchange(mfb_ctx* c, int ncomp, double* scal, int ns) {
+  if (c->world <= 1) return MFB_OK;
+  int rc = ensure_xbuf(c, ncomp);
+  if (rc) return rc;
+  return halo_exchange_on(c, ncomp, scal, ns, c->stream);
+}
+
+// the whole point-to-point interface sum of (a | b) on stream st
+int p2p_interface_sum_on(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns, cudaStream_t st) {
+  const int w = na + (b ? nb : 0);
+  int rc = ensure_xbuf(c, w);
+  if (rc) return rc;
+  const int64_t n = (int64_t)c->n_ent * w;
+  if (n > 0) k_p2p_pack<<<nblk(n), 256, 0, st>>>(c->ent_local.p, c->n_ent, a, na, b, b ? nb : 0, c->xsend.p);
+  if ((rc = halo_exchange_on(c, w, scal, ns, st))) return rc;
+  if (n > 0) k_p2p_unpack_add<<<nblk(n), 256, 0, st>>>(c->ent_local.p, c->n_ent, a, na, b, b ? nb : 0, c->xrecv.p);
+  c->launches += 2;
+  MFB_CUDA(cudaGetLastError());
+  return MFB_OK;
+}
 
 // a (na per free vertex) and optionally b (nb per free vertex) <- sums over ranks at interface vertices; `scal` (ns
 // doubles, device) is summed over ranks in the same collective.
 int interface_sum(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns) {
   if (c->world <= 1) return MFB_OK;
+  if (c->use_p2p && c->ent_local.p) return p2p_interface_sum_on(c, a, na, b, nb, scal, ns, c->stream);
+  if (!c->if_inv.p) { g_last_error = "interface_sum: no interface description (mfb_comm_set_interface / mfb_comm_set_partition)"; return MFB_ERR_INVALID; }
   NcclApi* api = nccl();
   const int w = na + (b ? nb : 0);
   const size_t need = (size_t)c->n_shared * w + ns;
@@ -112,6 +209,8 @@ int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop) {
 }
 
 void comm_free(mfb_ctx* c) {
+  if (c->xstream) { cudaStreamDestroy(c->xstream); c->xstream = 0; }
+  if (c->ev_x0) { cudaEventDestroy(c->ev_x0); cudaEventDestroy(c->ev_x1); c->ev_x0 = c->ev_x1 = 0; }
   if (c->comm && nccl()->ok) nccl()->CommDestroy((ncclComm_t)c->comm);
   c->comm = nullptr; c->world = 1; c->rank = 0;
 }
@@ -149,6 +248,16 @@ extern "C" int mfb_comm_set_interface(mfb_ctx* c, const int32_t* if_local, const
                                       const double* dot_weight) {
   CHECK_CTX(c);
   if (n_if_local < 0 || n_shared < 0 || (n_if_local > 0 && (!if_local || !if_pos)) || !dot_weight) return MFB_ERR_INVALID;
+  {   // a bad description would make the pack / unpack kernels read and write out of bounds: check it on the host
+    std::vector<char> seen((size_t)n_shared, 0);
+    for (int i = 0; i < n_if_local; ++i) {
+      if (if_local[i] < 0 || if_local[i] >= c->nF || if_pos[i] < 0 || if_pos[i] >= n_shared || seen[if_pos[i]]) {
+        g_last_error = "mfb_comm_set_interface: if_local / if_pos out of range or slots not unique";
+        return MFB_ERR_INVALID;
+      }
+      seen[if_pos[i]] = 1;
+    }
+  }
   int rc;
   if ((rc = c->if_local.alloc((size_t)n_if_local + 1)) || (rc = c->if_pos.alloc((size_t)n_if_local + 1)) || (rc = c->dot_w.alloc((size_t)c->nF + 1))) return rc;
   if (n_if_local > 0) {
@@ -161,6 +270,41 @@ extern "C" int mfb_comm_set_interface(mfb_ctx* c, const int32_t* if_local, const
   if (n_if_local > 0) k_if_invert<<<nblk(n_if_local), 256, 0, c->stream>>>(c->if_local.p, c->if_pos.p, n_if_local, c->if_inv.p);
   MFB_CUDA(cudaStreamSynchronize(c->stream));
   c->n_if_local = n_if_local; c->n_shared = n_shared;
+  return MFB_OK;
+}
+
+extern "C" int mfb_comm_set_partition(mfb_ctx* c, const mfb_partition* p) {
+  CHECK_CTX(c);
+  PartitionView v;
+  if (partition_view(p, &v)) { g_last_error = "mfb_comm_set_partition: null partition"; return MFB_ERR_INVALID; }
+  if (v.nF != c->nF || v.nE != c->nE) { g_last_error = "mfb_comm_set_partition: the partition is not the one this context was created from"; return MFB_ERR_INVALID; }
+  if (c->world != v.nparts || c->rank != v.rank) { g_last_error = "mfb_comm_set_partition: call mfb_comm_init with the partition's rank / world first"; return MFB_ERR_INVALID; }
+  int rc = mfb_comm_set_interface(c, v.if_local->data(), v.if_pos->data(), (int32_t)v.if_local->size(), v.n_shared, v.dot_weight->data());
+  if (rc) return rc;
+  c->n_nbr = (int)v.nbr_rank->size();
+  c->nbr_rank.assign(v.nbr_rank->begin(), v.nbr_rank->end());
+  c->nbr_off.assign((size_t)c->n_nbr + 1, 0);
+  for (int q = 0; q < c->n_nbr; ++q) c->nbr_off[q + 1] = c->nbr_off[q] + (*v.nbr_count)[q];
+  c->n_ent = c->nbr_off[c->n_nbr];
+  c->n_if_elems = v.n_if_elems;
+  c->xbuf_comp = 0;
+  // per local free row: its entries
+  std::vector<int> ptr((size_t)c->nF + 1, 0), idx((size_t)c->n_ent);
+  for (int i = 0; i < c->n_ent; ++i) {
+    const int l = (*v.nbr_local)[i];
+    if (l < 0 || l >= c->nF) { g_last_error = "mfb_comm_set_partition: entry out of range"; return MFB_ERR_INVALID; }
+    ptr[l + 1] += 1;
+  }
+  for (int l = 0; l < c->nF; ++l) ptr[l + 1] += ptr[l];
+  { std::vector<int> fill(ptr.begin(), ptr.end() - 1);
+    for (int i = 0; i < c->n_ent; ++i) idx[fill[(*v.nbr_local)[i]]++] = i; }
+  if ((rc = c->ent_local.alloc((size_t)c->n_ent + 1)) || (rc = c->rowif_ptr.alloc((size_t)c->nF + 1)) || (rc = c->rowif_idx.alloc((size_t)c->n_ent + 1))) return rc;
+  if (c->n_ent) {
+    MFB_CUDA(cudaMemcpyAsync(c->ent_local.p, v.nbr_local->data(), (size_t)c->n_ent * 4, cudaMemcpyHostToDevice, c->stream));
+    MFB_CUDA(cudaMemcpyAsync(c->rowif_idx.p, idx.data(), (size_t)c->n_ent * 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  MFB_CUDA(cudaMemcpyAsync(c->rowif_ptr.p, ptr.data(), ((size_t)c->nF + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
   return MFB_OK;
 }
 

@@ -504,8 +504,10 @@ __global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_tail(
   const int w = threadIdx.x >> 5;
   double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;
   int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;
+  // list entries [counters[6], counters[5]): counters[6] is 0 unless an earlier tail launch of the same update() has
+  // already processed a prefix (interface elements first, see mfb_update_dev / k_mark_tail)
   const long long n = (long long)st.counters[5];
-  for (long long i0 = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += (long long)gridDim.x * blockDim.x) {
+  for (long long i0 = (long long)st.counters[6] + (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += (long long)gridDim.x * blockDim.x) {
     const long long i = i0 + (threadIdx.x & 31);
     const bool in = i < n;
     update_tet_v4_body<FUSE_RHS, true, ASM>(m, st, as, x, as.slow_list[in ? i : n - 1], in, h2, smem4, sW, sC);
@@ -558,6 +560,8 @@ static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restr
     if (qd >= 0) __stcs(&A[D0 + (int64_t)r * rowlen + qd], -(dval[r] + tot));
   }
 }
+
+static __global__ void k_mark_tail(unsigned long long* counters) { counters[6] = counters[5]; }
 
 static __global__ void __launch_bounds__(256) k_deinterleave_vec(const double* __restrict__ gxrh, int nF, double* __restrict__ gx, double* __restrict__ rh, int with_rhs) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

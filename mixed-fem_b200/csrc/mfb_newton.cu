@@ -336,6 +336,9 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
   int i = 0;
   double grad_norm = 0, E = 0, E_prev = 0, res = 0;
   log->n_iters = 0; log->cg_iters_total = 0;
+  // multi-GPU: b = rhs_ - PM diff is summed over ranks ONCE below; update() must leave rhs_ as this rank's element sums
+  struct NoUpdateExchange { mfb_ctx* c; int saved; NoUpdateExchange(mfb_ctx* c_) : c(c_), saved(c_->update_exchange) { c->update_exchange = 0; }
+                            ~NoUpdateExchange() { c->update_exchange = saved; } } no_update_exchange(c);
   do {
     // update_system(): var->update(unprojected x, dt)
     phase_begin(c, MFB_PH_UPDATE);

@@ -221,7 +221,10 @@ template <int DIM>
 __global__ void __launch_bounds__(256) k_pcg_spmv_dot(const int* __restrict__ blockptr, const int* __restrict__ bcol, int nF,
                                                       const double* __restrict__ A, const double* __restrict__ p,
                                                       double* __restrict__ t, double* __restrict__ scal,
-                                                      double* __restrict__ partials, unsigned* __restrict__ ticket) {
+                                                      double* __restrict__ partials, unsigned* __restrict__ ticket,
+                                                      const int* __restrict__ rowif_ptr, const int* __restrict__ rowif_idx,
+                                                      double* __restrict__ send) {
+  // multi-GPU (rowif_ptr != nullptr): an interface row also goes straight into the send buffer of the halo exchange
   __shared__ double sh[8];
   if (scal[2] != 0.0) return;
   const int lane = threadIdx.x & 31, hl = lane & 15;
@@ -258,6 +261,13 @@ __global__ void __launch_bounds__(256) k_pcg_spmv_dot(const int* __restrict__ bl
     if (hl == 0 && row < nF) {
 #pragma unroll
       for (int r = 0; r < DIM; ++r) { t[DIM * row + r] = acc[r]; dot = fma(acc[r], p[DIM * row + r], dot); }
+      if (rowif_ptr) {
+        for (int j = rowif_ptr[row]; j < rowif_ptr[row + 1]; ++j) {
+          const int64_t s0 = (int64_t)DIM * rowif_idx[j];
+#pragma unroll
+          for (int r = 0; r < DIM; ++r) send[s0 + r] = acc[r];
+        }
+      }
     }
     b0 = n0; b1 = n1;
   }
@@ -274,18 +284,30 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
                                                     const double* __restrict__ p, const double* __restrict__ t,
                                                     double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
                                                     const double* __restrict__ dinv, int nF, int mode,
-                                                    double* __restrict__ part_out, const double* __restrict__ w, int dist) {
+                                                    double* __restrict__ part_out, const double* __restrict__ w, int dist,
+                                                    const int* __restrict__ rowif_ptr, const int* __restrict__ rowif_idx,
+                                                    const double* __restrict__ recv) {
+  // multi-GPU (rowif_ptr != nullptr): the neighbours' parts of an interface row of t = L p arrive in recv
   __shared__ double sh[8];
   if (scal[2] != 0.0) return;
   const double alpha = scal[(iter + 1) & 1] / scal[7];
   double rr = 0.0, rz = 0.0;
   for (int gi = blockIdx.x * 256 + threadIdx.x; gi < nF; gi += gridDim.x * 256) {
-    double rv[DIM], zv[DIM];
+    double rv[DIM], zv[DIM], tv[DIM];
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) tv[k] = t[DIM * gi + k];
+    if (rowif_ptr) {
+      for (int j = rowif_ptr[gi]; j < rowif_ptr[gi + 1]; ++j) {
+        const int64_t s0 = (int64_t)DIM * rowif_idx[j];
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) tv[k] += recv[s0 + k];
+      }
+    }
 #pragma unroll
     for (int k = 0; k < DIM; ++k) {
       const int i = DIM * gi + k;
       x[i] += alpha * p[i];
-      rv[k] = r[i] - alpha * t[i];
+      rv[k] = r[i] - alpha * tv[k];
       r[i] = rv[k];
     }
     if (mode == 0) {
@@ -553,16 +575,26 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
     const unsigned gv = std::max(one, std::min(nblk(c->nF), (unsigned)kPcgBlocks));      // one vertex per thread
     const unsigned gn = std::max(one, std::min(nblk(n), (unsigned)kPcgBlocks));
     const unsigned gs = std::max(one, std::min(nblk((int64_t)c->nF * 16), (unsigned)kSpmvBlocks));
+    // multi-GPU with a partition set: the halo of t = L p goes point-to-point, written / read inside the CG kernels
+    const bool p2p = dist && c->use_p2p && c->ent_local.p;
+    double *hsend = nullptr, *hrecv = nullptr;
+    const int *rif_ptr = nullptr, *rif_idx = nullptr;
+    if (p2p) {
+      if ((rc = halo_buffers(c, c->dim, &hsend, &hrecv))) return rc;
+      rif_ptr = c->rowif_ptr.p; rif_idx = c->rowif_idx.p;
+    }
     int launched = 0, batch = 8;
     while (launched < max_iters) {
       const int nb = (max_iters - launched < batch) ? max_iters - launched : batch;
       for (int k = launched; k < launched + nb; ++k) {
-        if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
-        else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets);
-        // multi-GPU: t <- sum over ranks at the interface and p.t <- sum of the local p.(L_r p), one collective
-        if (dist && (rc = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1))) return rc;
-        if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0);
-        else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0);
+        if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+        else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+        // multi-GPU: t <- sum over ranks at the interface and p.t <- sum of the local p.(L_r p): one NCCL group
+        // (neighbour send / recv + the scalar), or one all-reduce over every shared vertex without a partition
+        if (p2p) { if ((rc = halo_exchange(c, c->dim, c->scal.p + 7, 1))) return rc; }
+        else if (dist && (rc = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1))) return rc;
+        if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
+        else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
         if (dist) {
           if ((rc = allreduce_scalars(c, c->scal.p + 8, 2, false))) return rc;
           k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);

@@ -4,8 +4,11 @@ The reference is a single-address-space OpenMP code; this is the 
 elements are split into contiguous slabs (sorted by centroid along the longest axis), every rank builds a LOCAL
 MixedStretch on its elements with locally renumbered vertices, and the only coupling is at vertices shared between
 slabs: the per-vertex vectors (grad_x_, rhs_, and matvec results of the sub-assembled matrix) are summed over ranks
-with ONE all-reduce on a packed interface buffer (NCCL over NVLink on GPUs, gloo in the CPU tests).  The assembled
-matrix is never exchanged: A = sum_r P_r^T A_r P_r is applied as local SpMV + interface sum.
+over ranks (NCCL over NVLink on GPUs: point-to-point with the neighbouring parts; gloo all-reduce in the CPU tests).
+The assembled matrix is never exchanged: A = sum_r P_r^T A_r P_r is applied as local SpMV + interface sum.
+
+The partitioner itself lives in the library (mfb_partition_create, csrc/mfb_partition.cu: host code behind the C ABI);
+`make_local` wraps it.  The numpy functions below restate the slab rule and are what the CPU tests check it against.
 """
 import numpy as np
 
@@ -80,10 +83,86 @@ def shared_free_vertices(T, free_map, parts, with_owner=False):
     return ids
 
 
-def make_local(V, T, free_map, nparts, rank):
+def make_local_numpy(V, T, free_map, nparts, rank):
+    """numpy restatement of the slab partition (kept as the cross-check of the library's partitioner in the tests)"""
     parts = partition_elements(V, T, nparts)
     shared, owner = shared_free_vertices(T, free_map, parts, with_owner=True)
     return LocalProblem(V, T, free_map, parts[rank], shared, owner, rank), parts, shared
+
+
+class CLocalProblem:
+    """This rank's part from the library's partitioner (mfb_partition_create, host code behind the C ABI): same
+    attributes as LocalProblem plus the per-neighbour lists and the interface-first element order."""
+
+    def __init__(self, V, T, free_map, nparts, rank, method=0):
+        import ctypes as C
+        from . import lib
+        L = lib()
+        V = np.ascontiguousarray(V, dtype=np.float64)
+        T = np.ascontiguousarray(T, dtype=np.int32)
+        fm = np.ascontiguousarray(free_map, dtype=np.int32)
+        L.mfb_partition_create.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32),
+                                           C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32]
+        L.mfb_partition_destroy.argtypes = [C.c_void_p]
+        L.mfb_partition_destroy.restype = None
+        L.mfb_partition_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        L.mfb_partition_get.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+        self._L = L
+        self.h = C.c_void_p()
+        rc = L.mfb_partition_create(C.byref(self.h), V.shape[1], T.shape[1], V.shape[0], T.shape[0], T.ctypes.data_as(C.POINTER(C.c_int32)),
+                                    V.ctypes.data_as(C.POINTER(C.c_double)), fm.ctypes.data_as(C.POINTER(C.c_int32)), nparts, rank, method)
+        if rc != 0:
+            raise RuntimeError("mfb_partition_create failed: %d %s" % (rc, L.mfb_last_error_string().decode()))
+        sizes = (C.c_int32 * 8)()
+        L.mfb_partition_sizes(self.h, sizes)
+        self.n_if_elems, self.n_shared = int(sizes[3]), int(sizes[4])
+        d, npe = V.shape[1], T.shape[1]
+
+        def get(what, dtype):
+            ptr, cnt = C.c_void_p(), C.c_int64()
+            L.mfb_partition_get(self.h, what, C.byref(ptr), C.byref(cnt))
+            if cnt.value == 0:
+                return np.zeros(0, dtype=dtype)
+            buf = (C.c_char * (cnt.value * np.dtype(dtype).itemsize)).from_address(ptr.value)
+            return np.frombuffer(buf, dtype=dtype).copy()
+        self.elems = get(0, np.int32).astype(np.int64)
+        self.vmap = get(1, np.int32).astype(np.int64)
+        self.T = get(2, np.int32).reshape(-1, npe)
+        self.V = get(3, np.float64).reshape(-1, d)
+        self.free_map = get(4, np.int32)
+        self.free_l2g = get(5, np.int64)
+        self.if_local = get(6, np.int32).astype(np.int64)
+        self.if_pos = get(7, np.int32).astype(np.int64)
+        self.dot_weight = get(8, np.float64)
+        self.nbr_rank = get(9, np.int32)
+        self.nbr_count = get(10, np.int32)
+        self.nbr_local = get(11, np.int32)
+        self.elem_part = get(12, np.int32)
+        self.rank, self.nparts = rank, nparts
+
+    restrict_vertex_vector = LocalProblem.restrict_vertex_vector
+    restrict_element_vector = LocalProblem.restrict_element_vector
+
+    def close(self):
+        if getattr(self, "h", None):
+            self._L.mfb_partition_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def make_local(V, T, free_map, nparts, rank, method=0):
+    """(this rank's part, list of element-index arrays of all parts, ascending global free ids of the shared vertices)
+    from the library's partitioner; method 0 = slabs along the longest axis, 1 = recursive coordinate bisection"""
+    loc = CLocalProblem(V, T, free_map, nparts, rank, method)
+    parts = [np.nonzero(loc.elem_part == q)[0] for q in range(nparts)]
+    fm = np.asarray(free_map)
+    shared = shared_free_vertices(np.asarray(T), fm, parts) if nparts > 1 else np.zeros(0, dtype=np.int64)
+    return loc, parts, shared
 
 
 def interface_sum_numpy(local, vec, dim, allreduce):
@@ -94,27 +173,3 @@ def interface_sum_numpy(local, vec, dim, allreduce):
     allreduce(buf)
     v[local.if_local] = buf[local.if_pos]
     return vec
-
-
-class TorchInterface:
-    """Device-side pack -> all_reduce -> unpack of interface entries for vectors living in HBM (torch is plumbing:
-    it owns the packed buffer and calls NCCL)."""
-
-    def __init__(self, local, dim, device):
-        import torch
-        self.torch = torch
-        self.dim = dim
-        self.idx_local = torch.as_tensor(local.if_local, device=device)
-        self.idx_pos = torch.as_tensor(local.if_pos, device=device)
-        self.buf = torch.zeros((local.n_shared, dim * 2), dtype=torch.float64, device=device)
-
-    def sum2(self, a, b):
-        """a, b: (nFl, dim) float64 tensors viewing grad_x_ and rhs_; one all-reduce for both."""
-        import torch.distributed as dist
-        d = self.dim
-        self.buf.zero_()
-        self.buf[self.idx_pos, :d] = a[self.idx_local]
-        self.buf[self.idx_pos, d:] = b[self.idx_local]
-        dist.all_reduce(self.buf)
-        a[self.idx_local] = self.buf[self.idx_pos, :d]
-        b[self.idx_local] = self.buf[self.idx_pos, d:]

@@ -35,3 +35,9 @@ def test_distributed_newton_step_matches_single_gpu(built):
     if _ngpu() < 2:
         pytest.skip("needs 2 GPUs")
     _torchrun("run_dist_newton.py", 2, 29533)
+
+
+def test_distributed_update_with_overlapped_exchange_matches_single_gpu(built):
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    _torchrun("run_dist_update.py", 2, 29535)
