@@ -370,7 +370,7 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   if (c->kind == MFB_TET) TRY(c->Lfac.alloc(NP * ld));
   TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
-  if (c->kind == MFB_TET) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 32)); TRY(c->gxrh.alloc((size_t)6 * nF + 32));   /* + the reduction sinks */ TRY(c->slow_list.alloc((size_t)nE + 1)); }
+  if (c->kind == MFB_TET) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 32 * kV4SinkSlots)); TRY(c->gxrh.alloc((size_t)6 * nF + 32 * kV4SinkSlots));   /* + the reduction sinks */ TRY(c->slow_list.alloc((size_t)nE + 1)); }
   TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));
   TRY(c->partials.alloc((size_t)c->grid() + 1024)); TRY(c->scal.alloc(16));
   TRY(c->soa_tmp.alloc(N * ld)); TRY(c->soa_tmp2.alloc(N * ld));

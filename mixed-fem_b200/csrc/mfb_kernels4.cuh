@@ -47,6 +47,7 @@ constexpr int kV4Warps = kV4Threads / 32;
 // [288,384) the 6 element->block codes per lane (int[6][32]), [384,448) fidx of the 4 local vertices (int[4][32]).
 // Codes and fidx stay in shared memory for the whole kernel: no registers, no spills, and their global loads are
 // cp.async issued at the top (ncu r1k: the late fidx loads + their spill stores were 10 % of all stall samples).
+constexpr int kV4SinkSlots = 128;          // x 32 doubles behind Ablk and behind gxrh
 constexpr int kV4RedDoubles = 32 * 9;
 constexpr int kV4StageDoubles = kV4RedDoubles + 96 + 64;
 constexpr int kV4SmemB = 54 * kV4Threads * (int)sizeof(double);
@@ -90,8 +91,10 @@ __device__ __forceinline__ void red_add_idx(double* base, int idx, double val) {
 // Every lane holds NV values for NV contiguous doubles at base[target .. target+NV) (target < 0: nothing to add).
 // The warp re-distributes them through its shared-memory buffer so that each RED instruction covers runs of NV
 // contiguous doubles with NV adjacent lanes.  All 32 lanes must call this.
-// `sink`: index of 32 scratch doubles behind the real targets of `base`; values without a target are added there (one
-// slot per lane), which keeps the reduction unconditional: ncu r1k showed a BSSY/BRA/BSYNC triple and a
+// `sink`: index of 32 scratch doubles behind the real targets of `base` (one of kV4SinkSlots groups, picked by the warp's
+// element range: the pinned face of a mesh sends ~2M reductions there, and FP64 reductions on ONE address retire at
+// about 16 ns each - with a single group of 32 the rank holding the pinned face of the 8-GPU run took 1.5 ms instead of
+// 0.6); values without a target are added there, which keeps the reduction unconditional: ncu r1k showed a BSSY/BRA/BSYNC triple and a
 // branch_resolving stall around every predicated RED, and every RED waiting on the shared-memory load issued right
 // before it - here all values are fetched first, then the NV reductions go out back to back.
 // `live` false (the lane's element went to the Jacobi tail list, or is grid padding): the lane adds 0.0 to its own
@@ -112,7 +115,7 @@ __device__ __forceinline__ void coop_red(double* __restrict__ base, const double
     const int b = q / NV, i = q - b * NV;
     const int t = sC[b];
     val[it] = sW[q];
-    idx[it] = (t >= 0) ? t + i : sink + lane;
+    idx[it] = (t >= 0) ? t + i : sink + lane;       // sink: already offset by the caller's warp slot (kV4SinkSlots x 32 doubles)
   }
 #pragma unroll
   for (int it = 0; it < NV; ++it) red_add_idx(base, idx[it], val[it]);
@@ -330,6 +333,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   // ---- 3 : vertex vectors, and B <- sqrt(vol) B L in place (one row at a time through registers)
   int f[4];
   double tl[6];
+  const int sink_ofs = ((e >> 5) & (kV4SinkSlots - 1)) * 32;
   const int* sI = reinterpret_cast<const int*>(sW + kV4RedDoubles);          // codes, fidx: read where they are used
   const int* sF = reinterpret_cast<const int*>(sW + kV4RedDoubles + 96);
   if (ASM == 1) {
@@ -388,7 +392,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
           }
         }
       } else {
-        if (!(m.exp & 2)) coop_red<6>(as.gxrh, vv, (fk >= 0 && inrange) ? 6 * fk : -1, live, sW, sC, lane, as.sinkV);
+        if (!(m.exp & 2)) coop_red<6>(as.gxrh, vv, (fk >= 0 && inrange) ? 6 * fk : -1, live, sW, sC, lane, as.sinkV + sink_ofs);
       }
     }
     if (ASM == 0) {
@@ -401,7 +405,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       }
     } else {
       const int f0 = sF[lane];
-      if (!(m.exp & 2)) coop_red<6>(as.gxrh, v0, (f0 >= 0 && inrange) ? 6 * f0 : -1, live, sW, sC, lane, as.sinkV);
+      if (!(m.exp & 2)) coop_red<6>(as.gxrh, v0, (f0 >= 0 && inrange) ? 6 * f0 : -1, live, sW, sC, lane, as.sinkV + sink_ofs);
     }
   }
 
@@ -478,7 +482,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
         for (int r = 0; r < 3; ++r)
 #pragma unroll
           for (int c = 0; c < 3; ++c) v[3 * r + c] = tr ? a[c][r] : a[r][c];
-        if (!(m.exp & 2)) coop_red<9>(as.Ablk, v, (cd >= 0 && inrange) ? 9 * (cd >> 1) : -1, live, sW, sC, lane, as.sinkA);
+        if (!(m.exp & 2)) coop_red<9>(as.Ablk, v, (cd >= 0 && inrange) ? 9 * (cd >> 1) : -1, live, sW, sC, lane, as.sinkA + sink_ofs);
       }
     }
   }
