@@ -25,6 +25,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "profile")) { c->profile = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "update_exchange")) { c->update_exchange = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "p2p")) { c->use_p2p = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "cg_graph")) { c->cg_graph = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch, 3 v4 (default)
   if (!strcmp(name, "exp")) { c->exp = value; return MFB_OK; }
   if (!strcmp(name, "cg_zero_guess")) { c->cg_zero_guess = value ? 1 : 0; return MFB_OK; }

@@ -341,8 +341,8 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
       else {
         scal[5] = rr2;
         scal[iter & 1] = rz2;
-        if (rr2 < scal[6]) { scal[2] = 1.0; scal[3] = (double)iter; }
-        else scal[3] = (double)(iter + 1);
+        if (rr2 < scal[6]) scal[2] = 1.0;       // the reference breaks before counting this iteration
+        else scal[3] += 1.0;                    // completed iterations, counted on the device (CUDA-graph replays)
       }
     }
   }
@@ -368,8 +368,8 @@ __global__ void __launch_bounds__(256) k_pcg_dir_dist(double* __restrict__ scal,
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     scal[5] = rr;
-    if (conv) { scal[2] = 1.0; scal[3] = (double)iter; }
-    else { scal[iter & 1] = rz; scal[3] = (double)(iter + 1); }
+    if (conv) scal[2] = 1.0;
+    else { scal[iter & 1] = rz; scal[3] += 1.0; }
   }
 }
 // weighted two-stage dots (w per vertex, dim entries each)
@@ -583,24 +583,57 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
       if ((rc = halo_buffers(c, c->dim, &hsend, &hrecv))) return rc;
       rif_ptr = c->rowif_ptr.p; rif_idx = c->rowif_idx.p;
     }
+    // One CG iteration = 3 launches (+ 2 NCCL groups on several GPUs).  The kernels only depend on the PARITY of the
+    // iteration number (the count itself lives in scal[3]), so an even number of iterations is captured ONCE per solve into a
+    // CUDA graph and replayed: no per-launch host cost, which is what a small per-GPU problem is made of (8 GPUs, 1M
+    // tets: 68 us per iteration enqueued from the host against ~15 us of kernels).  The first iterations run eagerly (NCCL
+    // sets up its connections on first use, which cannot be captured); a failed capture falls back to the eager loop.
+    auto enqueue_iteration = [&](int k) -> int {
+      if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+      else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+      // multi-GPU: t <- sum over ranks at the interface and p.t <- sum of the local p.(L_r p): one NCCL group
+      // (neighbour send / recv + the scalar), or one all-reduce over every shared vertex without a partition
+      int e = MFB_OK;
+      if (p2p) e = halo_exchange(c, c->dim, c->scal.p + 7, 1);
+      else if (dist) e = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1);
+      if (e) return e;
+      if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
+      else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
+      if (dist) {
+        if ((e = allreduce_scalars(c, c->scal.p + 8, 2, false))) return e;
+        k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
+      } else {
+        k_pcg_dir<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
+      }
+      return MFB_OK;
+    };
     int launched = 0, batch = 8;
+    cudaGraphExec_t gexec = nullptr;
+    const int gbatch = 32;                           // iterations per graph launch (even)
+    bool try_graph = c->cg_graph != 0 && max_iters >= 3 * gbatch;
     while (launched < max_iters) {
-      const int nb = (max_iters - launched < batch) ? max_iters - launched : batch;
-      for (int k = launched; k < launched + nb; ++k) {
-        if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
-        else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
-        // multi-GPU: t <- sum over ranks at the interface and p.t <- sum of the local p.(L_r p): one NCCL group
-        // (neighbour send / recv + the scalar), or one all-reduce over every shared vertex without a partition
-        if (p2p) { if ((rc = halo_exchange(c, c->dim, c->scal.p + 7, 1))) return rc; }
-        else if (dist && (rc = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1))) return rc;
-        if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
-        else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
-        if (dist) {
-          if ((rc = allreduce_scalars(c, c->scal.p + 8, 2, false))) return rc;
-          k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
-        } else {
-          k_pcg_dir<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
+      if (try_graph && !gexec && launched >= 8 && max_iters - launched >= gbatch) {
+        cudaGraph_t graph = nullptr;
+        bool okc = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+        if (okc) {
+          int e = MFB_OK;
+          for (int k = launched; k < launched + gbatch && !e; ++k) e = enqueue_iteration(k);      // launched is even here
+          const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+          okc = !e && ce == cudaSuccess && graph;
         }
+        if (okc) okc = cudaGraphInstantiate(&gexec, graph, 0) == cudaSuccess;
+        if (graph) cudaGraphDestroy(graph);
+        if (!okc) { gexec = nullptr; try_graph = false; (void)cudaGetLastError(); }
+      }
+      int nb;
+      if (gexec && max_iters - launched >= gbatch) {
+        nb = gbatch;
+        MFB_CUDA(cudaGraphLaunch(gexec, st));
+      } else {
+        nb = (max_iters - launched < batch) ? max_iters - launched : batch;
+        if (gexec || try_graph) nb = std::min(nb, 8);                 // keep `launched` even and the eager prefix short
+        for (int k = launched; k < launched + nb; ++k)
+          if ((rc = enqueue_iteration(k))) { if (gexec) cudaGraphExecDestroy(gexec); return rc; }
       }
       launched += nb;
       c->launches += 3 * nb;
@@ -609,6 +642,7 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
       if (c->h_scal[2] != 0.0) break;
       if (batch < 64) batch *= 2;
     }
+    if (gexec) cudaGraphExecDestroy(gexec);
     it = (int)c->h_scal[3];
     resNorm2 = c->h_scal[5];
   }
