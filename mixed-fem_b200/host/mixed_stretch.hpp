@@ -72,10 +72,10 @@ class MixedStretch {
     check(mfb_reset(ctx_, nullptr));
     s_.resize((size_t)N() * nelem_); ds_.assign((size_t)N() * nelem_, 0.0); la_.assign((size_t)N() * nelem_, 0.0);
     check(mfb_get(ctx_, MFB_F_S, s_.data()));
-    s_dev_ = s_; la_dev_ = la_;
+    s_dirty_ = false; la_dirty_ = false;
   }
   void pre_solve() {}
-  void post_solve() { la_.assign(la_.size(), 0.0); }                       // mixed_stretch.cpp:340-343
+  void post_solve() { la_.assign(la_.size(), 0.0); check(mfb_post_solve(ctx_)); la_dirty_ = false; }   // mixed_stretch.cpp:340-343
   std::vector<double> rhs() {
     push_state();
     std::vector<double> r((size_t)DIM * nfree_); check(mfb_rhs(ctx_, r.data())); return r;
@@ -88,11 +88,16 @@ class MixedStretch {
     check(mfb_solve(ctx_, dx.data()));
     check(mfb_get(ctx_, MFB_F_DS, ds_.data()));
     check(mfb_get(ctx_, MFB_F_LA, la_.data()));
-    la_dev_ = la_;
+    la_dirty_ = false;
   }
+  // The reference hands these out by non-const reference and its callers write through them (linesearch.h:120-125,
+  // linear_system.h:97,189).  A non-const access marks the host copy as newer than the device's; the next call that reads
+  // the state uploads it once (no O(nE) comparison per call).  const access does not.
   std::vector<double>& delta() { return ds_; }
-  std::vector<double>& value() { return s_; }
-  std::vector<double>& lambda() { return la_; }
+  std::vector<double>& value() { s_dirty_ = true; return s_; }
+  std::vector<double>& lambda() { la_dirty_ = true; return la_; }
+  const std::vector<double>& value() const { return s_; }
+  const std::vector<double>& lambda() const { return la_; }
   int size() const { return N() * nelem_; }
   int size_dual() const { return N() * nelem_; }
   std::vector<double> max_stresses() { return get(MFB_F_EVALS); }
@@ -141,16 +146,16 @@ class MixedStretch {
   std::vector<double> get(int f) {
     std::vector<double> v((size_t)mfb_field_size(ctx_, f)); check(mfb_get(ctx_, f, v.data())); return v;
   }
-  // value()/lambda() are handed out by reference: upload them when they differ from what the device holds
+  // value()/lambda() were handed out by non-const reference since the last upload: push them to the device
   void push_state() {
-    if (s_ != s_dev_) { check(mfb_set(ctx_, MFB_F_S, s_.data())); s_dev_ = s_; }
-    if (la_ != la_dev_) { check(mfb_set(ctx_, MFB_F_LA, la_.data())); la_dev_ = la_; }
+    if (s_dirty_) { check(mfb_set(ctx_, MFB_F_S, s_.data())); s_dirty_ = false; }
+    if (la_dirty_) { check(mfb_set(ctx_, MFB_F_LA, la_.data())); la_dirty_ = false; }
   }
   mfb_ctx* ctx_ = nullptr;
   int32_t nelem_ = 0, nfree_ = 0;
   int64_t nnz_ = 0;
-  std::vector<double> s_, ds_, la_, s_dev_, la_dev_, lhs_vals_;
-  bool lhs_valid_ = false;
+  std::vector<double> s_, ds_, la_, lhs_vals_;
+  bool lhs_valid_ = false, s_dirty_ = false, la_dirty_ = false;
 };
 
 // The linear solve of the condensed system as the reference's solver factory names it (linear_solver_factory.cpp:107-173):
@@ -177,6 +182,12 @@ class NewtonStep {
   NewtonStep(MixedStretch<DIM>& var, const MeshView& mesh, double density, double h, const double* force = nullptr,
              const double* x0 = nullptr, const double* v0 = nullptr) : var_(var), nx_((size_t)DIM * mesh.nV) {
     check(mfb_newton_init(var_.ctx(), mesh.free_map, density, h, force, x0, v0));
+  }
+  // one density per ELEMENT: the density of the material each element's OBJECT was created with (meshes.cpp:100-108)
+  NewtonStep(MixedStretch<DIM>& var, const MeshView& mesh, const std::vector<double>& density_e, double h, const double* force = nullptr,
+             const double* x0 = nullptr, const double* v0 = nullptr) : var_(var), nx_((size_t)DIM * mesh.nV) {
+    if ((int)density_e.size() != mesh.nE) throw std::runtime_error("NewtonStep: one density per element expected");
+    check(mfb_newton_init_density(var_.ctx(), mesh.free_map, density_e.data(), h, force, x0, v0));
   }
   ~NewtonStep() { mfb_newton_free(var_.ctx()); }
   // one time step; returns the OptimizerData columns (newton_optimizer.cpp:92-97)

@@ -231,3 +231,8 @@ def test_host_cpp_shim_compiles_and_links(built, tmp_path):
                         "-Wl,-rpath," + libdir, "-L/usr/local/cuda/lib64", "-Wl,-rpath-link,/usr/local/cuda/lib64"],
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
+    # the program that actually RUNS the shim on the GPU box (tests/test_gpu_cpp_shim.py) must build here too
+    r = subprocess.run([cxx, "-std=c++17", "-I", ROOT, os.path.join(ROOT, "tests", "harness", "shim_run.cpp"), "-o", str(tmp_path / "shim_run"),
+                        "-L", libdir, "-lmfem_b200", "-Wl,-rpath," + libdir, "-L/usr/local/cuda/lib64", "-Wl,-rpath-link,/usr/local/cuda/lib64"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
