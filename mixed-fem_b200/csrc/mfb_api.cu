@@ -29,7 +29,11 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch, 3 v4 (default)
   if (!strcmp(name, "exp")) { c->exp = value; return MFB_OK; }
   if (!strcmp(name, "cg_zero_guess")) { c->cg_zero_guess = value ? 1 : 0; return MFB_OK; }
-  if (!strcmp(name, "asm_mode")) { c->asm_mode = value ? 1 : 0; return MFB_OK; }   // v4: 1 bulk reductions into block-CSR, 0 RED into scalar CSR
+  if (!strcmp(name, "asm_mode")) {   // v4: 1 bulk reductions into block-CSR, 0 RED into scalar CSR, 2 deterministic gather
+    if (value < 0 || value > 2) return MFB_ERR_INVALID;
+    c->asm_mode = value;
+    return MFB_OK;
+  }
   g_last_error = "unknown option";
   return MFB_ERR_INVALID;
 }
@@ -115,8 +119,12 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     MFB_CUDA(cudaMemcpyAsync(c->xupd.p, x_dev, (size_t)c->dim * c->nV * 8, cudaMemcpyDeviceToDevice, st));
   const bool v4 = c->kind == MFB_TET && c->smem_b == 3;
   const bool bulk = v4 && c->asm_mode == 1;
+  const bool det = v4 && c->asm_mode == 2;
+  if (det) { int rcd = build_det_lists(c); if (rcd) return rcd; }
   MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
-  if (bulk) {
+  if (det) {
+    // every CSR value and every vertex entry is WRITTEN by the gather kernels: nothing to zero
+  } else if (bulk) {
     MFB_CUDA(cudaMemsetAsync(c->gxrh.p, 0, (size_t)6 * c->nF * 8, st));
     if (c->nbu) MFB_CUDA(cudaMemsetAsync(c->Ablk.p, 0, (size_t)c->nbu * 9 * 8, st));
   } else {
@@ -154,11 +162,24 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       attr4_done = true;
     }
     const int grid4 = (c->nE + kV4Threads - 1) / kV4Threads;
     const int tail_grid = grid4 < 148 * MFB_V4_MINB ? grid4 : 148 * MFB_V4_MINB;
-    if (bulk) {
+    if (det) {
+      // deterministic mode: the element kernel stores its blocks / vertex values, two gather kernels sum them in a fixed
+      // order per CSR block and per vertex (no atomics anywhere: two runs give bit-identical results)
+      if (c->fuse_rhs) { k_update_tet_v4<true, 2><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 2><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      else { k_update_tet_v4<false, 2><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<false, 2><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
+      if (c->nF > 0) k_det_gather_vec<<<nblk(c->nF), 256, 0, st>>>(c->det_vptr.p, c->det_vent.p, c->nF, c->Velem.p, c->grad_x.p, c->rhs.p, c->fuse_rhs);
+      if (c->ev_vec) { MFB_CUDA(cudaEventRecord(c->ev_vec, st)); vec_recorded = true; }
+      if (c->nb > 0) k_det_gather_blocks<<<nblk(c->nb), 256, 0, st>>>(c->blockptr.p, c->brow.p, c->det_bptr.p, c->det_bent.p, c->nb, c->Kelem.p, c->Avals.p);
+      LAUNCHED(c, 3);
+    } else if (bulk) {
       if (c->x_host_chunked && c->nE >= (1 << 18)) {
         // host positions: upload x in pieces on the copy stream and start each element chunk when its vertices are there
         const double* xh = c->x_host_chunked;
@@ -264,7 +285,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   }
-  if (c->kind == MFB_TET && c->nb > 0 && !bulk) {   // RED variants accumulate the upper triangle only
+  if (c->kind == MFB_TET && c->nb > 0 && !bulk && !det) {   // RED variants accumulate the upper triangle only
     k_mirror_lower<<<nblk((int64_t)c->n_mirror * 9), 256, 0, st>>>(c->mirror.p, c->n_mirror, 3, c->Avals.p);
     LAUNCHED(c, 1);
   }

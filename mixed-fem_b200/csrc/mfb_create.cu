@@ -227,6 +227,63 @@ static int build_pattern(mfb_ctx* c) {
   return MFB_OK;
 }
 
+// ---- deterministic assembly lists (asm_mode 2) ----
+__global__ void k_vert_keys(const int* __restrict__ fidx, int nE, int64_t ld, int* keys, int* vals) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (int64_t)nE * 4) return;
+  const int e = (int)(q >> 2), k = (int)(q & 3);
+  const int f = fidx[k * ld + e];
+  keys[q] = f < 0 ? INT_MAX : f;
+  vals[q] = (int)q;
+}
+__global__ void k_head_positions(const int* __restrict__ head, const int* __restrict__ bid, int64_t n, int nb, int* bptr) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (head[i]) bptr[bid[i] - 1] = (int)i;
+  if (i == n - 1) bptr[nb] = (int)n;
+}
+
+int build_det_lists(mfb_ctx* c) {
+  if (c->det_ready) return MFB_OK;
+  if (c->kind != MFB_TET) { g_last_error = "asm_mode 2 is implemented for tetrahedra"; return MFB_ERR_UNSUPPORTED; }
+  const int nE = c->nE, nF = c->nF, nb = c->nb;
+  const int64_t np = (int64_t)nE * 16;
+  if (np > (int64_t)INT_MAX) { g_last_error = "asm_mode 2: contribution list exceeds int32"; return MFB_ERR_TOO_LARGE; }
+  cudaStream_t st = c->stream;
+  auto pol = thrust::cuda::par.on(st);
+  int rc;
+  {   // matrix: all (e, j, k) with both vertices free, grouped by CSR block, ascending p = 16 e + 4 j + k inside a block
+    DBuf<long long> keys; DBuf<int> head, bid;
+    if ((rc = keys.alloc(np)) || (rc = c->det_bent.alloc(np)) || (rc = head.alloc(np)) || (rc = bid.alloc(np)) || (rc = c->det_bptr.alloc((size_t)nb + 1))) return rc;
+    k_pair_keys<<<nblk(np), 256, 0, st>>>(c->fidx.p, 4, nE, c->ld, nF, keys.p, c->det_bent.p);
+    thrust::stable_sort_by_key(pol, thrust::device_ptr<long long>(keys.p), thrust::device_ptr<long long>(keys.p + np), thrust::device_ptr<int>(c->det_bent.p));
+    const int64_t nvalid = thrust::lower_bound(pol, thrust::device_ptr<long long>(keys.p), thrust::device_ptr<long long>(keys.p + np), KEY_INVALID) -
+                           thrust::device_ptr<long long>(keys.p);
+    if (nvalid > 0) {
+      k_heads<<<nblk(nvalid), 256, 0, st>>>(keys.p, nvalid, head.p);
+      thrust::inclusive_scan(pol, thrust::device_ptr<int>(head.p), thrust::device_ptr<int>(head.p + nvalid), thrust::device_ptr<int>(bid.p));
+      k_head_positions<<<nblk(nvalid), 256, 0, st>>>(head.p, bid.p, nvalid, nb, c->det_bptr.p);
+    } else {
+      MFB_CUDA(cudaMemsetAsync(c->det_bptr.p, 0, ((size_t)nb + 1) * 4, st));
+    }
+    MFB_CUDA(cudaStreamSynchronize(st));
+  }
+  {   // vectors: all (e, k) with a free vertex, grouped by free vertex, ascending q = 4 e + k
+    const int64_t nq = (int64_t)nE * 4;
+    DBuf<int> keys;
+    if ((rc = keys.alloc(nq)) || (rc = c->det_vent.alloc(nq)) || (rc = c->det_vptr.alloc((size_t)nF + 1))) return rc;
+    k_vert_keys<<<nblk(nq), 256, 0, st>>>(c->fidx.p, nE, c->ld, keys.p, c->det_vent.p);
+    thrust::stable_sort_by_key(pol, thrust::device_ptr<int>(keys.p), thrust::device_ptr<int>(keys.p + nq), thrust::device_ptr<int>(c->det_vent.p));
+    thrust::lower_bound(pol, thrust::device_ptr<int>(keys.p), thrust::device_ptr<int>(keys.p + nq), thrust::counting_iterator<int>(0),
+                        thrust::counting_iterator<int>(nF + 1), thrust::device_ptr<int>(c->det_vptr.p));
+    MFB_CUDA(cudaStreamSynchronize(st));
+  }
+  if ((rc = c->Kelem.alloc((size_t)nE * 54 + 1)) || (rc = c->Velem.alloc((size_t)nE * 24 + 1))) return rc;
+  MFB_CUDA(cudaGetLastError());
+  c->det_ready = true;
+  return MFB_OK;
+}
+
 template <typename T>
 static int upload(DBuf<T>& d, const std::vector<T>& h, cudaStream_t st) {
   int rc = d.alloc(h.size());

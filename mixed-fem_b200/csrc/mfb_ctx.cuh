@@ -64,6 +64,7 @@ struct NewtonView {
 void phase_begin(mfb_ctx* c, int key);                            // mfb_api.cu
 void phase_end(mfb_ctx* c, int key);
 int partition_view(const mfb_partition* p, PartitionView* v);      // mfb_partition.cu
+int build_det_lists(mfb_ctx* c);                                  // mfb_create.cu (asm_mode 2)
 // point-to-point halo of the CG (mfb_dist.cu): group{ send/recv of the packed interface rows ; all-reduce of `ns` scalars }
 int halo_exchange(mfb_ctx* c, int ncomp, double* scal, int ns);
 int halo_buffers(mfb_ctx* c, int ncomp, double** send, double** recv);
@@ -86,7 +87,8 @@ struct mfb_ctx {
   int assembly = 0;
   int smem_b = 3;       // update kernel variant: 3 = k_update_tet_v4 (default), 0/1/2 = the earlier register / shared-memory / fused variants
   int exp = 0;
-  int asm_mode = 1;     // v4 assembly: 1 = warp-cooperative coalesced RED into the block-CSR upper triangle, 0 = FP64 RED into the scalar CSR
+  int asm_mode = 1;     // v4 assembly: 1 = warp-cooperative coalesced RED into the block-CSR upper triangle, 0 = FP64 RED into the scalar CSR,
+                        // 2 = deterministic owner-computes gather (no atomics; bit-identical from run to run)
   // mesh (device)
   mfb::DBuf<int> T, fidx, matid, smap, sstride;
   mfb::DBuf<double> dphi, vol, vref, nrest, xupd;   // xupd: shells, positions of the last update()
@@ -100,6 +102,12 @@ struct mfb_ctx {
   mfb::DBuf<double> Ablk, gxrh;
   mfb::DBuf<int> bmap, slow_list;
   mfb::DBuf<int> fcode;       // per block: 2 * upper block + transposed
+  // deterministic assembly (asm_mode 2, built on first use): per CSR block the (element, local pair) contributions in ascending
+  // element order - the reference Assembler's own structure (sparse_utils.cpp:58-99) - per free vertex its (element, local
+  // vertex) incidences, and the per-element scratch the gather kernels read (6 off-diagonal 3x3 blocks, 4 x 6 vertex values)
+  mfb::DBuf<int> det_bptr, det_bent, det_vptr, det_vent;
+  mfb::DBuf<double> Kelem, Velem;
+  bool det_ready = false;
   int nbu = 0;
   // state (device)
   mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals, Lfac;
@@ -181,6 +189,7 @@ struct mfb_ctx {
     mfb::DevAsm a;
     a.Ablk = Ablk.p; a.gxrh = gxrh.p; a.bmap = bmap.p; a.slow_list = slow_list.p;
     a.sinkA = nbu * 9; a.sinkV = 6 * nF;
+    a.Kelem = Kelem.p; a.Velem = Velem.p;
     return a;
   }
   int grid() const { return (nE + 127) / 128; }

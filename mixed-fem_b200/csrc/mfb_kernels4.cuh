@@ -59,6 +59,7 @@ struct DevAsm {
   const int* bmap;       // [6][ld]   pairs j < k: 2*upper_block + transposed; one vertex pinned: the free vertex's diagonal slot; both: -1
   int* slow_list;        // [nE]
   int sinkA, sinkV;      // first of 32 scratch doubles behind Ablk / gxrh (reductions without a target land there)
+  double *Kelem, *Velem; // ASM 2: [nE][54] off-diagonal blocks K_e(j,k), j < k, row-major ; [nE][4][6] vertex values (grad_x | rhs)
 };
 
 __device__ __forceinline__ void cp_async8(void* sdst, const void* gsrc) {
@@ -150,7 +151,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   const double vol = __ldcs(&m.vol[e]);
   // step-3 inputs (la, element->block codes) start moving now, asynchronously and without registers, into the warp's
   // reduction buffer, which is idle until step 3: layout la[n] at sW[n*32 + lane], code[q] at int(sW + 192)[q*32 + lane]
-  if (ASM == 1) {
+  if (ASM >= 1) {
     __syncwarp();     // tail kernel: the previous element's last reduction round has finished reading the buffer
 #pragma unroll
     for (int n = 0; n < 6; ++n) cp_async8(&sW[n * 32 + lane], &st.la[n * ld + e]);
@@ -179,6 +180,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   // An FP64 reduction whose line is not in the L2 waits for the DRAM fill and, behind it, so does everything else in
   // the SM's memory pipe: without this the reductions cost 1.6 ms per 10M tets, with it 0.7 ms.  (The vertex targets
   // are L2-resident already; prefetching them, a second line per block, or the next CTAs' inputs measured slower.)
+  if (ASM == 2) asm volatile("cp.async.wait_all;" ::: "memory");
   if (ASM == 1) {
     asm volatile("cp.async.wait_all;" ::: "memory");
     const int* sI = reinterpret_cast<const int*>(sW + kV4RedDoubles);
@@ -336,7 +338,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   const int sink_ofs = ((e >> 5) & (kV4SinkSlots - 1)) * 32;
   const int* sI = reinterpret_cast<const int*>(sW + kV4RedDoubles);          // codes, fidx: read where they are used
   const int* sF = reinterpret_cast<const int*>(sW + kV4RedDoubles + 96);
-  if (ASM == 1) {
+  if (ASM >= 1) {
     asm volatile("cp.async.wait_all;" ::: "memory");
 #pragma unroll
     for (int n = 0; n < 6; ++n) tl[n] = ((n < 3) ? 1.0 : 2.0) * sW[n * 32 + lane];
@@ -360,7 +362,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
 #endif
     for (int k = 0; k < 3; ++k) {
-      const int fk = (ASM == 1) ? sF[(k + 1) * 32 + lane] : ((k == 0) ? f[1] : (k == 1) ? f[2] : f[3]);
+      const int fk = (ASM >= 1) ? sF[(k + 1) * 32 + lane] : ((k == 0) ? f[1] : (k == 1) ? f[2] : f[3]);
       double vv[6];
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
@@ -391,6 +393,11 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
             if (FUSE_RHS) red_add(&st.rhs[3 * (int64_t)fk + r], vv[3 + r]);
           }
         }
+      } else if (ASM == 2) {          // deterministic mode: the element's own slot, summed per vertex by k_det_gather_vec
+        if (live) {
+#pragma unroll
+          for (int i = 0; i < 6; ++i) as.Velem[(int64_t)e * 24 + (k + 1) * 6 + i] = vv[i];
+        }
       } else {
         if (!(m.exp & 2)) coop_red<6>(as.gxrh, vv, (fk >= 0 && inrange) ? 6 * fk : -1, live, sW, sC, lane, as.sinkV + sink_ofs);
       }
@@ -402,6 +409,11 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
           red_add(&st.grad_x[3 * (int64_t)f[0] + r], v0[r]);
           if (FUSE_RHS) red_add(&st.rhs[3 * (int64_t)f[0] + r], v0[3 + r]);
         }
+      }
+    } else if (ASM == 2) {
+      if (live) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) as.Velem[(int64_t)e * 24 + i] = v0[i];
       }
     } else {
       const int f0 = sF[lane];
@@ -475,6 +487,16 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
             for (int n = 0; n < 6; ++n) t += bj[r][n] * bk[n];
             a[r][c] = t;
           }
+        }
+        if (ASM == 2) {             // deterministic mode: K_e(j,k) as computed, row-major, gathered per CSR block later
+          if (live) {
+            double* dst = as.Kelem + (int64_t)e * 54 + pair6(j, k) * 9;
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+              for (int c = 0; c < 3; ++c) dst[3 * r + c] = a[r][c];
+          }
+          continue;
         }
         const bool tr = (cd & 1) != 0;     // the stored block is (g_k, g_j): park the transpose
         double v[9];
@@ -566,6 +588,70 @@ static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restr
 }
 
 static __global__ void k_mark_tail(unsigned long long* counters) { counters[6] = counters[5]; }
+
+// ---- deterministic assembly (asm_mode 2): owner-computes gather, the reference's own structure (sparse_utils.cpp:124-170:
+// one block-row per OpenMP iteration, contributions summed in a fixed order, no atomics).  One thread per CSR block: its
+// contributions (element, local pair) in ascending element order; the diagonal pair (j,j) of an element is minus the sum
+// of its three off-diagonal blocks of row j (zero block-row sums of the element matrix), taken in ascending m.
+static __global__ void __launch_bounds__(256) k_det_gather_blocks(const int* __restrict__ blockptr, const int* __restrict__ brow,
+                                                                  const int* __restrict__ bptr, const int* __restrict__ bent, int nb,
+                                                                  const double* __restrict__ Kelem, double* __restrict__ A) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  double acc[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) acc[i] = 0.0;
+  for (int i = bptr[b]; i < bptr[b + 1]; ++i) {
+    const int p = bent[i];
+    const int e = p >> 4, j = (p >> 2) & 3, k = p & 3;
+    const double* K = Kelem + (int64_t)e * 54;
+    if (j < k) {
+      const double* q = K + pair6(j, k) * 9;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) acc[t] += q[t];
+    } else if (j > k) {
+      const double* q = K + pair6(k, j) * 9;
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) acc[3 * r + c] += q[3 * c + r];
+    } else {
+      for (int m2 = 0; m2 < 4; ++m2) {
+        if (m2 == j) continue;
+        if (m2 > j) {
+          const double* q = K + pair6(j, m2) * 9;
+#pragma unroll
+          for (int t = 0; t < 9; ++t) acc[t] -= q[t];
+        } else {
+          const double* q = K + pair6(m2, j) * 9;
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) acc[3 * r + c] -= q[3 * c + r];
+        }
+      }
+    }
+  }
+  const int gi = brow[b], p0 = blockptr[gi], rowlen = 3 * (blockptr[gi + 1] - p0), rank = b - p0;
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) A[9 * (int64_t)p0 + (int64_t)r * rowlen + 3 * rank + c] = acc[3 * r + c];
+}
+static __global__ void __launch_bounds__(256) k_det_gather_vec(const int* __restrict__ vptr, const int* __restrict__ vent, int nF,
+                                                               const double* __restrict__ Velem, double* __restrict__ gx, double* __restrict__ rh, int with_rhs) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nF) return;
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  for (int i = vptr[v]; i < vptr[v + 1]; ++i) {
+    const int q = vent[i];
+    const double* s = Velem + (int64_t)(q >> 2) * 24 + (q & 3) * 6;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) acc[t] += s[t];
+  }
+#pragma unroll
+  for (int r = 0; r < 3; ++r) { gx[3 * (int64_t)v + r] = acc[r]; if (with_rhs) rh[3 * (int64_t)v + r] = acc[3 + r]; }
+}
 
 static __global__ void __launch_bounds__(256) k_deinterleave_vec(const double* __restrict__ gxrh, int nF, double* __restrict__ gx, double* __restrict__ rh, int with_rhs) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -29,6 +29,8 @@ def _run(dim, model, n, h, steps=2, outer=3, pin=0.01):
     ont = onewton.OracleNewton(cpu, V, T, fm, density=1000.0, h=h)
     gpu.newton_init(density=1000.0, h=h)
     gpu.set_option("cg_zero_guess", 1)        # the oracle solves exactly; see the note on the guess in mfb_newton.cu
+    if dim == 3:
+        gpu.set_option("asm_mode", 2)         # deterministic assembly: the history is bit-reproducible from run to run
     for _ in range(steps):
         lo = ont.step(outer_steps=outer, newton_tol=1e-10)
         lg = gpu.newton_step(outer_steps=outer, newton_tol=1e-10, precond=2, cg_tol=1e-13, cg_max_iters=5000)

@@ -86,7 +86,7 @@ def test_update_parity_irregular_mesh_heterogeneous_materials(built):
     gpu.close()
 
 
-@pytest.mark.parametrize("variant,asm", [(3, 1), (3, 0), (1, 0), (0, 0), (2, 0)])
+@pytest.mark.parametrize("variant,asm", [(3, 1), (3, 2), (3, 0), (1, 0), (0, 0), (2, 0)])
 def test_update_kernel_variants_agree_with_oracle(built, variant, asm):
     """every update-kernel variant the library can select (option smem_b / asm_mode): default = v4 with bulk-reduction
     assembly; the mesh is irregular with pinned vertices; about a third of the elements get an indefinite Hessian so
@@ -345,4 +345,43 @@ def test_explicit_jacobian_x_matches_the_products(built, kind):
         assert vec_rel(J @ xe, a) <= 1e-11
         b = o.product("jacobian_x", xv, np.zeros(N * nE), transposed=False)
         assert vec_rel(J.T @ xv, b) <= 1e-11
+    gpu.close()
+
+
+def test_deterministic_assembly_is_bit_stable_and_matches_the_oracle(built):
+    """asm_mode 2: owner-computes gather per CSR block and per vertex in ascending element order - the reference's own
+    structure (sparse_utils.cpp:124-170, no atomics).  Two contexts, repeated updates: np.array_equal on the CSR values
+    and the vertex vectors (the RED modes agree only to rounding), and the usual 1e-10 against the oracle.  Irregular mesh,
+    pinned vertices, a third of the Hessians on the Jacobi tail."""
+    import mixed_fem_b200 as mf
+    V, T, fm, h = mesh(3, (9, 6, 5), shuffle=True, jitter=0.12, pin=0.12)
+    mats = [("Stable-Neohookean", MU, LA)]
+    gpu, cpu, st = pair(V, T, fm, mats, h=h)
+    gpu.set_option("asm_mode", 2)
+    rng = np.random.default_rng(7)
+    s = st["s"].reshape(-1, 6).copy()
+    sel = rng.uniform(size=s.shape[0]) < 0.33
+    s[sel, :3] *= rng.uniform(0.45, 0.8, size=(int(sel.sum()), 1))
+    runs = []
+    for rep in range(3):
+        g = gpu if rep == 0 else mf.MixedStretch(V, T, fm, mats)
+        if rep:
+            g.reset(); g.set("R", st["R"]); g.set("la", st["la"])
+            g.set_option("asm_mode", 2)
+        g.set("s", s.reshape(-1))
+        g.update(st["x"], DT)
+        runs.append((g.lhs()[2].copy(), g.rhs().copy(), g.get("grad_x").copy()))
+        if rep == 0:
+            cpu.set("s", s.reshape(-1)); cpu.update(st["x"], DT)
+            check_update(g, cpu, 3)
+            assert 0 < g.status()["psd_slow"] < g.nE
+            g.set("R", st["R"])              # same warm start again (update() moved R_ to the converged rotations)
+            g.update(st["x"], DT)            # again on the same context: nothing accumulates, same bits
+            assert np.array_equal(g.lhs()[2], runs[0][0]) and np.array_equal(g.rhs(), runs[0][1])
+        else:
+            g.close()
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
+    for a, b in zip(runs[0], runs[2]):
+        assert np.array_equal(a, b)
     gpu.close()
