@@ -281,6 +281,20 @@ int mfb_comm_set_partition(mfb_ctx* ctx, const mfb_partition* p);
 int mfb_interface_sum_dev(mfb_ctx* ctx, double* a_dev, int ncomp_a, double* b_dev, int ncomp_b);
 int mfb_allreduce_dev(mfb_ctx* ctx, double* v_dev, int n, int op);   /* op 0 sum, 1 max; stream-ordered */
 
+/* ---- allocation-free entry point.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * mfb_energy_noalloc_dev = mfb_energy_dev (MixedStretch::energy, sum of psi(s_e) vol_e) with the scratch of its two-stage sum
+ * in a file-scope static __device__ array of MFB_NOALLOC_MAX_PARTIALS doubles (1 MiB, held by every GPU that loads the
+ * library until exit; one double per 128 elements, i.e. at most mfb_noalloc_max_elements() = 16 777 216 elements - larger
+ * contexts get MFB_ERR_TOO_LARGE) and the result written to a DEVICE pointer, stream-ordered on the context stream with no
+ * host synchronisation.  It calls no cudaMalloc / cudaFree / event creation and no allocating library routine; the first
+ * call on a device looks the array's address up once (cudaGetSymbolAddress): make it before starting a capture.  All calls
+ * on a device share the array: calls that overlap on the GPU race - keep them on one stream or order them with events.
+ * s_dev_soa_or_null: component-major N x ld stretches (NULL: the context's s_), e_dev: one double on the device. ---- */
+#define MFB_NOALLOC_MAX_PARTIALS 131072
+int mfb_energy_noalloc_dev(mfb_ctx* ctx, const double* s_dev_soa_or_null, double* e_dev);
+int64_t mfb_noalloc_max_elements(void);
+
 /* ---- instrumentation ---- */
 int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels this library launched on ctx */
 int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0), "cg_zero_guess" (0:

@@ -36,6 +36,7 @@ EXPORTS = [
     "mfb_stretch_update", "mfb_stretch_update_dev", "mfb_stretch_lhs_values", "mfb_stretch_gradient", "mfb_stretch_dev", "mfb_stretch_energy",
     "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_comm_set_partition", "mfb_interface_sum_dev", "mfb_allreduce_dev",
     "mfb_partition_create", "mfb_partition_destroy", "mfb_partition_sizes", "mfb_partition_get",
+    "mfb_energy_noalloc_dev", "mfb_noalloc_max_elements",
 ]
 
 
@@ -131,6 +132,8 @@ def lib():
     L.mfb_energy.argtypes = [vp, dp, dp, dp]
     L.mfb_constraint_value.argtypes = [vp, dp, dp, dp]
     L.mfb_energy_dev.argtypes = [vp, vp, dp]
+    L.mfb_energy_noalloc_dev.argtypes = [vp, vp, vp]
+    L.mfb_noalloc_max_elements.restype = C.c_int64
     L.mfb_constraint_value_dev.argtypes = [vp, vp, vp, dp]
     L.mfb_evaluate_constraint.argtypes = [vp, dp, dp]
     L.mfb_lhs_values.argtypes = [vp, dp]
@@ -339,6 +342,11 @@ class MixedStretch:
         e = C.c_double()
         self._check(self.L.mfb_energy_dev(self.h, C.c_void_p(s_ptr) if s_ptr else None, C.byref(e)))
         return e.value
+
+    def energy_noalloc_dev(self, e_ptr, s_ptr=None):
+        """allocation-free energy(): result written to the device double at e_ptr, stream-ordered, no host sync (no counterpart
+        in the reference; see include/mfem_b200.h)"""
+        self._check(self.L.mfb_energy_noalloc_dev(self.h, C.c_void_p(s_ptr) if s_ptr else None, C.c_void_p(e_ptr)))
 
     def constraint_value_dev(self, x_ptr, s_ptr=None):
         e = C.c_double()
