@@ -86,9 +86,9 @@ def test_full_size_properties_C2(built):
 
 
 def test_full_size_properties_C3_1M(built):
-    """BASELINE config C3 size (55^3 x 6 = 998 250 tets, ARAP): size-independent properties, no oracle.
-    symmetry x.(Ay) = y.(Ax); idempotence (a second update at the same x takes zero polar iterations and
-    reproduces every field); product_jacobian_x(gl) reproduces rhs; counters clean."""
+    """BASELINE config C3 size (55^3 x 6 = 998 250 tets, ARAP): size-independent properties - symmetry x.(Ay) = y.(Ax);
+    idempotence (a second update at the same x takes zero polar iterations and reproduces every field);
+    product_jacobian_x(gl) reproduces rhs; counters clean.  Full oracle parity at this size: the next test."""
     import torch
     from mixed_fem_b200 import meshgen
     import mixed_fem_b200 as mf
@@ -120,6 +120,25 @@ def test_full_size_properties_C3_1M(built):
     assert st2["polar_iters"] == 0
     assert vec_rel(gpu.get("S"), S1) <= 1e-14 and vec_rel(gpu.rhs(), rhs1) <= 1e-12 and vec_rel(gpu.lhs()[2], A1) <= 1e-12
     gpu.close()
+
+
+def test_full_oracle_parity_C3_1M(built):
+    """BASELINE config C3 as a parity case: 55^3 x 6 = 998 250 tets, ARAP (and Corot, the other material the config
+    names), every update field, the assembled matrix, rhs and the CSR pattern against the oracle (a few seconds of CPU)."""
+    from tests.test_gpu_parity import check_update
+    V, T, fm, h = mesh(3, (55, 55, 55))
+    for model in ("ARAP", "Corot"):
+        gpu, cpu, st = pair(V, T, fm, [(model, MU, LA)], h=h)
+        for o in (gpu, cpu):
+            o.update(st["x"], DT)
+        errs = check_update(gpu, cpu, 3)
+        print("C3", model, errs)
+        if model == "ARAP":
+            go, gi = gpu.csr_pattern()
+            co, ci, _ = cpu.csr(values=False)
+            assert np.array_equal(go, co) and np.array_equal(gi, ci)
+        gpu.close()
+        del cpu
 
 
 @pytest.mark.parametrize("dim", [3, 2])
