@@ -147,7 +147,11 @@ int mfb_last_status(mfb_ctx* ctx, mfb_status* st);
 /* ---- linear-solver side (src/linear_solvers/linear_system.h:9-62 SystemMatrixPD, eigen_iterative_solver.h:27-65,
  * pcg.h:11-80).  All pointers are DEVICE pointers; the matrix is  M_vals (same CSR pattern, may be NULL) + A. ---- */
 int mfb_spmv_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* x_dev, double* y_dev);
-/* precond: 0 none, 1 diagonal (Eigen DiagonalPreconditioner), 2 block-Jacobi d x d (preconditioners/block_jacobi.h:45-60).
+/* precond: 0 none, 1 diagonal (Eigen DiagonalPreconditioner), 2 block-Jacobi d x d (preconditioners/block_jacobi.h:45-60),
+ * 3 Chebyshev polynomial over block-Jacobi (NOT in the reference, whose stronger preconditioners are factorisations / AMG:
+ *   linear_solver_factory.cpp:119-173): degree "cheb_degree" (option, default 6) on [lmax / "cheb_ratio" (120), lmax], lmax of
+ *   Dinv L by 12 power iterations x 1.2, capped by the rigorous bound vertices-per-element.  Cuts CG iterations 4x at config C3
+ *   (500 -> 137) but costs 1.5x the SpMVs: slower on one GPU (44.8 vs 31.0 ms per Newton iteration), meant for several.
  * Solves (M + A) x = b from the initial guess in x; stops when |r| <= tol*|b| (Eigen ConjugateGradient criterion). */
 int mfb_pcg_dev(mfb_ctx* ctx, const double* M_vals_dev, const double* b_dev, double* x_dev, int precond,
                 double tol, int max_iters, int* iters_out, double* relres_out);
@@ -163,7 +167,7 @@ typedef struct mfb_newton_opts {
   int32_t outer_steps;    /* SimConfig::outer_steps (config.h:112, default 5) */
   int32_t ls_iters;       /* SimConfig::ls_iters (config.h:113, default 20) */
   double newton_tol;      /* SimConfig::newton_tol (config.h:127, default 1e-10) */
-  int32_t precond;        /* 0 none, 1 diagonal ("eigen-pcg-diag"), 2 block-Jacobi ("eigen-pcg-block_jacobi") */
+  int32_t precond;        /* 0 none, 1 diagonal ("eigen-pcg-diag"), 2 block-Jacobi ("eigen-pcg-block_jacobi"), 3 Chebyshev (see mfb_pcg_dev) */
   double cg_tol;          /* SimConfig::itr_tol (config.h:131, default 1e-4) */
   int32_t cg_max_iters;   /* SimConfig::max_iterative_solver_iters (default 500) */
 } mfb_newton_opts;

@@ -117,6 +117,8 @@ struct mfb_ctx {
   mfb::DBuf<double> xdev, vecF, partials, scal, aos, soa_tmp, soa_tmp2;
   // pcg work vectors
   mfb::DBuf<double> pcg_r, pcg_p, pcg_z, pcg_t, pcg_dinv, pcg_part, pcg_lhs;
+  mfb::DBuf<double> pcg_res, pcg_d;          // Chebyshev preconditioner (precond 3): inner residual and correction
+  int cheb_degree = 6, cheb_ratio = 120;       // options "cheb_degree", "cheb_ratio" (lambda_max / lambda_min of the target interval)
   double* h_scal = nullptr;   // pinned
   // host copies (lazy)
   std::vector<int32_t> h_outer, h_inner, h_smap, h_sstride;

@@ -8,6 +8,8 @@
 // index per d x d block, not one per scalar entry) + the vectors.
 #include "mfb_ctx.cuh"
 #include <algorithm>
+#include <cmath>
+#include <vector>
 
 using namespace mfb;
 
@@ -372,6 +374,140 @@ __global__ void __launch_bounds__(256) k_pcg_dir_dist(double* __restrict__ scal,
     else { scal[iter & 1] = rz; scal[3] += 1.0; }
   }
 }
+// ---------------------------------------------------------------------------------------------------------------
+// precond 3: Chebyshev polynomial over block-Jacobi.  z = q(Dinv L) Dinv r with q the degree-(deg-1) Chebyshev
+// polynomial for the interval [lmax / ratio, lmax] of the spectrum of Dinv L: every step is an SpMV plus a vertex-wise
+// update, nothing sequential (the reference's stronger preconditioners - IncompleteCholesky, the Laplacian LLT, amgcl,
+// src/factories/linear_solver_factory.cpp:119-173 - are triangular solves / hierarchies; this is the one that maps onto
+// the SpMV this file already has).  NOT in the reference.  A fixed SPD operator for lmax >= lambda_max, hence a valid CG
+// preconditioner; oracle/pcg.py::make_chebyshev restates it.
+//   k_cheb_update : the x / r update of the CG iteration (k_pcg_update's part) + step 0: res = r, d = Dinv r / theta, z = d,
+//                   local |r|^2 -> scal[8] (and r.z -> scal[9] when deg == 1)
+//   k_cheb_step   : res -= t (t = L d from the SpMV before), d = c1 d + c2 Dinv res, z += d; last step: r.z -> scal[9]
+// then k_pcg_dir_dist takes the decision and forms p (after the all-reduce of scal[8..9] on several GPUs).
+// ---------------------------------------------------------------------------------------------------------------
+template <int DIM>
+__device__ __forceinline__ void dinv_apply(const double* __restrict__ dinv, int gi, const double* v, double* o) {
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) s += dinv[(int64_t)gi * DIM * DIM + a * DIM + k] * v[k];
+    o[a] = s;
+  }
+}
+// cg != 0: the CG update x += alpha p, r -= alpha t precedes step 0 (t gets the neighbours' halo parts first);
+// cg == 0: plain step 0 on the given r (the application before the first iteration)
+template <int DIM>
+__global__ void __launch_bounds__(256) k_cheb_update(double* __restrict__ scal, int iter, unsigned* __restrict__ ticket, int cg,
+                                                     const double* __restrict__ p, const double* __restrict__ t,
+                                                     double* __restrict__ x, double* __restrict__ r, double* __restrict__ res,
+                                                     double* __restrict__ d, double* __restrict__ z,
+                                                     const double* __restrict__ dinv, int nF, double inv_theta, int want_rz,
+                                                     double* __restrict__ part_out, const double* __restrict__ w,
+                                                     const int* __restrict__ rowif_ptr, const int* __restrict__ rowif_idx,
+                                                     const double* __restrict__ recv) {
+  __shared__ double sh[8];
+  if (cg && scal[2] != 0.0) return;
+  const double alpha = cg ? scal[(iter + 1) & 1] / scal[7] : 0.0;
+  double rr = 0.0, rz = 0.0;
+  for (int gi = blockIdx.x * 256 + threadIdx.x; gi < nF; gi += gridDim.x * 256) {
+    double rv[DIM], y[DIM];
+    if (cg) {
+      double tv[DIM];
+#pragma unroll
+      for (int k = 0; k < DIM; ++k) tv[k] = t[DIM * gi + k];
+      if (rowif_ptr) {
+        for (int j = rowif_ptr[gi]; j < rowif_ptr[gi + 1]; ++j) {
+          const int64_t s0 = (int64_t)DIM * rowif_idx[j];
+#pragma unroll
+          for (int k = 0; k < DIM; ++k) tv[k] += recv[s0 + k];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < DIM; ++k) {
+        const int i = DIM * gi + k;
+        x[i] += alpha * p[i];
+        rv[k] = r[i] - alpha * tv[k];
+        r[i] = rv[k];
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < DIM; ++k) rv[k] = r[DIM * gi + k];
+    }
+    dinv_apply<DIM>(dinv, gi, rv, y);
+    double lr = 0.0, lz = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) {
+      const int i = DIM * gi + k;
+      const double dv = y[k] * inv_theta;
+      res[i] = rv[k]; d[i] = dv; z[i] = dv;
+      lr += rv[k] * rv[k]; lz += rv[k] * dv;
+    }
+    const double wi = w ? w[gi] : 1.0;
+    rr += wi * lr; rz += wi * lz;
+  }
+  const double s0 = block_sum_256(rr, sh);
+  const double s1 = block_sum_256(rz, sh);
+  if (threadIdx.x == 0) { part_out[blockIdx.x] = s0; part_out[kPcgBlocks + blockIdx.x] = s1; }
+  if (last_block_done(ticket)) {
+    const double rr2 = sum_partials_all(part_out, sh);
+    const double rz2 = sum_partials_all(part_out + kPcgBlocks, sh);
+    if (threadIdx.x == 0) { scal[8] = rr2; if (want_rz) scal[9] = rz2; }
+  }
+}
+template <int DIM>
+__global__ void __launch_bounds__(256) k_cheb_step(double* __restrict__ scal, unsigned* __restrict__ ticket, int check_flag,
+                                                   const double* __restrict__ t, const double* __restrict__ r, double* __restrict__ res,
+                                                   double* __restrict__ d, double* __restrict__ z, const double* __restrict__ dinv, int nF,
+                                                   double c1, double c2, int want_rz, double* __restrict__ part_out,
+                                                   const double* __restrict__ w, const int* __restrict__ rowif_ptr,
+                                                   const int* __restrict__ rowif_idx, const double* __restrict__ recv) {
+  __shared__ double sh[8];
+  if (check_flag && scal[2] != 0.0) return;
+  double rz = 0.0;
+  for (int gi = blockIdx.x * 256 + threadIdx.x; gi < nF; gi += gridDim.x * 256) {
+    double rs[DIM], y[DIM];
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) rs[k] = res[DIM * gi + k] - t[DIM * gi + k];
+    if (rowif_ptr) {
+      for (int j = rowif_ptr[gi]; j < rowif_ptr[gi + 1]; ++j) {
+        const int64_t s0 = (int64_t)DIM * rowif_idx[j];
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) rs[k] -= recv[s0 + k];
+      }
+    }
+    dinv_apply<DIM>(dinv, gi, rs, y);
+    double lz = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) {
+      const int i = DIM * gi + k;
+      const double dv = c1 * d[i] + c2 * y[k];
+      const double zv = z[i] + dv;
+      res[i] = rs[k]; d[i] = dv; z[i] = zv;
+      if (want_rz) lz += r[i] * zv;
+    }
+    rz += (w ? w[gi] : 1.0) * lz;
+  }
+  if (!want_rz) return;
+  const double s1 = block_sum_256(rz, sh);
+  if (threadIdx.x == 0) part_out[blockIdx.x] = s1;
+  if (last_block_done(ticket)) {
+    const double rz2 = sum_partials_all(part_out, sh);
+    if (threadIdx.x == 0) scal[9] = rz2;
+  }
+}
+// power-iteration start: a rough vector (integer hash of the dof index, reproducible on the host), so that it has a
+// component along the top of the spectrum - Dinv b is smooth (gravity) and made 10 iterations underestimate lambda_max
+__global__ void k_hash_vec(double* __restrict__ v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] = (double)((unsigned)i * 2654435761u) * (1.0 / 4294967296.0) - 0.5;
+}
+__global__ void k_scale_vec(double* __restrict__ v, double a, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] *= a;
+}
+
 // weighted two-stage dots (w per vertex, dim entries each)
 __global__ void __launch_bounds__(256) k_dot2w(const double* __restrict__ a, const double* __restrict__ b, const double* __restrict__ c2,
                                                const double* __restrict__ d2, const double* __restrict__ w, int dim, int n,
@@ -490,7 +626,10 @@ extern "C" int mfb_spmv_dev(mfb_ctx* c, const double* M_vals_dev, const double* 
 extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double* x, int precond, double tol, int max_iters,
                            int* iters_out, double* relres_out) {
   CHECK_CTX(c);
-  if (!b || !x || precond < 0 || precond > 2) return MFB_ERR_INVALID;
+  if (!b || !x || precond < 0 || precond > 3) return MFB_ERR_INVALID;
+  const bool cheb = precond == 3;
+  const int pmode = cheb ? 2 : precond;          // what the diagonal-block kernels build: Chebyshev runs over block-Jacobi
+  const int deg = cheb ? std::max(1, c->cheb_degree) : 1;
   const bool dist = c->world > 1;
   if (dist && !c->dot_w.p) { g_last_error = "mfb_pcg_dev: multi-GPU context without mfb_comm_set_interface"; return MFB_ERR_INVALID; }
   const double* w = dist ? c->dot_w.p : nullptr;
@@ -501,6 +640,9 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
     if ((rc = c->pcg_r.alloc((size_t)n + 1)) || (rc = c->pcg_p.alloc((size_t)n + 1)) || (rc = c->pcg_z.alloc((size_t)n + 1)) ||
         (rc = c->pcg_t.alloc((size_t)n + 1)) || (rc = c->pcg_dinv.alloc((size_t)c->nF * dd + 1)))
       return rc;
+  }
+  if (cheb && c->pcg_res.n < (size_t)n + 1) {
+    if ((rc = c->pcg_res.alloc((size_t)n + 1)) || (rc = c->pcg_d.alloc((size_t)n + 1))) return rc;
   }
   if (c->partials.n < (size_t)2 * kDotBlocks) { if ((rc = c->partials.alloc((size_t)2 * kDotBlocks + c->grid()))) return rc; }
   if (c->pcg_part.n < (size_t)5 * kPcgBlocks) { if ((rc = c->pcg_part.alloc((size_t)5 * kPcgBlocks))) return rc; }
@@ -532,15 +674,15 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
   };
   if (precond && c->nF) {
     if (!dist) {
-      if (c->dim == 3) k_build_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
-      else k_build_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, precond, c->pcg_dinv.p);
+      if (c->dim == 3) k_build_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, pmode, c->pcg_dinv.p);
+      else k_build_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, nullptr, pmode, c->pcg_dinv.p);
       c->launches += 1;
     } else {       // the diagonal blocks of the GLOBAL operator: local blocks summed at the interface, then inverted
       if (c->dim == 3) k_extract_diag<3><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, c->pcg_dinv.p);
       else k_extract_diag<2><<<nblk(c->nF), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->nF, L, c->pcg_dinv.p);
       if ((rc = interface_sum(c, c->pcg_dinv.p, dd, nullptr, 0, nullptr, 0))) return rc;
-      if (c->dim == 3) k_invert_diag<3><<<nblk(c->nF), 256, 0, st>>>(c->nF, precond, c->pcg_dinv.p);
-      else k_invert_diag<2><<<nblk(c->nF), 256, 0, st>>>(c->nF, precond, c->pcg_dinv.p);
+      if (c->dim == 3) k_invert_diag<3><<<nblk(c->nF), 256, 0, st>>>(c->nF, pmode, c->pcg_dinv.p);
+      else k_invert_diag<2><<<nblk(c->nF), 256, 0, st>>>(c->nF, pmode, c->pcg_dinv.p);
       c->launches += 2;
     }
   }
@@ -561,20 +703,72 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
   }
   const double threshold = tol * tol * rhsNorm2;
   if (resNorm2 >= threshold && max_iters > 0) {
-    // p = Dinv r ; absNew = r.p
-    if (c->nF) {
-      if (c->dim == 3) k_apply_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
-      else k_apply_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, r, p, c->nF, precond);
-      c->launches += 1;
-    }
-    if ((rc = dots(r, p, nullptr, nullptr, 0, -1))) return rc;         // scal[0] = absNew
     double* part = c->pcg_part.p;                   // pt[G] | rr[G] | rz[G] | two ticket counters
     unsigned* tickets = reinterpret_cast<unsigned*>(part + 3 * kPcgBlocks);
-    k_pcg_init<<<1, 1, 0, st>>>(c->scal.p, tol, tickets); c->launches += 1;
+    // ---- Chebyshev set-up: lambda_max of Dinv L by power iteration from Dinv b, then the step coefficients
+    double inv_theta = 1.0;
+    std::vector<double> cc1, cc2;
+    double *res = c->pcg_res.p, *dvec = c->pcg_d.p;
+    auto plain_product = [&](const double* xx, double* yy) -> int {       // yy = L xx, consistent on every rank
+      spmv_L(xx, yy);
+      return dist ? interface_sum(c, yy, c->dim, nullptr, 0, nullptr, 0) : MFB_OK;
+    };
+    auto apply_dinv = [&](const double* in, double* out) {
+      if (!c->nF) return;
+      if (c->dim == 3) k_apply_precond<3><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, in, out, c->nF, pmode);
+      else k_apply_precond<2><<<nblk(c->nF), 256, 0, st>>>(c->pcg_dinv.p, in, out, c->nF, pmode);
+      c->launches += 1;
+    };
+    if (cheb) {
+      double lam = 1.0;
+      constexpr int kPower = 12;
+      k_hash_vec<<<nblk(n), 256, 0, st>>>(z, n);                          // (z, t, p are free here)
+      for (int itp = 0; itp <= kPower; ++itp) {
+        if ((rc = dots(z, z, nullptr, nullptr, 10, -1))) return rc;
+        MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p + 10, sizeof(double), cudaMemcpyDeviceToHost, st));
+        MFB_CUDA(cudaStreamSynchronize(st));
+        const double nrm = sqrt(c->h_scal[0]);
+        if (!(nrm > 0.0) || !std::isfinite(nrm)) { g_last_error = "mfb_pcg_dev: Chebyshev power iteration broke down"; return MFB_ERR_STATE; }
+        if (itp > 0) lam = nrm;                                           // |Dinv L v| for |v| = 1
+        if (itp == kPower) break;
+        k_scale_vec<<<nblk(n), 256, 0, st>>>(z, 1.0 / nrm, n);
+        if ((rc = plain_product(z, t))) return rc;
+        apply_dinv(t, z);
+        c->launches += 1;
+      }
+      // never above the rigorous bound: K_e <= npe blockdiag(K_e) for every PSD element matrix (and the mass blocks), hence
+      // lambda_max(Dinv L) <= vertices per element
+      const double lmax = std::min(1.2 * lam, (double)c->npe), lmin = lmax / (c->cheb_ratio > 1 ? (double)c->cheb_ratio : 30.0);
+      const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
+      inv_theta = 1.0 / theta;
+      double rho = 1.0 / sigma;
+      for (int j = 1; j < deg; ++j) {
+        const double rho_new = 1.0 / (2.0 * sigma - rho);
+        cc1.push_back(rho_new * rho); cc2.push_back(2.0 * rho_new / delta);
+        rho = rho_new;
+      }
+    }
     const unsigned one = 1u;
     const unsigned gv = std::max(one, std::min(nblk(c->nF), (unsigned)kPcgBlocks));      // one vertex per thread
     const unsigned gn = std::max(one, std::min(nblk(n), (unsigned)kPcgBlocks));
     const unsigned gs = std::max(one, std::min(nblk((int64_t)c->nF * 16), (unsigned)kSpmvBlocks));
+    // p = (preconditioner) r ; absNew = r.p
+    if (!cheb) {
+      apply_dinv(r, p);
+    } else {                                       // z = Cheb(r) with plain launches (no flags yet), then p = z
+      MFB_CUDA(cudaMemsetAsync(tickets, 0, 2 * sizeof(unsigned), st));
+      if (c->dim == 3) k_cheb_update<3><<<gv, 256, 0, st>>>(c->scal.p, 0, tickets + 1, 0, nullptr, nullptr, nullptr, r, res, dvec, z, c->pcg_dinv.p, c->nF, inv_theta, 0, part + kPcgBlocks, w, nullptr, nullptr, nullptr);
+      else k_cheb_update<2><<<gv, 256, 0, st>>>(c->scal.p, 0, tickets + 1, 0, nullptr, nullptr, nullptr, r, res, dvec, z, c->pcg_dinv.p, c->nF, inv_theta, 0, part + kPcgBlocks, w, nullptr, nullptr, nullptr);
+      for (int j = 1; j < deg; ++j) {
+        if ((rc = plain_product(dvec, t))) return rc;
+        if (c->dim == 3) k_cheb_step<3><<<gv, 256, 0, st>>>(c->scal.p, tickets + 1, 0, t, r, res, dvec, z, c->pcg_dinv.p, c->nF, cc1[j - 1], cc2[j - 1], 0, part + kPcgBlocks, w, nullptr, nullptr, nullptr);
+        else k_cheb_step<2><<<gv, 256, 0, st>>>(c->scal.p, tickets + 1, 0, t, r, res, dvec, z, c->pcg_dinv.p, c->nF, cc1[j - 1], cc2[j - 1], 0, part + kPcgBlocks, w, nullptr, nullptr, nullptr);
+      }
+      MFB_CUDA(cudaMemcpyAsync(p, z, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+      c->launches += deg;
+    }
+    if ((rc = dots(r, p, nullptr, nullptr, 0, -1))) return rc;         // scal[0] = absNew
+    k_pcg_init<<<1, 1, 0, st>>>(c->scal.p, tol, tickets); c->launches += 1;
     // multi-GPU with a partition set: the halo of t = L p goes point-to-point, written / read inside the CG kernels
     const bool p2p = dist && c->use_p2p && c->ent_local.p;
     double *hsend = nullptr, *hrecv = nullptr;
@@ -597,6 +791,25 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
       if (p2p) e = halo_exchange(c, c->dim, c->scal.p + 7, 1);
       else if (dist) e = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1);
       if (e) return e;
+      if (cheb) {
+        // CG update + Chebyshev step 0, then (deg - 1) x [SpMV of the correction, halo, step]; r.r and r.z end up in scal[8..9]
+        if (c->dim == 3) k_cheb_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, 1, p, t, x, r, res, dvec, z, c->pcg_dinv.p, c->nF, inv_theta, deg == 1, part + kPcgBlocks, w, rif_ptr, rif_idx, hrecv);
+        else k_cheb_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, 1, p, t, x, r, res, dvec, z, c->pcg_dinv.p, c->nF, inv_theta, deg == 1, part + kPcgBlocks, w, rif_ptr, rif_idx, hrecv);
+        for (int j = 1; j < deg; ++j) {
+          if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, dvec, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+          else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, dvec, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+          if (p2p) e = halo_exchange(c, c->dim, nullptr, 0);
+          else if (dist) e = interface_sum(c, t, c->dim, nullptr, 0, nullptr, 0);
+          if (e) return e;
+          const int lastj = j == deg - 1;
+          if (c->dim == 3) k_cheb_step<3><<<gv, 256, 0, st>>>(c->scal.p, tickets + 1, 1, t, r, res, dvec, z, c->pcg_dinv.p, c->nF, cc1[j - 1], cc2[j - 1], lastj, part + kPcgBlocks, w, rif_ptr, rif_idx, hrecv);
+          else k_cheb_step<2><<<gv, 256, 0, st>>>(c->scal.p, tickets + 1, 1, t, r, res, dvec, z, c->pcg_dinv.p, c->nF, cc1[j - 1], cc2[j - 1], lastj, part + kPcgBlocks, w, rif_ptr, rif_idx, hrecv);
+        }
+        c->launches += 2 * (deg - 1);
+        if (dist && (e = allreduce_scalars(c, c->scal.p + 8, 2, false))) return e;
+        k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
+        return MFB_OK;
+      }
       if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
       else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
       if (dist) {

@@ -169,6 +169,7 @@ struct PcgSolver {
     if (n == "eigen-pcg-diag") s.precond = 1;
     else if (n == "eigen-pcg-block_jacobi") s.precond = 2;
     else if (n == "eigen-pcg-identity") s.precond = 0;
+    else if (n == "mfb-pcg-chebyshev") s.precond = 3;          // not a reference solver name: Chebyshev over block-Jacobi (mfb_pcg_dev)
     else throw std::runtime_error("PcgSolver: no device implementation of solver '" + n + "'");
     return s;
   }

@@ -9,6 +9,55 @@ src/linear_solvers/pcg.h:11-80.  Eigen is absent from this container, so this fo
 import numpy as np
 
 
+def chebyshev_coefficients(lmax, ratio, degree):
+    """(theta, [(c1, c2) for steps 1..degree-1]) of the Chebyshev iteration on [lmax / ratio, lmax]:
+    d_0 = Dinv r / theta ; d_j = c1_j d_{j-1} + c2_j Dinv (r - A z_{j-1}) ; z_j = z_{j-1} + d_j"""
+    lmin = lmax / ratio
+    theta, delta = 0.5 * (lmax + lmin), 0.5 * (lmax - lmin)
+    sigma = theta / delta
+    rho = 1.0 / sigma
+    coef = []
+    for _ in range(degree - 1):
+        rho_new = 1.0 / (2.0 * sigma - rho)
+        coef.append((rho_new * rho, 2.0 * rho_new / delta))
+        rho = rho_new
+    return theta, coef
+
+
+def chebyshev_lmax(A, dinv, npe, iters=12, safety=1.2):
+    """largest eigenvalue of Dinv A as mfb_pcg_dev estimates it for precond 3: power iteration from an integer-hash
+    vector, times a safety factor, capped by the rigorous bound lambda_max <= vertices per element"""
+    i = np.arange(A.shape[0], dtype=np.uint64)
+    v = ((i * np.uint64(2654435761)) & np.uint64(0xFFFFFFFF)).astype(np.float64) / 4294967296.0 - 0.5
+    v /= np.sqrt(float(v @ v))
+    lam = 1.0
+    for _ in range(iters):
+        w = dinv(A @ v)
+        lam = np.sqrt(float(w @ w))
+        v = w / lam
+    return min(safety * lam, float(npe))
+
+
+def make_chebyshev(A, dim, b, degree=6, ratio=120.0, npe=None):
+    """precond 3 of mfb_pcg_dev: a fixed polynomial of degree-1 in (block-Jacobi)^-1 A applied to (block-Jacobi)^-1 r.
+    Not in the reference (its non-Jacobi preconditioners are factorisations / AMG, src/factories/linear_solver_factory.cpp:
+    119-173); symmetric positive definite for lmax >= lambda_max, hence a valid CG preconditioner."""
+    dinv = make_precond(A, 2, dim)
+    lmax = chebyshev_lmax(A, dinv, dim + 1 if npe is None else npe)
+    theta, coef = chebyshev_coefficients(lmax, ratio, degree)
+
+    def apply(r):
+        d = dinv(r) / theta
+        z = d.copy()
+        res = r.copy()
+        for c1, c2 in coef:
+            res = res - A @ d
+            d = c1 * d + c2 * dinv(res)
+            z = z + d
+        return z
+    return apply
+
+
 def make_precond(A, kind, dim):
     """kind: 0 identity, 1 diagonal (zero diagonal -> 1), 2 dim x dim block-Jacobi inverse"""
     n = A.shape[0]
