@@ -26,6 +26,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "update_exchange")) { c->update_exchange = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "p2p")) { c->use_p2p = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "cg_graph")) { c->cg_graph = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "pipe")) { c->pipe = value; return MFB_OK; }       // 0 off, n > 0: persistent pipelined update kernel, n CTAs per SM slot
   if (!strcmp(name, "cheb_degree")) { if (value < 1 || value > 16) return MFB_ERR_INVALID; c->cheb_degree = value; return MFB_OK; }
   if (!strcmp(name, "cheb_ratio")) { if (value < 2) return MFB_ERR_INVALID; c->cheb_ratio = value; return MFB_OK; }
   if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch, 3 v4 (default)
@@ -168,6 +169,11 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_tail<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_pipe<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem + kV4SmemPipe));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_pipe<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem + kV4SmemPipe));
+      // two CTAs of 110 KB only fit with the whole L1 / shared array configured as shared memory
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_pipe<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+      MFB_CUDA(cudaFuncSetAttribute(k_update_tet_v4_pipe<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
       attr4_done = true;
     }
     const int grid4 = (c->nE + kV4Threads - 1) / kV4Threads;
@@ -234,6 +240,11 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
         MFB_CUDA(cudaStreamWaitEvent(st, c->ev_x1, 0));
         LAUNCHED(c, 4);
         exchanged = true;
+      } else if (c->pipe > 0) {
+        // persistent pipelined variant: MFB_V4_MINB CTAs per SM, `pipe` waves of tiles interleaved over them
+        const int gp = std::min(grid4, 148 * MFB_V4_MINB * c->pipe);
+        if (c->fuse_rhs) k_update_tet_v4_pipe<true><<<gp, kV4Threads, smem + kV4SmemPipe, st>>>(m, s, a, x_dev, h2, 0, c->nE);
+        else k_update_tet_v4_pipe<false><<<gp, kV4Threads, smem + kV4SmemPipe, st>>>(m, s, a, x_dev, h2, 0, c->nE);
       } else if (c->fuse_rhs) k_update_tet_v4<true, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
       else k_update_tet_v4<false, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
       if (!exchanged) {
@@ -603,6 +614,18 @@ extern "C" int mfb_phase_times(mfb_ctx* c, double* ms, int32_t* counts, int rese
     c->ph_spans.clear();
   }
   return MFB_OK;
+}
+
+// resident CTAs per SM of the tet update kernels as the runtime computes them (which: 0 plain, 1 pipelined) - tools only
+extern "C" int mfb_debug_occupancy(int which) {
+  int n = -1;
+  const int smem = kV4SmemB + kV4SmemStage;
+  cudaFuncSetAttribute(k_update_tet_v4<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaFuncSetAttribute(k_update_tet_v4_pipe<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem + kV4SmemPipe);
+  cudaFuncSetAttribute(k_update_tet_v4_pipe<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (which == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_update_tet_v4<true, 1>, kV4Threads, smem);
+  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_update_tet_v4_pipe<true>, kV4Threads, smem + kV4SmemPipe);
+  return n;
 }
 
 extern "C" int mfb_kernel_time_ms(mfb_ctx* c, double* total_ms, int* count) {

@@ -162,6 +162,7 @@ struct mfb_ctx {
   // point-to-point exchange (mfb_comm_set_partition): neighbour ranks, entry offsets, local free id per entry, and per
   // local free row the list of its entries (rowif_ptr / rowif_idx: the CG kernels write / read their halo through it)
   int use_p2p = 1, update_exchange = 0;
+  int pipe = 0;                               // update kernel: persistent software-pipelined variant (option "pipe")
   int cg_graph = 0;                           // mfb_pcg_dev: replay batches of 32 iterations as a CUDA graph (option "cg_graph"; measured: no gain, the
                                               // iteration is bound by its kernels on 1 GPU and by the latency of its 3 NCCL kernels on several)
   int n_if_elems = 0, n_nbr = 0, n_ent = 0;

@@ -53,6 +53,19 @@ constexpr int kV4StageDoubles = kV4RedDoubles + 96 + 64;
 constexpr int kV4SmemB = 54 * kV4Threads * (int)sizeof(double);
 constexpr int kV4SmemStage = kV4Warps * (kV4StageDoubles * (int)sizeof(double) + 32 * (int)sizeof(int));
 
+// Pipelined (persistent) variant: per thread one staging slot for the NEXT tile's streamed inputs - dphi[9], vol, R[9],
+// s[6] (25 doubles), T[4] (ints) - and one for its 12 gathered vertex coordinates, all thread-private columns
+// (component-major, [c][thread]): no block-level synchronisation, cp.async completion is per thread.
+constexpr int kV4PipeIn = 25;
+constexpr int kV4SmemPipe = (kV4PipeIn + 12) * kV4Threads * (int)sizeof(double) + 4 * kV4Threads * (int)sizeof(int);
+
+struct PipeStage {
+  double* in;      // [25][kV4Threads]
+  int* T;          // [4][kV4Threads]
+  double* x;       // [12][kV4Threads]
+  int e_next;      // element whose inputs are (being) staged, -1: none
+};
+
 struct DevAsm {
   double* Ablk;          // [nbu][9]  block-CSR copy of the upper triangle (row-major 3x3)
   double* gxrh;          // [nF][6]   grad_x | rhs interleaved
@@ -132,9 +145,35 @@ __device__ __forceinline__ constexpr int pair6(int j, int k) { return j * 3 - j 
 
 // `inrange` false: the lane has no element (grid padding); it runs on a clamped element index so that the warp stays
 // convergent for the cooperative reductions, and stores nothing.
-template <bool FUSE_RHS, bool TAIL, int ASM>
+// streamed inputs of element e -> the thread's staging slot (25 x 8-byte + 4 x 4-byte cp.async)
+__device__ __forceinline__ void pipe_issue_inputs(const DevMesh& m, const DevState& st, const PipeStage& ps, int e) {
+  const int64_t ld = m.ld;
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) cp_async4(&ps.T[k * kV4Threads + t], &m.T[k * ld + e]);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) cp_async8(&ps.in[i * kV4Threads + t], &m.dphi[i * ld + e]);
+  cp_async8(&ps.in[9 * kV4Threads + t], &m.vol[e]);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) cp_async8(&ps.in[(10 + i) * kV4Threads + t], &st.R[i * ld + e]);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) cp_async8(&ps.in[(19 + k) * kV4Threads + t], &st.s[k * ld + e]);
+}
+// the 12 vertex coordinates of the staged element (its T has landed) -> the thread's x slot
+__device__ __forceinline__ void pipe_issue_gather(const PipeStage& ps, const double* __restrict__ x) {
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int v = ps.T[k * kV4Threads + t];
+#pragma unroll
+    for (int l = 0; l < 3; ++l) cp_async8(&ps.x[(3 * k + l) * kV4Threads + t], &x[3 * (int64_t)v + l]);
+  }
+}
+
+template <bool FUSE_RHS, bool TAIL, int ASM, bool PIPE = false>
 __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevState& st, const DevAsm& as, const double* __restrict__ x,
-                                                   int e, bool inrange, double h2, double* sB, double* sW, int* sC) {
+                                                   int e, bool inrange, double h2, double* sB, double* sW, int* sC,
+                                                   PipeStage ps = PipeStage{nullptr, nullptr, nullptr, -1}) {
   double* myB = sB + threadIdx.x;                       // element (row, n) at myB[(6*row + n) * kV4Threads]
   const int lane = threadIdx.x & 31;
   const int64_t ld = m.ld;
@@ -142,13 +181,40 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 
   // ---- 1 : deformation gradient, polar, stretch, dS/dF
   double dphi[9], F[9], R[9], Y[9];
-  tet_F(m, e, x, dphi, F);
-#pragma unroll
-  for (int i = 0; i < 9; ++i) R[i] = __ldcs(&st.R[i * ld + e]);
   double s[6];
+  double vol;
+  if constexpr (PIPE) {
+    // this element's inputs were staged while the previous tile computed: everything outstanding has to land first
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    const int t = threadIdx.x;
 #pragma unroll
-  for (int k = 0; k < 6; ++k) s[k] = __ldcs(&st.s[k * ld + e]);
-  const double vol = __ldcs(&m.vol[e]);
+    for (int i = 0; i < 9; ++i) dphi[i] = ps.in[i * kV4Threads + t];
+    vol = ps.in[9 * kV4Threads + t];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = ps.in[(10 + i) * kV4Threads + t];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s[k] = ps.in[(19 + k) * kV4Threads + t];
+    double x0[3], dx[9];
+#pragma unroll
+    for (int l = 0; l < 3; ++l) x0[l] = ps.x[l * kV4Threads + t];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+      for (int l = 0; l < 3; ++l) dx[3 * k + l] = ps.x[(3 * (k + 1) + l) * kV4Threads + t] - x0[l];
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) F[3 * c + r] = dx[r] * dphi[c] + dx[3 + r] * dphi[3 + c] + dx[6 + r] * dphi[6 + c];
+    asm volatile("" ::: "memory");        // the slot is read: refill it with the next tile's inputs (lands during the polar iteration)
+    if (ps.e_next >= 0) pipe_issue_inputs(m, st, ps, ps.e_next);
+  } else {
+    tet_F(m, e, x, dphi, F);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = __ldcs(&st.R[i * ld + e]);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s[k] = __ldcs(&st.s[k * ld + e]);
+    vol = __ldcs(&m.vol[e]);
+  }
   // step-3 inputs (la, element->block codes) start moving now, asynchronously and without registers, into the warp's
   // reduction buffer, which is idle until step 3: layout la[n] at sW[n*32 + lane], code[q] at int(sW + 192)[q*32 + lane]
   if (ASM >= 1) {
@@ -183,6 +249,9 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
   if (ASM == 2) asm volatile("cp.async.wait_all;" ::: "memory");
   if (ASM == 1) {
     asm volatile("cp.async.wait_all;" ::: "memory");
+    if constexpr (PIPE) {              // the next tile's T has landed with the rest: start its vertex gather now
+      if (ps.e_next >= 0) { pipe_issue_gather(ps, x); asm volatile("cp.async.commit_group;" ::: "memory"); }
+    }
     const int* sI = reinterpret_cast<const int*>(sW + kV4RedDoubles);
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
@@ -521,6 +590,53 @@ __global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4(DevMe
   int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;
   if ((e & ~31) >= m.nE) return;                       // whole warp out of range
   update_tet_v4_body<FUSE_RHS, false, ASM>(m, st, as, x, e < m.nE ? e : m.nE - 1, e < m.nE, h2, smem4, sW, sC);
+}
+
+// Persistent, software-pipelined form of k_update_tet_v4 (ASM 1): each CTA walks the element tiles
+// e_begin + (blockIdx.x + i gridDim.x) 128 < e_end and, while it computes tile i, cp.async moves tile i+1's streamed inputs
+// (at the top) and its 12 gathered vertex coordinates (after the polar iteration, when tile i+1's vertex ids have landed)
+// into thread-private shared-memory slots.  ncu (profiles/README.md, round 2): 12.8 % of the stall samples of the plain
+// kernel sit on the two chained global latencies at its top (T, then x[T]), which 2 warps per scheduler cannot cover.
+template <bool FUSE_RHS>
+__global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_pipe(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
+                                                                      int e_begin, int e_end) {
+  extern __shared__ __align__(128) double smem4[];
+  const int w = threadIdx.x >> 5;
+  double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;
+  int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;
+  PipeStage ps;
+  ps.in = reinterpret_cast<double*>(reinterpret_cast<char*>(smem4) + kV4SmemB + kV4SmemStage);
+  ps.x = ps.in + kV4PipeIn * kV4Threads;
+  ps.T = reinterpret_cast<int*>(ps.x + 12 * kV4Threads);
+  const int last = e_end - 1;
+  const int ntiles = (e_end - e_begin + kV4Threads - 1) / kV4Threads;
+  int tile = blockIdx.x;
+  if (tile >= ntiles) return;
+  // prologue: the first tile's inputs, then its gather (lanes past the end work on a clamped element and store nothing)
+  {
+    const int e0 = e_begin + tile * kV4Threads + threadIdx.x;
+    ps.e_next = e0 <= last ? e0 : last;
+    pipe_issue_inputs(m, st, ps, ps.e_next);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    pipe_issue_gather(ps, x);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (; tile < ntiles; tile += gridDim.x) {
+    // re-align the CTA's warps once per tile: nothing else synchronises them, and warps that drift into different phases
+    // of the ~100 KB instruction stream thrash the instruction cache (ncu: no_instruction 4.6 % -> 22 % of the samples
+    // without this barrier; the one-tile kernel keeps its warps together simply because they start together)
+    __syncthreads();
+    const int e = e_begin + tile * kV4Threads + threadIdx.x;
+    const int nxt = tile + gridDim.x;
+    const int en = e_begin + nxt * kV4Threads + threadIdx.x;
+    ps.e_next = nxt < ntiles ? (en <= last ? en : last) : -1;
+    if ((e & ~31) > last) {           // whole warp past the end (last tile only): nothing staged for a next tile either
+      asm volatile("cp.async.wait_all;" ::: "memory");
+      continue;
+    }
+    update_tet_v4_body<FUSE_RHS, false, 1, true>(m, st, as, x, e <= last ? e : last, e <= last, h2, smem4, sW, sC, ps);
+  }
 }
 
 // elements the fast PSD path refused: grid-stride over the list the main kernel built (count in counters[5])

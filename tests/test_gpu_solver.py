@@ -121,14 +121,19 @@ def test_chebyshev_cuts_cg_iterations_at_C3(built):
     assert np.all(np.abs(logs[3]["energy"] - logs[1]["energy"]) <= 1e-3 * np.abs(logs[1]["energy"]))
 
 
-def test_full_size_properties_C2(built):
-    """BASELINE config C2 (64x16x16x6 = 98 304 tets): full parity against the oracle, which finishes in seconds."""
+@pytest.mark.parametrize("pipe", [0, 1])
+def test_full_size_properties_C2(built, pipe):
+    """BASELINE config C2 (64x16x16x6 = 98 304 tets): full parity against the oracle, which finishes in seconds.
+    pipe = 1: the persistent software-pipelined update kernel (768 tiles over 296 CTAs: every CTA walks 2-3 tiles), twice in
+    a row so that the second update starts from the rotations the first one stored."""
     from tests.test_gpu_parity import check_update
     V, T, fm, h = mesh(3, (64, 16, 16))
     gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
-    for o in (gpu, cpu):
-        o.update(st["x"], DT)
-    check_update(gpu, cpu, 3)
+    gpu.set_option("pipe", pipe)
+    for xx in (st["x"], 0.5 * (st["x"] + st["xprev"])) if pipe else (st["x"],):
+        for o in (gpu, cpu):
+            o.update(xx, DT)
+        check_update(gpu, cpu, 3)
     go, gi = gpu.csr_pattern()
     co, ci, _ = cpu.csr(values=False)
     assert np.array_equal(go, co) and np.array_equal(gi, ci)
