@@ -1,7 +1,8 @@
 """ORACLE — TEST INFRASTRUCTURE ONLY (imported by tests/ only; never by the product).
 
-numpy restatement of the reference's NON-mixed variable for tetrahedra and 2D triangles with the Stable Neo-Hookean
-F-form:
+numpy restatement of the reference's NON-mixed variable for tetrahedra and 2D triangles with the F-form overloads of
+Stable Neo-Hookean, Neo-Hookean (3D), ARAP and FixedCorot (closed forms; tests/test_oracle_stretch.py pins them against
+numbers evaluated from the reference's generated expression text, tests/golden/fform_golden.json):
 
   Stretch<DIM>::energy / update / rhs / gradient ..... src/variables/stretch.cpp:16-68
   StableNeohookean::energy/gradient/hessian(Vector9d)  src/energies/stable_neohookean.cpp:93-232 (Vector4d: :274-324)
@@ -57,6 +58,97 @@ def gradient_hessian(F, mu, la):
         d2 = np.broadcast_to(np.einsum("rs,cd->crds", _EPS2, _EPS2).reshape(1, M, M), (nE, M, M))
     H = mu * np.eye(M)[None] + la * np.einsum("ei,ej->eij", vec(cof), vec(cof)) + k1[:, None, None] * d2
     return g, H
+
+
+def _cof_d2J(F):
+    """(J, vec cof F (nE,M), d2J/dF2 (nE,M,M)) with index d*c + r (column-major vec F)"""
+    nE, d = F.shape[0], F.shape[1]
+    M = d * d
+    J = np.linalg.det(F)
+    cof = J[:, None, None] * np.transpose(np.linalg.inv(F), (0, 2, 1))
+    vcof = np.transpose(cof, (0, 2, 1)).reshape(nE, M)
+    if d == 3:
+        d2 = np.einsum("rsm,cdn,emn->ecrds", _EPS, _EPS, F).reshape(nE, M, M)
+    else:
+        d2 = np.broadcast_to(np.einsum("rs,cd->crds", _EPS2, _EPS2).reshape(1, M, M), (nE, M, M))
+    return J, vcof, d2
+
+
+def neohookean_energy(F, mu, la):
+    """neohookean.cpp:93-106: mu/2 (|F|^2 - 3) - mu log J + la/2 (log J)^2"""
+    J = np.linalg.det(F)
+    return 0.5 * mu * (np.einsum("eij,eij->e", F, F) - 3.0) - mu * np.log(J) + 0.5 * la * np.log(J) ** 2
+
+
+def neohookean_gradient_hessian(F, mu, la):
+    """closed form of neohookean.cpp:108-227 (81 symbolic-toolbox expressions), BEFORE sim::simple_psd_fix(H) (tol 1e-6):
+    g = mu F + (la log J - mu)/J cof F ; H = mu I + (la (1 - log J) + mu)/J^2 cof cof^T + (la log J - mu)/J d2J/dF2"""
+    nE = F.shape[0]
+    J, vcof, d2 = _cof_d2J(F)
+    lj = np.log(J)
+    k1 = (la * lj - mu) / J
+    k2 = (la * (1.0 - lj) + mu) / (J * J)
+    vec = lambda A: np.transpose(A, (0, 2, 1)).reshape(nE, 9)
+    g = mu * vec(F) + k1[:, None] * vcof
+    H = mu * np.eye(9)[None] + k2[:, None, None] * np.einsum("ei,ej->eij", vcof, vcof) + k1[:, None, None] * d2
+    return g, H
+
+
+def volume_term(F, la):
+    """the term FixedCorot adds to the ARAP part (fixed_corotational.cpp:233-254, :266-357; 2D: :160-169, :196-209):
+    g += la (J - 1) cof F ; H += la (cof cof^T + (J - 1) d2J/dF2)"""
+    J, vcof, d2 = _cof_d2J(F)
+    return la * (J - 1.0)[:, None] * vcof, la * (np.einsum("ei,ej->eij", vcof, vcof) + (J - 1.0)[:, None, None] * d2)
+
+
+def arap2d_parts(F):
+    """R = U V^T with the flip fix of mfem::svd<double,2> (svd_eigen.h:7-31) and dR/dF = 2/(s0 + s1) q0 q0^T,
+    q0 = vec(U [0 -1; 1 0] V^T)/sqrt 2 (arap.cpp:112-132): returns (R (nE,2,2), dRdF (nE,4,4), s0 + s1)"""
+    U, sig, Vt = np.linalg.svd(F)
+    flip = np.linalg.det(U @ Vt) < 0
+    U = U.copy(); sig = sig.copy()
+    U[flip, :, -1] *= -1.0
+    sig[flip, -1] *= -1.0
+    R = U @ Vt
+    Sk = np.array([[0.0, -1.0], [1.0, 0.0]])
+    Q0 = (U @ Sk[None] @ Vt) / np.sqrt(2.0)
+    q0 = np.transpose(Q0, (0, 2, 1)).reshape(-1, 4)
+    l0 = 2.0 / (sig[:, 0] + sig[:, 1])
+    return R, l0[:, None, None] * np.einsum("ei,ej->eij", q0, q0), sig[:, 0] + sig[:, 1]
+
+
+def model_energy_gradient_hessian(model, F, mu, la):
+    """(psi (nE,), g (nE,M), H (nE,M,M) AFTER the model's psd fix) of the F-form overloads, d = 2 or 3:
+    Stable-Neohookean (fix at 0), Neohookean (3D; fix at 1e-6), ARAP (no fix), FixedCorot (fix at 1e-6).
+    FixedCorot quirks reproduced: the 3D energy has no volume term (fixed_corotational.cpp:215-223) and carries mu/2, the 2D
+    one mu and la/2 (J-1)^2 (:136-151); the 3D gradient / Hessian use mu, the 2D ones 2 mu (:225-232 vs :153-172)."""
+    nE, d = F.shape[0], F.shape[1]
+    M = d * d
+    vec = lambda A: np.transpose(A, (0, 2, 1)).reshape(nE, M)
+    Fv = vec(F)
+    if model == "Stable-Neohookean":
+        psi = energy_expanded(Fv, mu, la) if d == 3 else energy_expanded_2d(Fv, mu, la)
+        g, H = gradient_hessian(F, mu, la)
+        return psi, g, simple_psd_fix(H, 0.0)
+    if model == "Neohookean":
+        assert d == 3
+        g, H = neohookean_gradient_hessian(F, mu, la)
+        return neohookean_energy(F, mu, la), g, simple_psd_fix(H, 1e-6)
+    if d == 3:
+        gA, HA, R = arap_gradient_hessian(F, mu)
+        psiA = arap_energy(F, mu)
+        if model == "ARAP":
+            return psiA, gA, HA
+        gv, Hv = volume_term(F, la)
+        return psiA, gA + gv, simple_psd_fix(HA + Hv, 1e-6)
+    R, dRdF, _ = arap2d_parts(F)
+    diff2 = np.einsum("eij,eij->e", F - R, F - R)
+    if model == "ARAP":
+        return 0.5 * mu * diff2, mu * (Fv - vec(R)), mu * (np.eye(4)[None] - dRdF)
+    assert model == "FixedCorot"
+    J = np.linalg.det(F)
+    gv, Hv = volume_term(F, la)
+    return mu * diff2 + 0.5 * la * (J - 1.0) ** 2, 2.0 * mu * (Fv - vec(R)) + gv, simple_psd_fix(2.0 * mu * (np.eye(4)[None] - dRdF) + Hv, 1e-6)
 
 
 def polar_rotation(F):
@@ -124,20 +216,14 @@ class OracleStretch:
         d = self.d
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
         Fv = np.transpose(F, (0, 2, 1)).reshape(-1, d * d)
-        if self.model == "ARAP":
-            return float(np.sum(arap_energy(F, self.mu) * self.vol))
-        psi = energy_expanded(Fv, self.mu, self.la) if d == 3 else energy_expanded_2d(Fv, self.mu, self.la)
+        psi, _, _ = model_energy_gradient_hessian(self.model, F, self.mu, self.la)
         return float(np.sum(psi * self.vol))
 
     def update(self, x, h):
         d = self.d
         nd = d * (d + 1)
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
-        if self.model == "ARAP":
-            g, H, _ = arap_gradient_hessian(F, self.mu)
-        else:
-            g, H = gradient_hessian(F, self.mu, self.la)
-            H = simple_psd_fix(H, 0.0)
+        _, g, H = model_energy_gradient_hessian(self.model, F, self.mu, self.la)
         w = self.vol * h * h
         He = np.einsum("eia,eij,ejb->eab", self.Jloc, H, self.Jloc) * w[:, None, None]      # (nE,nd,nd)
         ge = np.einsum("eia,ei->ea", self.Jloc, g) * w[:, None]                              # (nE,nd)

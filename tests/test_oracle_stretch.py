@@ -2,6 +2,7 @@
 are checked against central differences of the reference's expanded energy expression (stable_neohookean.cpp:107), the
 assembled vector / matrix against differences of the assembled energy."""
 import numpy as np
+import pytest
 
 from mixed_fem_b200 import meshgen
 from oracle import stretch as ostretch
@@ -100,3 +101,64 @@ def test_arap_f_form_closed_dRdF_matches_finite_differences():
         assert np.allclose(fd_e, g[:, i], rtol=1e-6, atol=1e-7 * MU)
         gp, _, _ = ostretch.arap_gradient_hessian(Fp, MU); gm, _, _ = ostretch.arap_gradient_hessian(Fm, MU)
         assert np.allclose((gp - gm) / (2 * eps), H[:, :, i], rtol=1e-5, atol=1e-7 * MU)
+
+
+def test_fform_closed_forms_match_the_reference_expressions():
+    """tests/golden/fform_golden.json holds numbers evaluated from the reference's OWN generated F-form code
+    (make_fform_golden.py): Stable-Neohookean 9- and 4-vector gradient / Hessian, Neohookean 9-vector energy / gradient /
+    Hessian (before the psd fix), and the volume term FixedCorot adds in 3D.  The oracle's closed forms reproduce them."""
+    import json
+    import os
+    from oracle import stretch as ost
+    cases = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fform_golden.json")))["cases"]
+    assert len(cases) >= 40
+    seen = set()
+    for c in cases:
+        n = c["n"]; d = 3 if n == 9 else 2
+        F = np.array(c["F"]).reshape(d, d).T[None]                 # column-major vec -> matrix
+        mu, la = c["mu"], c["la"]
+        scale = max(mu, la)
+        if c["model"] == "Stable-Neohookean":
+            g, H = ost.gradient_hessian(F, mu, la)
+            assert np.abs(g[0] - c["g_assign"]).max() <= 1e-12 * scale
+            assert np.abs(H[0] - np.array(c["H_assign"])).max() <= 1e-12 * scale
+            Fv = np.array(c["F"])[None]
+            e = ost.energy_expanded(Fv, mu, la) if d == 3 else ost.energy_expanded_2d(Fv, mu, la)
+            assert abs(e[0] - c["energy"]) <= 1e-12 * scale
+        elif c["model"] == "Neohookean":
+            g, H = ost.neohookean_gradient_hessian(F, mu, la)
+            assert np.abs(g[0] - c["g_assign"]).max() <= 1e-11 * scale
+            Href = np.array(c["H_assign"])
+            assert np.abs(H[0] - Href).max() <= 1e-11 * max(scale, np.abs(Href).max())
+            assert abs(ost.neohookean_energy(F, mu, la)[0] - c["energy"]) <= 1e-12 * scale
+        else:
+            gv, Hv = ost.volume_term(F, la)
+            assert np.abs(gv[0] - c["g_add"]).max() <= 1e-12 * scale
+            assert np.abs(Hv[0] - np.array(c["H_add"])).max() <= 1e-12 * scale
+        seen.add((c["model"], n))
+    assert seen == {("Stable-Neohookean", 9), ("Stable-Neohookean", 4), ("Neohookean", 9), ("FixedCorot", 9)}
+
+
+@pytest.mark.parametrize("model,dim", [("Neohookean", 3), ("FixedCorot", 3), ("ARAP", 2), ("FixedCorot", 2)])
+def test_fform_gradients_are_derivatives_of_the_energies(model, dim):
+    """central differences: g = d psi / dF and (before the psd fix) H = dg / dF for the F-forms that are not pure expression
+    text - the ARAP parts (rotation and its derivative) and, for FixedCorot 2D, the whole form.  FixedCorot 3D: the
+    reference's energy lacks the volume term its gradient has (fixed_corotational.cpp:215-223), so g is checked against
+    psi + la/2 (J - 1)^2."""
+    from oracle import stretch as ost
+    rng = np.random.default_rng(2)
+    mu, la = 3.0, 7.0
+    F = np.eye(dim)[None] + 0.2 * rng.standard_normal((6, dim, dim))
+    M = dim * dim
+
+    def psi(Fm):
+        e, _, _ = ost.model_energy_gradient_hessian(model, Fm, mu, la)
+        if model == "FixedCorot" and dim == 3:
+            e = e + 0.5 * la * (np.linalg.det(Fm) - 1.0) ** 2
+        return e
+    _, g, _ = ost.model_energy_gradient_hessian(model, F, mu, la)
+    eps = 1e-6
+    for k in range(M):
+        dF = np.zeros((dim, dim)); dF[k % dim, k // dim] = eps
+        fd = (psi(F + dF[None]) - psi(F - dF[None])) / (2 * eps)
+        assert np.abs(fd - g[:, k]).max() <= 1e-7 * (mu + la)
