@@ -226,8 +226,10 @@ int mfb_dual_solve_cg(mfb_ctx* ctx, double* la, double tol, int max_iters, int* 
 
 /* ---- the non-mixed Stretch<DIM> variable (src/variables/stretch.cpp:16-91) on the same mesh, Assembler
  * pattern and scatter map: F-form material (material_model.h:43-62), H_e = Jloc^T d2psi/dF2 Jloc vol h^2 with
- * sim::simple_psd_fix(H, 0), g_e = Jloc^T dpsi/dF vol h^2.  One material per mesh: Stable-Neohookean (tets, 2D triangles) or ARAP (tets; H = mu (I - dR/dF), no psd fix)
- * (MFB_ERR_UNSUPPORTED otherwise).  x: d*nV. ---- */
+ * sim::simple_psd_fix, g_e = Jloc^T dpsi/dF vol h^2.  One material per mesh, every F-form overload the reference has: Stable-Neohookean
+ * (tets, 2D triangles; fix at 0), Neohookean (tets; fix at 1e-6), FixedCorot (tets, 2D triangles; ARAP part + volume term, fix at 1e-6, the
+ * reference's quirks kept: no volume term in the 3D energy, mu in 3D where 2D has 2 mu), ARAP (tets, 2D triangles; H = mu (I - dR/dF), no
+ * fix).  Corot has no F-form in the reference and Fung's returns zeros: MFB_ERR_UNSUPPORTED.  x: d*nV. ---- */
 int mfb_stretch_update(mfb_ctx* ctx, const double* x, double h);             /* Stretch::update, stretch.cpp:33-60 (x host) */
 int mfb_stretch_update_dev(mfb_ctx* ctx, const double* x_dev, double h);
 int mfb_stretch_lhs_values(mfb_ctx* ctx, double* values);                    /* lhs().valuePtr(), nnz values on mfb_csr_pattern */

@@ -127,6 +127,23 @@ __device__ __forceinline__ bool arap_f_form(const double* F, double mu, double* 
   return ok;
 }
 
+// 2D ARAP part (arap.cpp:96-132, fixed_corotational.cpp:153-195): R = U V^T with the flip fix of mfem::svd<double,2>, and
+// dR/dF = 2/(s0 + s1) q0 q0^T, q0 = vec(U [0 -1; 1 0] V^T)/sqrt 2.  In closed form: R = Rot(atan2(c - b, a + d)),
+// s0 + s1 = 2 Q = |(a + d, c - b)|, U Sk V^T = +-R Sk, so dR/dF = vec(R Sk) vec(R Sk)^T / (2 Q), vec(R Sk) = (-sr, cr, -cr, -sr).
+__device__ __forceinline__ void arap2_parts(const double* F, double* R, double* q, double* inv_sum) {
+  const double E = 0.5 * (F[0] + F[3]), Hh = 0.5 * (F[1] - F[2]);
+  const double Q = sqrt(E * E + Hh * Hh);
+  const double cr = Q > 0.0 ? E / Q : 1.0, sr = Q > 0.0 ? Hh / Q : 0.0;
+  R[0] = cr; R[1] = sr; R[2] = -sr; R[3] = cr;
+  q[0] = -sr; q[1] = cr; q[2] = -cr; q[3] = -sr;
+  *inv_sum = Q > 0.0 ? 1.0 / (2.0 * Q) : 0.0;
+}
+
+// psd-fix tolerance of each F-form Hessian: Stable-Neohookean simple_psd_fix(H, 0.0) (stable_neohookean.cpp:228,322),
+// Neohookean / FixedCorot simple_psd_fix(H) with the default 1e-6 (neohookean.cpp:227, fixed_corotational.cpp:210,358),
+// ARAP none (arap.cpp:112-162): negative = no fix
+__device__ __forceinline__ double fform_fix_tol(int model) { return model == 0 ? 0.0 : (model == 4 ? -1.0 : 1e-6); }
+
 template <int DIM>
 __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double* __restrict__ x, double h2, double* __restrict__ Avals,
                                                         double* __restrict__ grad, unsigned long long* __restrict__ counters) {
@@ -142,17 +159,40 @@ __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double*
   const double k1 = la * (J - 1.0) - mu;
   const double scale = m.vol[e] * h2;
   double g9[M], H[M * (M + 1) / 2];
-  bool arap = false;
-  if constexpr (DIM == 3) arap = mat.model == 4;
-  if (arap) {
+  const int model = mat.model;
+  // ---- the ARAP part of ARAP / FixedCorot: g = c (F - R), H = c (I - dR/dF); c = mu, except FixedCorot 2D: 2 mu
+  if (model == 4 || model == 3) {
     if constexpr (DIM == 3) {
       double R[9];
       if (!arap_f_form(F, mu, R, g9, H)) atomicAdd(&counters[1], 1ull);     // polar_hfail
+    } else {
+      const double cm = (model == 3) ? 2.0 * mu : mu;
+      double R[4], q[4], is;
+      arap2_parts(F, R, q, &is);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) g9[i] = cm * (F[i] - R[i]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) H[symidx(i, j)] = cm * ((i == j ? 1.0 : 0.0) - is * q[i] * q[j]);
     }
   } else {
-    // Stable Neo-Hookean: gradient, Hessian (packed lower), then simple_psd_fix(H, 0)
 #pragma unroll
-    for (int i = 0; i < M; ++i) g9[i] = mu * F[i] + k1 * C[i];
+    for (int i = 0; i < M; ++i) g9[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < M * (M + 1) / 2; ++i) H[i] = 0.0;
+  }
+  // ---- the part that goes through J:  g += a0 F + a1 cof F ;  H += a0 I + a2 cof cof^T + a1 d2J/dF2
+  //   Stable-Neohookean  a0 = mu, a1 = la (J - 1) - mu,        a2 = la                        (stable_neohookean.cpp:109-226)
+  //   Neohookean         a0 = mu, a1 = (la log J - mu) / J,     a2 = (la (1 - log J) + mu) / J^2  (neohookean.cpp:108-226)
+  //   FixedCorot         a0 = 0,  a1 = la (J - 1),              a2 = la                        (fixed_corotational.cpp:233-357)
+  if (model != 4) {
+    double a0 = 0.0, a1, a2;
+    if (model == 0) { a0 = mu; a1 = k1; a2 = la; }
+    else if (model == 1) { const double lj = log(J), ij = 1.0 / J; a0 = mu; a1 = (la * lj - mu) * ij; a2 = (la * (1.0 - lj) + mu) * ij * ij; }
+    else { a1 = la * (J - 1.0); a2 = la; }
+#pragma unroll
+    for (int i = 0; i < M; ++i) g9[i] += a0 * F[i] + a1 * C[i];
 #pragma unroll
     for (int i = 0; i < M; ++i)
 #pragma unroll
@@ -160,13 +200,16 @@ __global__ void __launch_bounds__(128) k_stretch_update(DevMesh m, const double*
         double dd;
         if constexpr (DIM == 3) dd = d2J(F, i % 3, i / 3, j % 3, j / 3);
         else dd = d2J2(i % 2, i / 2, j % 2, j / 2);
-        H[symidx(i, j)] = (i == j ? mu : 0.0) + la * C[i] * C[j] + k1 * dd;
+        H[symidx(i, j)] += (i == j ? a0 : 0.0) + a2 * C[i] * C[j] + a1 * dd;
       }
+  }
+  // ---- sim::simple_psd_fix(H, tol): eigenvalues below tol are set to tol
+  const double ftol = fform_fix_tol(model);
+  if (ftol >= 0.0) {
     double V[M * M], ev[M];
     jacobi_eig<M>(H, V);
 #pragma unroll
-    for (int k = 0; k < M; ++k) ev[k] = H[symidx(k, k)] < 0.0 ? 0.0 : H[symidx(k, k)];
-    // Hfix = V max(L, 0) V^T, packed lower, back into H
+    for (int k = 0; k < M; ++k) ev[k] = H[symidx(k, k)] < ftol ? ftol : H[symidx(k, k)];
 #pragma unroll
     for (int i = 0; i < M; ++i)
 #pragma unroll
@@ -235,17 +278,25 @@ __global__ void __launch_bounds__(128) k_stretch_energy(DevMesh m, const double*
     double i1 = 0.0;
 #pragma unroll
     for (int i = 0; i < M; ++i) i1 += F[i] * F[i];
-    val = (mat.mu * (1.0 - J) + 0.5 * mat.la * (1.0 - J) * (1.0 - J) + 0.5 * mat.mu * (i1 - (double)DIM)) * m.vol[e];
-    if constexpr (DIM == 3) {
-      if (mat.model == 4) {      // ARAP: mu/2 (|F|^2 - 2 tr S + 3), tr S = R : F   (arap.cpp:134-141)
-        double R[9], Y[9];
+    double psi = mat.mu * (1.0 - J) + 0.5 * mat.la * (1.0 - J) * (1.0 - J) + 0.5 * mat.mu * (i1 - (double)DIM);      // Stable-Neohookean
+    if (mat.model == 1) { const double lj = log(J); psi = 0.5 * mat.mu * (i1 - 3.0) - mat.mu * lj + 0.5 * mat.la * lj * lj; }   // neohookean.cpp:93-106
+    if (mat.model == 3 || mat.model == 4) {
+      if constexpr (DIM == 3) {      // ARAP and (sic, no volume term) FixedCorot: mu/2 (|F|^2 - 2 tr S + 3), tr S = R : F (arap.cpp:134-141,
+        double R[9], Y[9];           // fixed_corotational.cpp:215-223)
         polar_from_identity(F, R, Y);
         double trS = 0.0;
 #pragma unroll
         for (int i = 0; i < 9; ++i) trS += R[i] * F[i];
-        val = 0.5 * mat.mu * (i1 - 2.0 * trS + 3.0) * m.vol[e];
+        psi = 0.5 * mat.mu * (i1 - 2.0 * trS + 3.0);
+      } else {                       // 2D: ARAP mu/2 |F - R|^2 (arap.cpp:82-94) ; FixedCorot mu |F - R|^2 + la/2 (J - 1)^2 (fixed_corotational.cpp:136-151)
+        double R[4], q[4], is, d2 = 0.0;
+        arap2_parts(F, R, q, &is);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) d2 += (F[i] - R[i]) * (F[i] - R[i]);
+        psi = (mat.model == 4) ? 0.5 * mat.mu * d2 : mat.mu * d2 + 0.5 * mat.la * (J - 1.0) * (J - 1.0);
       }
     }
+    val = psi * m.vol[e];
   }
   const double r = block_sum_128(val, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = r;
@@ -261,8 +312,11 @@ int stretch_get(mfb_ctx* c, StretchState** out) {
   if (c->matid.p) {
     g_last_error = "Stretch variable: one material per mesh"; return MFB_ERR_UNSUPPORTED;
   }
-  if (!(c->mat0_host.model == 0 || (c->mat0_host.model == 4 && c->dim == 3))) {
-    g_last_error = "Stretch variable: F-forms on the device are Stable-Neohookean (2D, 3D) and ARAP (3D)"; return MFB_ERR_UNSUPPORTED;
+  const int mdl = c->mat0_host.model;      // the F-form overloads the reference has: material_model.h:43-62 and the per-model files
+  if (!(mdl == 0 || mdl == 3 || mdl == 4 || (mdl == 1 && c->dim == 3))) {
+    g_last_error = "Stretch variable: the reference has F-forms for Stable-Neohookean, ARAP, FixedCorot (2D, 3D) and Neohookean (3D) only "
+                   "(Corot has none, Fung's returns zeros)";
+    return MFB_ERR_UNSUPPORTED;
   }
   if (!c->stretch) {
     StretchState* s = new StretchState();
