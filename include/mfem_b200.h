@@ -177,6 +177,10 @@ typedef struct mfb_newton_log {   /* the OptimizerData columns of newton_optimiz
   double energy[MFB_NEWTON_LOG_MAX], energy_res[MFB_NEWTON_LOG_MAX], decrement[MFB_NEWTON_LOG_MAX], alpha[MFB_NEWTON_LOG_MAX];
   double cg_error[MFB_NEWTON_LOG_MAX];
   int32_t cg_iters[MFB_NEWTON_LOG_MAX], ls_iters[MFB_NEWTON_LOG_MAX];
+  /* option "convergence_log" = 1: what apps/convergence.cpp:21-51 records through Optimizer::callback at the TOP of every
+   * Newton iteration (newton_optimizer.cpp:37) - |x.rhs() + Stretch.rhs()|_2 of the NON-mixed system (the Stretch<DIM>
+   * variable with each element's F-form material) at the current mixed iterate; else untouched */
+  double fem_gradient_norm[MFB_NEWTON_LOG_MAX];
 } mfb_newton_log;
 /* Displacement::reset + BDF1 state: free_map as given to mfb_create; h = SimConfig::h; force = body force d-vector
  * (NULL: gravity (0,-9.8,0)); x0 / v0 host d*nV or NULL (vec(Vref^T), zero).  Also builds PMP^T on the Assembler pattern.

@@ -73,7 +73,8 @@ class _NewtonLog(C.Structure):
                 ("energy", C.c_double * NEWTON_LOG_MAX), ("energy_res", C.c_double * NEWTON_LOG_MAX),
                 ("decrement", C.c_double * NEWTON_LOG_MAX), ("alpha", C.c_double * NEWTON_LOG_MAX),
                 ("cg_error", C.c_double * NEWTON_LOG_MAX),
-                ("cg_iters", C.c_int32 * NEWTON_LOG_MAX), ("ls_iters", C.c_int32 * NEWTON_LOG_MAX)]
+                ("cg_iters", C.c_int32 * NEWTON_LOG_MAX), ("ls_iters", C.c_int32 * NEWTON_LOG_MAX),
+                ("fem_gradient_norm", C.c_double * NEWTON_LOG_MAX)]
 
 
 def build(force=False, verbose=False):
@@ -263,7 +264,8 @@ class MixedStretch:
         return {"n_iters": log.n_iters, "cg_iters_total": log.cg_iters_total,
                 "energy": np.array(log.energy[:n]), "energy_res": np.array(log.energy_res[:n]),
                 "decrement": np.array(log.decrement[:n]), "alpha": np.array(log.alpha[:n]),
-                "cg_iters": np.array(log.cg_iters[:n]), "cg_error": np.array(log.cg_error[:n]), "ls_iters": np.array(log.ls_iters[:n])}
+                "cg_iters": np.array(log.cg_iters[:n]), "cg_error": np.array(log.cg_error[:n]), "ls_iters": np.array(log.ls_iters[:n]),
+                "fem_gradient_norm": np.array(log.fem_gradient_norm[:n])}
 
     def newton_positions_dev(self):
         """(device pointer of x, d*nV ; device pointer of the PMP^T values on the Assembler pattern)"""

@@ -26,6 +26,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "update_exchange")) { c->update_exchange = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "p2p")) { c->use_p2p = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "cg_graph")) { c->cg_graph = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "convergence_log")) { c->convergence_log = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "pipe")) { c->pipe = value; return MFB_OK; }       // 0 off, n > 0: persistent pipelined update kernel, n CTAs per SM slot
   if (!strcmp(name, "cheb_degree")) { if (value < 1 || value > 16) return MFB_ERR_INVALID; c->cheb_degree = value; return MFB_OK; }
   if (!strcmp(name, "cheb_ratio")) { if (value < 2) return MFB_ERR_INVALID; c->cheb_ratio = value; return MFB_OK; }

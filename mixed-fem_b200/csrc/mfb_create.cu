@@ -414,6 +414,8 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
     TRY(upload(c->matid, hmat, st));
     c->h_matid.assign(d->mat_id, d->mat_id + nE);
   }
+  c->h_mat_model.resize(d->n_mat);
+  for (int i = 0; i < d->n_mat; ++i) c->h_mat_model[i] = d->materials[i].model;
   c->h_mat_density.resize(d->n_mat);
   for (int i = 0; i < d->n_mat; ++i) c->h_mat_density[i] = d->materials[i].density > 0 ? d->materials[i].density : 1000.0;
   std::vector<MaterialDev> hm(d->n_mat);

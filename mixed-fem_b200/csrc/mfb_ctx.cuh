@@ -124,6 +124,7 @@ struct mfb_ctx {
   std::vector<int32_t> h_outer, h_inner, h_smap, h_sstride;
   std::vector<int32_t> h_matid;          // kept for mfb_newton_init's per-material densities
   std::vector<double> h_mat_density;
+  std::vector<int32_t> h_mat_model;      // model of every material (the Stretch variable checks that each has an F-form)
   // flags
   bool rhs_valid = false;     // rhs_/gl_ match the current S_, s_, g_, H_, dSdF_
   bool updated = false;
@@ -162,6 +163,7 @@ struct mfb_ctx {
   // point-to-point exchange (mfb_comm_set_partition): neighbour ranks, entry offsets, local free id per entry, and per
   // local free row the list of its entries (rowif_ptr / rowif_idx: the CG kernels write / read their halo through it)
   int use_p2p = 1, update_exchange = 0;
+  int convergence_log = 0;                    // mfb_newton_step records the non-mixed gradient norm per iteration (apps/convergence.cpp)
   int pipe = 0;                               // update kernel: persistent software-pipelined variant (option "pipe")
   int cg_graph = 0;                           // mfb_pcg_dev: replay batches of 32 iterations as a CUDA graph (option "cg_graph"; measured: no gain, the
                                               // iteration is bound by its kernels on 1 GPU and by the latency of its 3 NCCL kernels on several)

@@ -112,6 +112,18 @@ __global__ void __launch_bounds__(128) k_inertia_energy(DevMesh m, const double*
   if (threadIdx.x == 0) partials[blockIdx.x] = r;
 }
 
+// partial sums of |a - b|^2 (deterministic two-stage sum: 256 blocks, then k_sum_partials)
+__global__ void __launch_bounds__(256) k_sub_sqnorm(const double* __restrict__ a, const double* __restrict__ b, int64_t n, double* __restrict__ partials) {
+  __shared__ double sh[8];
+  double v = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) { const double d = a[i] - b[i]; v += d * d; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) { double r = 0.0; for (int k = 0; k < 8; ++k) r += sh[k]; partials[blockIdx.x] = r; }
+}
+
 // y(full) = x(full) + a * P^T dx(free)
 template <int DIM>
 __global__ void k_unproject_axpy(const double* __restrict__ x, const int* __restrict__ vfree, const double* __restrict__ dx, double a, int nV, double* __restrict__ y) {
@@ -340,6 +352,26 @@ extern "C" int mfb_newton_step(mfb_ctx* c, const mfb_newton_opts* o, mfb_newton_
   struct NoUpdateExchange { mfb_ctx* c; int saved; NoUpdateExchange(mfb_ctx* c_) : c(c_), saved(c_->update_exchange) { c->update_exchange = 0; }
                             ~NoUpdateExchange() { c->update_exchange = saved; } } no_update_exchange(c);
   do {
+    if (c->convergence_log) {
+      // Optimizer::callback at the top of the iteration (newton_optimizer.cpp:37) as apps/convergence.cpp:21-51 uses it:
+      // rhs = x.rhs() + Stretch.rhs() = -PM (x - x_tilde - h^2 f) - grad_stretch(x), its 2-norm
+      if (c->world > 1) { g_last_error = "convergence_log: single-GPU contexts only"; return MFB_ERR_UNSUPPORTED; }
+      const double* gs = nullptr;
+      if ((rc = mfb_stretch_update_dev(c, s->x.p, s->h)) || (rc = mfb_stretch_dev(c, nullptr, &gs))) return rc;
+      MFB_CUDA(cudaMemsetAsync(s->b.p, 0, (size_t)nf * 8, st));
+      if (dim == 3) {
+        k_inertia_diff<3><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], h2 * s->f[2], nV, s->diff.p);
+        k_mass_rows_apply<3><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, -1.0, s->b.p);
+      } else {
+        k_inertia_diff<2><<<nblk(nx), 256, 0, st>>>(s->x.p, s->xt.p, h2 * s->f[0], h2 * s->f[1], 0.0, nV, s->diff.p);
+        k_mass_rows_apply<2><<<c->grid(), 128, 0, st>>>(c->mesh(), s->emass.p, s->diff.p, -1.0, s->b.p);
+      }
+      k_sub_sqnorm<<<256, 256, 0, st>>>(s->b.p, gs, nf, c->partials.p);
+      c->launches += 3;
+      double n2 = 0.0;
+      if ((rc = sum_partials(c, 256, &n2))) return rc;
+      if (i < MFB_NEWTON_LOG_MAX) log->fem_gradient_norm[i] = std::sqrt(n2);
+    }
     // update_system(): var->update(unprojected x, dt)
     phase_begin(c, MFB_PH_UPDATE);
     rc = mfb_update_dev(c, s->x.p, s->h);

@@ -309,14 +309,14 @@ struct StretchState {
 
 int stretch_get(mfb_ctx* c, StretchState** out) {
   if (c->kind == MFB_SHELL) { g_last_error = "Stretch variable: tetrahedra and 2D triangles only"; return MFB_ERR_UNSUPPORTED; }
-  if (c->matid.p) {
-    g_last_error = "Stretch variable: one material per mesh"; return MFB_ERR_UNSUPPORTED;
-  }
-  const int mdl = c->mat0_host.model;      // the F-form overloads the reference has: material_model.h:43-62 and the per-model files
-  if (!(mdl == 0 || mdl == 3 || mdl == 4 || (mdl == 1 && c->dim == 3))) {
-    g_last_error = "Stretch variable: the reference has F-forms for Stable-Neohookean, ARAP, FixedCorot (2D, 3D) and Neohookean (3D) only "
-                   "(Corot has none, Fung's returns zeros)";
-    return MFB_ERR_UNSUPPORTED;
+  // every material of the mesh needs an F-form overload in the reference: material_model.h:43-62 and the per-model files
+  for (size_t i = 0; i < c->h_mat_model.size(); ++i) {
+    const int mdl = c->h_mat_model[i];
+    if (!(mdl == 0 || mdl == 3 || mdl == 4 || (mdl == 1 && c->dim == 3))) {
+      g_last_error = "Stretch variable: the reference has F-forms for Stable-Neohookean, ARAP, FixedCorot (2D, 3D) and Neohookean (3D) only "
+                     "(Corot has none, Fung's returns zeros)";
+      return MFB_ERR_UNSUPPORTED;
+    }
   }
   if (!c->stretch) {
     StretchState* s = new StretchState();

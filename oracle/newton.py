@@ -76,13 +76,20 @@ class OracleNewton:
         diff = x - self.x_tilde() - self.h ** 2 * self.fext
         return 0.5 * float(diff @ (self.M @ diff))
 
-    def step(self, outer_steps=5, ls_iters=20, newton_tol=1e-10, cg=None):
+    def step(self, outer_steps=5, ls_iters=20, newton_tol=1e-10, cg=None, stretch=None):
+        """stretch: an oracle.stretch.OracleStretch on the same mesh => log["fem_gradient_norm"] holds what
+        apps/convergence.cpp:21-51 records at the top of every iteration (Optimizer::callback, newton_optimizer.cpp:37):
+        |x.rhs() + Stretch.rhs()|_2 of the non-mixed system at the current mixed iterate"""
         var, h = self.var, self.h
         h2 = h * h
-        log = {k: [] for k in ("energy", "energy_res", "decrement", "alpha", "cg_iters", "ls_iters")}
+        log = {k: [] for k in ("energy", "energy_res", "decrement", "alpha", "cg_iters", "ls_iters", "fem_gradient_norm")}
         i, E_prev = 0, 0.0
         tm = self.timers
         while True:
+            if stretch is not None:
+                stretch.update(self.x, h)
+                d0 = self.x - self.x_tilde() - h2 * self.fext
+                log["fem_gradient_norm"].append(float(np.linalg.norm(-(self.PM @ d0) + stretch.rhs())))
             t0 = time.perf_counter()
             var.update(self.x, h)
             t1 = time.perf_counter(); tm["update"] += t1 - t0

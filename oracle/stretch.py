@@ -197,9 +197,13 @@ def simple_psd_fix(H, tol=0.0):
 
 
 class OracleStretch:
-    def __init__(self, V, T, free_map, mu, la, model="Stable-Neohookean"):
+    def __init__(self, V, T, free_map, mu=None, la=None, model="Stable-Neohookean", materials=None, mat_id=None):
+        """one material (mu, la, model) or `materials` = [(model, mu, la), ...] with a per-element index `mat_id`
+        (Mesh::elements_[i].material_, mesh.cpp:21-23: Stretch::update asks each element's own material, stretch.cpp:41-46)"""
         self.V, self.T, self.fm = np.asarray(V, float), np.asarray(T), np.asarray(free_map)
-        self.mu, self.la, self.model = mu, la, model
+        self.materials = [(model, mu, la)] if materials is None else [tuple(m[:3]) for m in materials]
+        self.mat_id = np.zeros(self.T.shape[0], dtype=np.int64) if mat_id is None else np.asarray(mat_id, dtype=np.int64)
+        self.mu, self.la, self.model = self.materials[0][1], self.materials[0][2], self.materials[0][0]
         self.d = d = self.V.shape[1]
         X = self.V[self.T]
         Dm = np.transpose(X[:, 1:, :] - X[:, :1, :], (0, 2, 1))
@@ -216,14 +220,24 @@ class OracleStretch:
         d = self.d
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
         Fv = np.transpose(F, (0, 2, 1)).reshape(-1, d * d)
-        psi, _, _ = model_energy_gradient_hessian(self.model, F, self.mu, self.la)
+        psi, _, _ = self._per_element(F)
         return float(np.sum(psi * self.vol))
+
+    def _per_element(self, F):
+        nE, d = F.shape[0], F.shape[1]
+        M = d * d
+        psi, g, H = np.zeros(nE), np.zeros((nE, M)), np.zeros((nE, M, M))
+        for k, (model, mu, la) in enumerate(self.materials):
+            sel = self.mat_id == k
+            if sel.any():
+                psi[sel], g[sel], H[sel] = model_energy_gradient_hessian(model, F[sel], mu, la)
+        return psi, g, H
 
     def update(self, x, h):
         d = self.d
         nd = d * (d + 1)
         F = meshgen.deformation_gradients(self.V, self.T, np.asarray(x, float))
-        _, g, H = model_energy_gradient_hessian(self.model, F, self.mu, self.la)
+        _, g, H = self._per_element(F)
         w = self.vol * h * h
         He = np.einsum("eia,eij,ejb->eab", self.Jloc, H, self.Jloc) * w[:, None, None]      # (nE,nd,nd)
         ge = np.einsum("eia,ei->ea", self.Jloc, g) * w[:, None]                              # (nE,nd)

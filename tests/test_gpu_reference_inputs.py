@@ -267,3 +267,33 @@ def test_C1_trampoline_device_resident_newton_step_per_object_density(built):
     assert np.array_equal(m2, m3) and m2.max() > 50 * m2[m2 > 0].min()
     for g in (gpu, g2, g3):
         g.close()
+
+
+def test_convergence_driver_gradient_norms_on_the_trampoline_scene(built, tmp_path):
+    """apps/convergence.cpp (the reference's integration harness, DIM = 2): per Newton iteration the gradient norm of the
+    NON-mixed system (Stretch variable, each element's own F-form material) at the mixed iterate.  tools/convergence.py on
+    scenes/2D/trampoline.json against the oracle's Newton loop + OracleStretch; the DMAT it writes round-trips."""
+    import importlib.util
+    from oracle import newton as onewton
+    from oracle import stretch as ostretch
+    spec = importlib.util.spec_from_file_location("convergence", os.path.join(ri.HERE, "..", "tools", "convergence.py"))
+    conv = importlib.util.module_from_spec(spec); spec.loader.exec_module(conv)
+    path = os.path.join(ri.RI, "scenes/2D/trampoline.json")
+    G = conv.run(path, 2, root=ri.SCENES_ROOT, dim=2, cg_tol=1e-14)
+    sc = _trampoline()
+    assert G.shape == (2, sc.outer_steps)
+    cpu = orc.OracleMixedStretch(sc.V, sc.T, sc.free_map, sc.materials, mat_id=sc.mat_id); cpu.reset()
+    no = onewton.OracleNewton(cpu, sc.V, sc.T, sc.free_map, density=sc.density_e, h=sc.h, force=sc.body_force)
+    st = ostretch.OracleStretch(sc.V, sc.T, sc.free_map, materials=sc.materials, mat_id=sc.mat_id)
+    for i in range(2):
+        lo = no.step(outer_steps=sc.outer_steps, ls_iters=sc.ls_iters, stretch=st)
+        ref = lo["fem_gradient_norm"]
+        # the first iterations are far from the noise floor: 1e-8; once the step is converged (norms 1e-6 of the first) both
+        # sides sit on rounding noise of the linear solves and only the order of magnitude is comparable
+        big = ref > 1e-5 * ref[0]
+        k = int(big.sum())
+        assert k >= 2
+        assert np.all(np.abs(G[i, :k] - ref[:k]) <= 1e-8 * ref[:k]), (G[i], ref)
+    p = str(tmp_path / "convergence.dmat")
+    sceneio.write_dmat(p, G)
+    assert np.array_equal(sceneio.read_dmat(p), G)

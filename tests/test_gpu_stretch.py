@@ -81,6 +81,31 @@ def test_stretch_remaining_f_forms_match_oracle(built, model, n, scale):
     gpu.close()
 
 
+def test_stretch_per_element_materials_match_oracle(built):
+    """one F-form material per element (the reference's Stretch variable asks each element's own material_,
+    stretch.cpp:36-60): SNH and FixedCorot halves of one mesh, different Lame parameters"""
+    V, T = meshgen.kuhn_grid(6, 4, 3)
+    fm = meshgen.pinned_free_map(V)
+    x = meshgen.deformed_positions(V, 1.0 / 6, scale=3.0)
+    mats = [("Stable-Neohookean", MU, LA), ("FixedCorot", 0.5 * MU, 2.0 * LA)]
+    mid = (np.arange(T.shape[0]) % 3 == 0).astype(np.int32)
+    h = 0.0333
+    gpu = mf.MixedStretch(V, T, fm, mats, mat_id=mid)
+    cpu = ostretch.OracleStretch(V, T, fm, materials=mats, mat_id=mid)
+    cpu.update(x, h)
+    gpu.stretch_update(x, h)
+    outer, inner, vals = gpu.stretch_lhs()
+    A = sp.csr_matrix((vals, inner, outer), shape=cpu.lhs.shape)
+    assert abs(A - cpu.lhs).max() <= 1e-10 * abs(cpu.lhs).max()
+    assert vec_rel(gpu.stretch_gradient(), cpu.grad) <= 1e-10
+    assert abs(gpu.stretch_energy(x) - cpu.energy(x)) <= 1e-10 * abs(cpu.energy(x))
+    # and it is not the single-material answer
+    one = ostretch.OracleStretch(V, T, fm, MU, LA)
+    one.update(x, h)
+    assert vec_rel(one.grad, cpu.grad) > 1e-3
+    gpu.close()
+
+
 def test_stretch_rejects_what_it_does_not_implement(built):
     V, T = meshgen.kuhn_grid(2, 2, 2)
     fm = meshgen.pinned_free_map(V)
