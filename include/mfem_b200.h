@@ -310,7 +310,19 @@ int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels t
 int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0), "cg_zero_guess" (0:
                                                                        mfb_newton_step starts CG from the reference's guess),
                                                                        "update_exchange" (0; multi-GPU, see mfb_comm_set_partition),
-                                                                       "p2p" (1: use the neighbour exchange when a partition is set) */
+                                                                       "p2p" (1: use the neighbour exchange when a partition is set).
+                                                                       Solver / optimizer: "cg_graph" (0), "cheb_degree" (6),
+                                                                       "cheb_ratio" (120), "convergence_log" (0: fill
+                                                                       mfb_newton_log.fem_gradient_norm, one GPU).
+                                                                       Update-kernel variants kept for A/B measurement, all
+                                                                       results identical to rounding: "asm_mode" (1 reductions
+                                                                       into the block-CSR upper triangle; 0 into the scalar CSR;
+                                                                       2 deterministic gather, bit-stable), "stage_finalize"
+                                                                       (0; 1 = finalize per element chunk on a side stream,
+                                                                       measured slower), "pipe" (0; persistent pipelined kernel,
+                                                                       measured slower), "smem_b" (3 = v4; 0..2 the round-1
+                                                                       kernels), "exp" (what-if timing bits, WRONG results).
+                                                                       Unknown names return MFB_ERR_INVALID. */
 /* device time of the update kernel alone, CUDA events on the ctx stream, accumulated while option "profile" is 1 */
 int mfb_kernel_time_ms(mfb_ctx* ctx, double* total_ms, int* count);
 /* Phase timers under the reference's own Timer keys (src/optimizers/optimizer_data.cpp:127-256; MixedStretch brackets its

@@ -27,6 +27,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "p2p")) { c->use_p2p = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "cg_graph")) { c->cg_graph = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "convergence_log")) { c->convergence_log = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "stage_finalize")) { c->stage_finalize = value != 0; return MFB_OK; }   // 1: k_finalize_rows per element chunk on a side stream under the next chunks (default 0: measured slower)
   if (!strcmp(name, "pipe")) { c->pipe = value; return MFB_OK; }       // 0 off, n > 0: persistent pipelined update kernel, n CTAs per SM slot
   if (!strcmp(name, "cheb_degree")) { if (value < 1 || value > 16) return MFB_ERR_INVALID; c->cheb_degree = value; return MFB_OK; }
   if (!strcmp(name, "cheb_ratio")) { if (value < 2) return MFB_ERR_INVALID; c->cheb_ratio = value; return MFB_OK; }
@@ -125,12 +126,51 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   const bool bulk = v4 && c->asm_mode == 1;
   const bool det = v4 && c->asm_mode == 2;
   if (det) { int rcd = build_det_lists(c); if (rcd) return rcd; }
+  const bool big = c->nE >= (1 << 18);
+  const bool multi_x = bulk && c->world > 1 && c->update_exchange && c->use_p2p && c->ent_local.p && c->n_if_elems > 0 && c->n_if_elems < c->nE;
+  const bool chunk_x = bulk && c->x_host_chunked && big;
+  const bool staged = bulk && c->stage_finalize && c->fin_rows.p && big && !multi_x && c->pipe == 0 && c->nb > 0;
   MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
   if (det) {
     // every CSR value and every vertex entry is WRITTEN by the gather kernels: nothing to zero
   } else if (bulk) {
     MFB_CUDA(cudaMemsetAsync(c->gxrh.p, 0, (size_t)6 * c->nF * 8, st));
-    if (c->nbu) MFB_CUDA(cudaMemsetAsync(c->Ablk.p, 0, (size_t)c->nbu * 9 * 8, st));
+    const size_t ablk_bytes = (size_t)c->nbu * 9 * 8;
+    if (staged) {
+      if (!c->fin_stream) {
+        int lo = 0, hi = 0;
+        MFB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        static const int fin_prio = getenv("MFB_FIN_PRIO") ? atoi(getenv("MFB_FIN_PRIO")) : 1;      // 1: highest priority
+        MFB_CUDA(cudaStreamCreateWithPriority(&c->fin_stream, cudaStreamNonBlocking, fin_prio ? hi : lo));
+        MFB_CUDA(cudaStreamCreateWithFlags(&c->zero_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < mfb_ctx::kChunks; ++k) MFB_CUDA(cudaEventCreateWithFlags(&c->ev_stage[k], cudaEventDisableTiming));
+        MFB_CUDA(cudaEventCreateWithFlags(&c->ev_fin, cudaEventDisableTiming));
+        MFB_CUDA(cudaEventCreateWithFlags(&c->ev_upd, cudaEventDisableTiming));
+        for (int k = 0; k < 2; ++k) MFB_CUDA(cudaEventCreateWithFlags(&c->ev_zero[k], cudaEventDisableTiming));
+      }
+      const int cur = c->ablk_cur, oth = cur ^ 1;
+      if (ablk_bytes) {
+        if (c->ablk_clean[cur]) MFB_CUDA(cudaStreamWaitEvent(st, c->ev_zero[cur], 0));
+        else MFB_CUDA(cudaMemsetAsync(c->ablk(cur), 0, ablk_bytes, st));
+        // the other accumulator is cleared for the NEXT update while this one runs: its last reader (the finalize of the
+        // previous update) was joined into this stream before anything queued here
+        static const int zero_overlap = getenv("MFB_ZERO_OVERLAP") ? atoi(getenv("MFB_ZERO_OVERLAP")) : 1;
+        if (!zero_overlap) { c->ablk_clean[oth] = false; goto zero_done; }
+        MFB_CUDA(cudaEventRecord(c->ev_upd, st));
+        MFB_CUDA(cudaStreamWaitEvent(c->zero_stream, c->ev_upd, 0));
+        MFB_CUDA(cudaMemsetAsync(c->ablk(oth), 0, ablk_bytes, c->zero_stream));
+        MFB_CUDA(cudaEventRecord(c->ev_zero[oth], c->zero_stream));
+        c->ablk_clean[oth] = true;
+      }
+      zero_done:
+      c->ablk_clean[cur] = false;
+      MFB_CUDA(cudaMemsetAsync(c->chunk_cnt.p, 0, 2 * mfb_ctx::kChunks * sizeof(unsigned long long), st));
+    } else {
+      // (a pending clear of this buffer on the zero stream, if any, is ordered before this one: same event)
+      if (c->ablk_clean[c->ablk_cur] && c->ev_zero[c->ablk_cur]) MFB_CUDA(cudaStreamWaitEvent(st, c->ev_zero[c->ablk_cur], 0));
+      else if (ablk_bytes) MFB_CUDA(cudaMemsetAsync(c->ablk(c->ablk_cur), 0, ablk_bytes, st));
+      c->ablk_clean[c->ablk_cur] = false;
+    }
   } else {
     MFB_CUDA(cudaMemsetAsync(c->grad_x.p, 0, (size_t)c->dim * c->nF * 8, st));
     if (c->fuse_rhs) MFB_CUDA(cudaMemsetAsync(c->rhs.p, 0, (size_t)c->dim * c->nF * 8, st));
@@ -189,32 +229,58 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       if (c->nb > 0) k_det_gather_blocks<<<nblk(c->nb), 256, 0, st>>>(c->blockptr.p, c->brow.p, c->det_bptr.p, c->det_bent.p, c->nb, c->Kelem.p, c->Avals.p);
       LAUNCHED(c, 3);
     } else if (bulk) {
-      if (c->x_host_chunked && c->nE >= (1 << 18)) {
-        // host positions: upload x in pieces on the copy stream and start each element chunk when its vertices are there
-        const double* xh = c->x_host_chunked;
-        MFB_CUDA(cudaEventRecord(c->ev_in, st));                       // everything queued so far (earlier readers of xdev)
-        MFB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_in, 0));
-        int vdone = 0;
-        for (int k = 0; k < mfb_ctx::kChunks; ++k) {
-          const int vhi = k + 1 == mfb_ctx::kChunks ? c->nV : c->chunk_vhi[k];
-          if (vhi > vdone) {
+      if (chunk_x || staged) {
+        // element chunks.  Host positions (mfb_update): x goes up in pieces on the copy stream and each chunk starts when
+        // its vertices are there.  Staged finalize: behind each chunk, on a side stream, its Jacobi tail and the block-rows
+        // that are final with it (see mfb_ctx::stage_finalize).
+        const double* xh = chunk_x ? c->x_host_chunked : nullptr;
+        if (xh) {
+          MFB_CUDA(cudaEventRecord(c->ev_in, st));                     // everything queued so far (earlier readers of xdev)
+          MFB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_in, 0));
+        }
+        static const int fin_threads = getenv("MFB_FIN_THREADS") ? atoi(getenv("MFB_FIN_THREADS")) : 256;
+        int vdone = 0, nlaunch = 0;
+        for (int k = 0; k < c->nchunks; ++k) {
+          const int vhi = k + 1 == c->nchunks ? c->nV : c->chunk_vhi[k];
+          if (xh && vhi > vdone) {
             MFB_CUDA(cudaMemcpyAsync(c->xdev.p + (size_t)3 * vdone, xh + (size_t)3 * vdone, (size_t)(vhi - vdone) * 24, cudaMemcpyHostToDevice, c->copy_stream));
             vdone = vhi;
-            if (k + 1 == mfb_ctx::kChunks) MFB_CUDA(cudaEventRecord(c->ev_in, c->copy_stream));     // the caller's buffer is free after this
+            if (k + 1 == c->nchunks) MFB_CUDA(cudaEventRecord(c->ev_in, c->copy_stream));     // the caller's buffer is free after this
             MFB_CUDA(cudaEventRecord(c->ev_chunk[k], c->copy_stream));
             MFB_CUDA(cudaStreamWaitEvent(st, c->ev_chunk[k], 0));
-          } else if (k + 1 == mfb_ctx::kChunks) {
+          } else if (xh && k + 1 == c->nchunks) {
             MFB_CUDA(cudaEventRecord(c->ev_in, c->copy_stream));
           }
           const int e0 = c->chunk_e0[k], ne = c->chunk_e0[k + 1] - e0;
           if (ne <= 0) continue;
           const unsigned g = (unsigned)((ne + kV4Threads - 1) / kV4Threads);
-          if (c->fuse_rhs) k_update_tet_v4<true, 1><<<g, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, e0);
-          else k_update_tet_v4<false, 1><<<g, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, e0);
+          DevAsm ak = a;
+          if (staged) { ak.slow_list = a.slow_list + e0; ak.slow_cnt = c->chunk_cnt.p + 2 * k; }
+          if (c->fuse_rhs) k_update_tet_v4<true, 1><<<g, kV4Threads, smem, st>>>(m, s, ak, x_dev, h2, e0);
+          else k_update_tet_v4<false, 1><<<g, kV4Threads, smem, st>>>(m, s, ak, x_dev, h2, e0);
+          ++nlaunch;
+          if (!staged) continue;
+          MFB_CUDA(cudaEventRecord(c->ev_stage[k], st));
+          MFB_CUDA(cudaStreamWaitEvent(c->fin_stream, c->ev_stage[k], 0));
+          const unsigned gt = std::min(g, (unsigned)tail_grid);
+          if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<gt, kV4Threads, smem, c->fin_stream>>>(m, s, ak, x_dev, h2);
+          else k_update_tet_v4_tail<false, 1><<<gt, kV4Threads, smem, c->fin_stream>>>(m, s, ak, x_dev, h2);
+          const int nrows = c->fin_ptr[k + 1] - c->fin_ptr[k];
+          if (nrows > 0)
+            k_finalize_rows<<<(unsigned)(((int64_t)nrows * 16 + fin_threads - 1) / fin_threads), fin_threads, 0, c->fin_stream>>>(
+                c->blockptr.p, c->diagblk.p, c->fcode.p, c->fin_rows.p + c->fin_ptr[k], nrows, a.Ablk, c->Avals.p);
+          nlaunch += 2;
         }
-        LAUNCHED(c, mfb_ctx::kChunks - 1);
-        c->x_host_chunked = nullptr;                                   // consumed
-      } else if (c->world > 1 && c->update_exchange && c->use_p2p && c->ent_local.p && c->n_if_elems > 0 && c->n_if_elems < c->nE) {
+        if (staged) {
+          MFB_CUDA(cudaEventRecord(c->ev_fin, c->fin_stream));
+          MFB_CUDA(cudaStreamWaitEvent(st, c->ev_fin, 0));
+          k_fold_chunk_counts<<<1, 32, 0, st>>>(c->chunk_cnt.p, c->nchunks, c->counters.p);
+          ++nlaunch;
+          c->ablk_cur ^= 1;
+        }
+        LAUNCHED(c, nlaunch - 1);
+        if (xh) c->x_host_chunked = nullptr;                           // consumed
+      } else if (multi_x) {
         // multi-GPU with a partition: the leading INTERFACE elements first (and their share of the Jacobi tail), then the
         // point-to-point sum of their vertex vectors (grad_x | rhs, still interleaved) on a side stream while the
         // interior elements - which touch no shared vertex - run on this one
@@ -248,7 +314,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
         else k_update_tet_v4_pipe<false><<<gp, kV4Threads, smem + kV4SmemPipe, st>>>(m, s, a, x_dev, h2, 0, c->nE);
       } else if (c->fuse_rhs) k_update_tet_v4<true, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
       else k_update_tet_v4<false, 1><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0);
-      if (!exchanged) {
+      if (!exchanged && !staged) {
         if (c->fuse_rhs) k_update_tet_v4_tail<true, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
         else k_update_tet_v4_tail<false, 1><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2);
       }
@@ -256,8 +322,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       // CSR values are still being written, see mfb_rhs)
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
       if (c->ev_vec) { MFB_CUDA(cudaEventRecord(c->ev_vec, st)); vec_recorded = true; }
-      if (c->nb > 0) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, c->nF, c->Ablk.p, c->Avals.p);
-      LAUNCHED(c, 3);
+      if (c->nb > 0 && !staged) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, nullptr, c->nF, a.Ablk, c->Avals.p);
+      LAUNCHED(c, staged ? 1 : 3);
     } else {
       if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
       else { k_update_tet_v4<false, 0><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<false, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }

@@ -392,16 +392,32 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
 #define TRY(x) do { rc = (x); if (rc) { delete c; return rc; } } while (0)
   { std::vector<double> hv(d->Vref, d->Vref + (size_t)dim * d->nV); TRY(upload(c->vref, hv, st)); MFB_CUDA(cudaStreamSynchronize(st)); }
   {   // element chunks (multiples of the 128-thread CTA) and the vertices each one needs
-    const int ctas = (nE + 127) / 128;
+    const int ctas = (nE + kV4Threads - 1) / kV4Threads;
     int vmax = -1;
-    for (int k = 0; k < mfb_ctx::kChunks; ++k) {
-      c->chunk_e0[k] = (int)((int64_t)ctas * k / mfb_ctx::kChunks) * 128;
-      const int e1 = k + 1 == mfb_ctx::kChunks ? nE : (int)((int64_t)ctas * (k + 1) / mfb_ctx::kChunks) * 128;
+    if (getenv("MFB_CHUNKS")) c->nchunks = std::max(1, std::min((int)mfb_ctx::kChunks, atoi(getenv("MFB_CHUNKS"))));   // experiments
+    for (int k = 0; k < c->nchunks; ++k) {
+      c->chunk_e0[k] = (int)((int64_t)ctas * k / c->nchunks) * kV4Threads;
+      const int e1 = k + 1 == c->nchunks ? nE : (int)((int64_t)ctas * (k + 1) / c->nchunks) * kV4Threads;
       for (int e = c->chunk_e0[k]; e < e1 && e < nE; ++e)
         for (int j = 0; j < npe; ++j) vmax = std::max(vmax, (int)d->T[(size_t)e * npe + j]);
       c->chunk_vhi[k] = vmax + 1;
     }
-    c->chunk_e0[mfb_ctx::kChunks] = nE;
+    for (int k = c->nchunks; k <= mfb_ctx::kChunks; ++k) c->chunk_e0[k] = nE;
+  }
+  std::vector<int> hfin;
+  if (d->elem_kind == MFB_TET && nF > 0) {   // staged finalize: block-rows grouped by the chunk of the last element that holds them
+    std::vector<int> lastc((size_t)nF, 0);
+    int k = 0;
+    for (int e = 0; e < nE; ++e) {
+      while (e >= c->chunk_e0[k + 1]) ++k;
+      for (int j = 0; j < npe; ++j) { const int f = hf[(size_t)j * ld + e]; if (f >= 0) lastc[f] = k; }     // e ascends: the last write wins
+    }
+    for (int q = 0; q <= mfb_ctx::kChunks; ++q) c->fin_ptr[q] = 0;
+    for (int f = 0; f < nF; ++f) c->fin_ptr[lastc[f] + 1]++;
+    for (int q = 0; q < mfb_ctx::kChunks; ++q) c->fin_ptr[q + 1] += c->fin_ptr[q];
+    hfin.resize((size_t)nF);
+    std::vector<int> pos(c->fin_ptr, c->fin_ptr + mfb_ctx::kChunks);
+    for (int f = 0; f < nF; ++f) hfin[(size_t)pos[lastc[f]]++] = f;
   }
   TRY(upload(c->T, hT, st)); TRY(upload(c->fidx, hf, st)); TRY(upload(c->dphi, hdphi, st)); TRY(upload(c->vol, hvol, st));
   if (d->elem_kind == MFB_SHELL) { TRY(upload(c->nrest, hnrm, st)); TRY(c->xupd.alloc((size_t)3 * d->nV)); MFB_CUDA(cudaMemcpyAsync(c->xupd.p, c->vref.p, (size_t)3 * d->nV * 8, cudaMemcpyDeviceToDevice, st)); }
@@ -430,6 +446,10 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
   if (c->kind == MFB_TET) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 32 * kV4SinkSlots)); TRY(c->gxrh.alloc((size_t)6 * nF + 32 * kV4SinkSlots));   /* + the reduction sinks */ TRY(c->slow_list.alloc((size_t)nE + 1)); }
+  if (c->kind == MFB_TET) {
+    TRY(c->Ablk2.alloc((size_t)c->nbu * 9 + 32 * kV4SinkSlots)); TRY(c->chunk_cnt.alloc(2 * mfb_ctx::kChunks));
+    if (!hfin.empty()) TRY(upload(c->fin_rows, hfin, st));
+  }
   TRY(c->counters.alloc(8)); TRY(c->xdev.alloc((size_t)dim * c->nV)); TRY(c->vecF.alloc((size_t)dim * nF + 1));
   TRY(c->partials.alloc((size_t)c->grid() + 1024)); TRY(c->scal.alloc(16));
   TRY(c->soa_tmp.alloc(N * ld)); TRY(c->soa_tmp2.alloc(N * ld));
@@ -460,6 +480,12 @@ extern "C" void mfb_destroy(mfb_ctx* c) {
     cudaStreamDestroy(c->copy_stream); cudaEventDestroy(c->ev_in); cudaEventDestroy(c->ev_vec);
     for (int k = 0; k < mfb_ctx::kChunks; ++k) if (c->ev_chunk[k]) cudaEventDestroy(c->ev_chunk[k]);
   }
+  for (int k = 0; k < mfb_ctx::kChunks; ++k) if (c->ev_stage[k]) cudaEventDestroy(c->ev_stage[k]);
+  if (c->ev_fin) cudaEventDestroy(c->ev_fin);
+  if (c->ev_upd) cudaEventDestroy(c->ev_upd);
+  for (int k = 0; k < 2; ++k) if (c->ev_zero[k]) cudaEventDestroy(c->ev_zero[k]);
+  if (c->fin_stream) cudaStreamDestroy(c->fin_stream);
+  if (c->zero_stream) cudaStreamDestroy(c->zero_stream);
   if (c->h_scal) cudaFreeHost(c->h_scal);
   delete c;
 }

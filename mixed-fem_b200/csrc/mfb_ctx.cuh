@@ -148,10 +148,30 @@ struct mfb_ctx {
   bool ev_vec_valid = false;
   // chunked upload of x in mfb_update: element chunk k needs the vertices below chunk_vhi[k] (prefix maximum over the
   // chunk's elements, from mfb_create), so its kernel starts as soon as that part of x has arrived
-  static constexpr int kChunks = 8;
+  static constexpr int kChunks = 32;      // at most
+  int nchunks = 8;
   int chunk_e0[kChunks + 1] = {0};
   int chunk_vhi[kChunks] = {0};
   cudaEvent_t ev_chunk[kChunks] = {0};
+  // staged finalize (option stage_finalize; OFF by default - measured on B200 at 10M tets: 5.15 .. 5.5 ms per update against
+  // 5.07 ms for the single pass, for 2 .. 16 chunks, either stream priority, finalize CTAs of 64 .. 256 threads, with and
+  // without the concurrent memset: the element kernel is latency-bound and loses more to the extra memory traffic beside it
+  // than the 0.8 ms of finalize + memset it hides; profiles/README.md): block-row gi of the CSR is final once
+  // the last element that holds vertex gi has run, so k_finalize_rows goes out per element chunk, on a side stream, over
+  // the rows whose last element lies in that chunk (fin_rows sorted by chunk, fin_ptr[k] .. fin_ptr[k+1]), while the next
+  // chunks run; each chunk keeps its own list of slow elements (slow_list + chunk_e0[k], counter chunk_cnt[2k]) so that its
+  // Jacobi tail can run right behind it.  The upper-triangle accumulator is double-buffered: while update n reduces into
+  // Ablk_buf[n % 2], a memset on a third stream clears the other one for update n + 1.
+  int stage_finalize = 0;
+  mfb::DBuf<int> fin_rows;
+  int fin_ptr[kChunks + 1] = {0};
+  mfb::DBuf<unsigned long long> chunk_cnt;       // [2 kChunks]
+  mfb::DBuf<double> Ablk2;
+  int ablk_cur = 0;                              // the buffer asmdesc() hands out
+  bool ablk_clean[2] = {false, false};           // zero (or being zeroed, ev_zero pending) since its last finalize
+  cudaStream_t fin_stream = nullptr, zero_stream = nullptr;
+  cudaEvent_t ev_stage[kChunks] = {0}, ev_fin = nullptr, ev_zero[2] = {nullptr, nullptr}, ev_upd = nullptr;
+  double* ablk(int i) const { return i ? Ablk2.p : Ablk.p; }
   const double* x_host_chunked = nullptr;   // set by mfb_update around its call of mfb_update_dev
   // multi-GPU (mfb_dist.cu): NCCL communicator, this rank's interface vertices (local free id, slot in the packed
   // buffer over all shared vertices), dot-product weights (1 interior / owned interface vertex, 0 copy owned elsewhere)
@@ -192,7 +212,7 @@ struct mfb_ctx {
   }
   mfb::DevAsm asmdesc() const {
     mfb::DevAsm a;
-    a.Ablk = Ablk.p; a.gxrh = gxrh.p; a.bmap = bmap.p; a.slow_list = slow_list.p;
+    a.Ablk = ablk(ablk_cur); a.gxrh = gxrh.p; a.bmap = bmap.p; a.slow_list = slow_list.p; a.slow_cnt = counters.p + 5;
     a.sinkA = nbu * 9; a.sinkV = 6 * nF;
     a.Kelem = Kelem.p; a.Velem = Velem.p;
     return a;

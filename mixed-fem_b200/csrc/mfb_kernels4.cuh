@@ -41,6 +41,19 @@ namespace mfb {
 #ifndef MFB_V4_ROLL_DSDF
 #define MFB_V4_ROLL_DSDF 0
 #endif
+// register cap of the three element kernels: __launch_bounds__(threads, MINB) by default; ptxas only knows a few register
+// levels for it (255 / 168 / 128 ...), so experiments with 9 or 10 warps per SM name the cap itself (MFB_V4_MAXNREG)
+// Experiment (off): CTA barriers at the phase boundaries of the one-tile kernel keep its warps in the same region of the
+// ~95 KB instruction stream (shared instruction-cache lines).
+#ifndef MFB_V4_SYNC
+#define MFB_V4_SYNC 0
+#endif
+#define MFB_V4_SYNCPT() do { if (MFB_V4_SYNC && !TAIL && !PIPE) __syncthreads(); } while (0)
+#ifdef MFB_V4_MAXNREG
+#define MFB_V4_BOUNDS __maxnreg__(MFB_V4_MAXNREG)
+#else
+#define MFB_V4_BOUNDS __launch_bounds__(kV4Threads, MFB_V4_MINB)
+#endif
 constexpr int kV4Threads = MFB_V4_THREADS;
 constexpr int kV4Warps = kV4Threads / 32;
 // per warp: [0,288) reduction staging (one 3x3 block per lane; la[6][32] parks here until step 3),
@@ -71,6 +84,7 @@ struct DevAsm {
   double* gxrh;          // [nF][6]   grad_x | rhs interleaved
   const int* bmap;       // [6][ld]   pairs j < k: 2*upper_block + transposed; one vertex pinned: the free vertex's diagonal slot; both: -1
   int* slow_list;        // [nE]
+  unsigned long long* slow_cnt;   // [0] entries appended, [1] entries an earlier tail launch has done (counters[5], [6], or a chunk's own pair)
   int sinkA, sinkV;      // first of 32 scratch doubles behind Ablk / gxrh (reductions without a target land there)
   double *Kelem, *Velem; // ASM 2: [nE][54] off-diagonal blocks K_e(j,k), j < k, row-major ; [nE][4][6] vertex values (grad_x | rhs)
 };
@@ -242,6 +256,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 #pragma unroll
       for (int r = 0; r < 3; ++r) Y[3 * c + r] = R[r] * F[c] + R[3 + r] * F[3 + c] + R[6 + r] * F[6 + c];
   }
+  MFB_V4_SYNCPT();
   // The block targets of step 3 are known (the codes have landed long ago): pull their lines into the L2 now.
   // An FP64 reduction whose line is not in the L2 waits for the DRAM fill and, behind it, so does everything else in
   // the SM's memory pipe: without this the reductions cost 1.6 ms per 10M tets, with it 0.7 ms.  (The vertex targets
@@ -316,6 +331,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     }
   }
 
+  MFB_V4_SYNCPT();
   // ---- 2 : material gradient / Hessian, PSD fix, inverse, lambda_max
   bool live = inrange;       // false: this lane stores / adds nothing from here on
   double L[21];
@@ -352,7 +368,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
       if (failm) {
         const int leader = __ffs(failm) - 1;
         unsigned long long base = 0;
-        if (lane == leader) base = atomicAdd(&st.counters[5], (unsigned long long)__popc(failm));
+        if (lane == leader) base = atomicAdd(as.slow_cnt, (unsigned long long)__popc(failm));
         base = __shfl_sync(0xffffffffu, base, leader);
         if (fail) as.slow_list[base + __popc(failm & ((1u << lane) - 1u))] = e;
         live = live && ok;
@@ -401,6 +417,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     }
   }
 
+  MFB_V4_SYNCPT();
   // ---- 3 : vertex vectors, and B <- sqrt(vol) B L in place (one row at a time through registers)
   int f[4];
   double tl[6];
@@ -490,6 +507,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
     }
   }
 
+  MFB_V4_SYNCPT();
   // ---- 3 : matrix blocks for the local pairs j <= k
   if (ASM == 0) {
     int stride[4], sidx[16];
@@ -581,7 +599,7 @@ __device__ __forceinline__ void update_tet_v4_body(const DevMesh& m, const DevSt
 }
 
 template <bool FUSE_RHS, int ASM>
-__global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
+__global__ void MFB_V4_BOUNDS k_update_tet_v4(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
                                                                  int e_begin) {
   extern __shared__ __align__(128) double smem4[];
   const int e = e_begin + blockIdx.x * blockDim.x + threadIdx.x;      // e_begin: a multiple of the CTA size (chunked launches)
@@ -598,7 +616,7 @@ __global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4(DevMe
 // into thread-private shared-memory slots.  ncu (profiles/README.md, round 2): 12.8 % of the stall samples of the plain
 // kernel sit on the two chained global latencies at its top (T, then x[T]), which 2 warps per scheduler cannot cover.
 template <bool FUSE_RHS>
-__global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_pipe(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
+__global__ void MFB_V4_BOUNDS k_update_tet_v4_pipe(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2,
                                                                       int e_begin, int e_end) {
   extern __shared__ __align__(128) double smem4[];
   const int w = threadIdx.x >> 5;
@@ -641,15 +659,15 @@ __global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_pipe(
 
 // elements the fast PSD path refused: grid-stride over the list the main kernel built (count in counters[5])
 template <bool FUSE_RHS, int ASM>
-__global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_tail(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
+__global__ void MFB_V4_BOUNDS k_update_tet_v4_tail(DevMesh m, DevState st, DevAsm as, const double* __restrict__ x, double h2) {
   extern __shared__ __align__(128) double smem4[];
   const int w = threadIdx.x >> 5;
   double* sW = smem4 + 54 * kV4Threads + w * kV4StageDoubles;
   int* sC = reinterpret_cast<int*>(smem4 + 54 * kV4Threads + kV4Warps * kV4StageDoubles) + w * 32;
   // list entries [counters[6], counters[5]): counters[6] is 0 unless an earlier tail launch of the same update() has
   // already processed a prefix (interface elements first, see mfb_update_dev / k_mark_tail)
-  const long long n = (long long)st.counters[5];
-  for (long long i0 = (long long)st.counters[6] + (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += (long long)gridDim.x * blockDim.x) {
+  const long long n = (long long)as.slow_cnt[0];
+  for (long long i0 = (long long)as.slow_cnt[1] + (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += (long long)gridDim.x * blockDim.x) {
     const long long i = i0 + (threadIdx.x & 31);
     const bool in = i < n;
     update_tet_v4_body<FUSE_RHS, true, ASM>(m, st, as, x, as.slow_list[in ? i : n - 1], in, h2, smem4, sW, sC);
@@ -662,11 +680,14 @@ __global__ void __launch_bounds__(kV4Threads, MFB_V4_MINB) k_update_tet_v4_tail(
 // upper-triangle copy (transposed when gj < gi), write, and accumulate the row sum.  Diagonal block: -(row sum of the
 // off-diagonal blocks + the K_e(free,pinned) blocks accumulated in its own slot), because every element matrix has
 // zero block-row sums.
+// `rows` (may be null: all rows 0 .. nF-1 in order) lists the nF block-rows of this launch - the staged finalize of
+// mfb_update_dev sends one launch per element chunk, over the rows that are final with that chunk.
 static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restrict__ blockptr, const int* __restrict__ diagblk, const int* __restrict__ fcode,
-                                                              int nF, const double* __restrict__ Ablk, double* __restrict__ A) {
+                                                              const int* __restrict__ rows, int nF, const double* __restrict__ Ablk, double* __restrict__ A) {
   const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int gi = (int)(gt >> 4), l = threadIdx.x & 15;
-  const bool rowok = gi < nF;
+  const int idx = (int)(gt >> 4), l = threadIdx.x & 15;
+  const bool rowok = idx < nF;
+  const int gi = rowok ? (rows ? rows[idx] : idx) : 0;
   int p0 = 0, nbr = 0, dslot = -1;
   if (rowok) { p0 = blockptr[gi]; nbr = blockptr[gi + 1] - p0; dslot = diagblk[gi] - p0; }
   const int rowlen = 3 * nbr, c = l % 3;
@@ -701,6 +722,14 @@ static __global__ void __launch_bounds__(256) k_finalize_rows(const int* __restr
     const double tot = __shfl_sync(0xffffffffu, t, c, 16);       // lanes 0..2 hold the totals of columns c = 0..2
     if (qd >= 0) __stcs(&A[D0 + (int64_t)r * rowlen + qd], -(dval[r] + tot));
   }
+}
+
+// staged finalize: the per-chunk counts of slow elements -> counters[5] (what mfb_status reports)
+static __global__ void k_fold_chunk_counts(const unsigned long long* __restrict__ cnt, int n, unsigned long long* counters) {
+  unsigned long long t = 0;
+  for (int k = threadIdx.x; k < n; k += 32) t += cnt[2 * k];
+  for (int o = 16; o; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+  if (threadIdx.x == 0) { counters[5] = t; counters[6] = t; }
 }
 
 static __global__ void k_mark_tail(unsigned long long* counters) { counters[6] = counters[5]; }

@@ -4,6 +4,7 @@ element->nonzero map bit-exact, procrustes iteration counts identical."""
 import numpy as np
 import pytest
 
+from mixed_fem_b200 import meshgen
 from tests.common import DT, LA, MU, TOL, block_rel, mesh, pair, vec_rel
 
 pytestmark = pytest.mark.gpu
@@ -385,3 +386,46 @@ def test_deterministic_assembly_is_bit_stable_and_matches_the_oracle(built):
     for a, b in zip(runs[0], runs[2]):
         assert np.array_equal(a, b)
     gpu.close()
+
+
+@pytest.mark.parametrize("shuffle", [False, True])
+def test_staged_finalize_matches_the_single_pass(built, shuffle):
+    """Above 2^18 tets update() runs in 16 element chunks and finalizes, behind each one on a side stream, the block-rows
+    whose last element lies in it (option stage_finalize, default 1; per-chunk Jacobi tails; double-buffered accumulator).
+    Same CSR values, vectors and status as the single pass (stage_finalize 0) - to rounding, the reductions are atomic in
+    both - on a coherent element order and on a shuffled one (every row final in the last chunks), through the host-x entry
+    (chunked upload) and the device-x one, three updates in a row (both accumulators in use), a third of the Hessians slow."""
+    import torch
+    import mixed_fem_b200 as mf
+    V, T, fm, h = mesh(3, (40, 40, 30), shuffle=shuffle, jitter=0.1, pin=0.02)
+    assert T.shape[0] >= (1 << 18)
+    mats = [("Stable-Neohookean", MU, LA)]
+    st = meshgen.synthetic_state(V, T, h, MU)
+    rng = np.random.default_rng(3)
+    s = st["s"].reshape(-1, 6).copy()
+    sel = rng.uniform(size=s.shape[0]) < 0.3
+    s[sel, :3] *= rng.uniform(0.45, 0.8, size=(int(sel.sum()), 1))
+    xs = [st["x"], 0.5 * (st["x"] + st["xprev"]), st["x"]]
+    out = {}
+    for mode in (0, 1):
+        g = mf.MixedStretch(V, T, fm, mats)
+        g.reset(); g.set("R", st["R"]); g.set("la", st["la"]); g.set("s", s.reshape(-1))
+        g.set_option("stage_finalize", mode)
+        res = []
+        for i, x in enumerate(xs):
+            if i == 1:
+                xd = torch.as_tensor(x, device="cuda")
+                g.update_dev(xd.data_ptr(), DT)
+            else:
+                g.update(x, DT)
+            stt = g.status()
+            res.append((g.lhs()[2].copy(), g.rhs().copy(), g.get("grad_x").copy(), stt["psd_slow"], g.get("Hinv").copy()))
+        out[mode] = res
+        g.close()
+    for a, b in zip(out[0], out[1]):
+        assert 0 < a[3] < T.shape[0] and a[3] == b[3]
+        assert np.array_equal(a[4], b[4])                       # per-element results do not depend on the launch shape
+        for i in range(3):
+            assert np.abs(a[i] - b[i]).max() <= 1e-12 * np.abs(a[i]).max()
+    # the three updates differ (nothing cached), and the third repeats the first state with a warm-started polar
+    assert np.abs(out[1][0][0] - out[1][1][0]).max() > 1e-6 * np.abs(out[1][0][0]).max()
