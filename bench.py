@@ -469,6 +469,9 @@ def newton_leg(args, grid, material, label, rank=0, world=1, local_rank=0, steps
         ms = mf.MixedStretch(V, T, fm, [(material, mu, la)], device=local_rank)
         del V, T
         ms.reset()
+    for kv in args.opt:                               # library options for A/B runs (e.g. peer=0: NCCL exchange in the CG)
+        name, val = kv.split("=")
+        ms.set_option(name, int(val))
     ms.set_stream(torch.cuda.current_stream().cuda_stream)
     ms.newton_init(density=1000.0, h=DT)
     ms.newton_step(outer_steps=1)                     # warm-up time step
@@ -518,12 +521,26 @@ def newton_leg(args, grid, material, label, rank=0, world=1, local_rank=0, steps
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     cg_ms = lin_ms / cg_total
+    cgcyc = None
+    try:                                              # block 0's SM cycles per phase of the persistent CG kernel (debug export)
+        import ctypes as C
+        buf = (C.c_longlong * 12)()
+        ms.L.mfb_debug_pcg_cycles.argtypes = [C.c_void_p, C.POINTER(C.c_longlong), C.c_int]
+        if ms.L.mfb_debug_pcg_cycles(ms.h, buf, 1) == 0 and sum(buf) > 0:
+            names = ["spmv", "barrier1", "sum1", "post1", "collect1", "update", "barrier2", "sum2", "post2", "collect2", "dir", "barrier3"]
+            tot_it = max(1, sum(int(v) for l in logs for v in l["cg_iters"]))
+            cgcyc = {k: round(buf[i] / tot_it / 1e3, 2) for i, k in enumerate(names)}
+    except Exception:
+        cgcyc = None
     cgb = cg_bytes_per_iteration(nb_l, nF_l)          # this rank's share
     out = {"workload": "%s: %dx%dx%d Kuhn grid = %d tets, %s, dt=%.4f, eigen-pcg-diag tol 1e-4, %d time steps x 3 Newton iterations" %
                        (label, nx, ny, nz, nE, material, DT, steps),
            "n_gpus": world, "ms_per_newton_iteration": el / n, "newton_iterations": n,
            "cg_iterations": [int(v) for l in logs for v in l["cg_iters"]],
            "ms_per_cg_iteration": cg_ms,
+           "cg_persistent_kcycles_per_iteration": cgcyc,
+           "cg_exchange": (None if world == 1 else {1: "peer mailboxes (CUDA IPC over NVLink, inside the CG kernels; no NCCL call per iteration)",
+                                                    -1: "NCCL (peer mailboxes unavailable on this node)", 0: "NCCL"}[ms.peer_state()]),
            "phase_ms_per_newton_iteration": {k: v[0] / n for k, v in ph.items()},
            "roofline_cg": {"bound": "hbm", "unit": "GB/s", "peak": peak, "achieved": cgb / (cg_ms * 1e-3) / 1e9,
                            "frac": cgb / (cg_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_iteration": cgb,

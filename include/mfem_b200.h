@@ -287,6 +287,14 @@ int mfb_comm_set_interface(mfb_ctx* ctx, const int32_t* if_local, const int32_t*
  * every shared vertex of the partition, the CG writes / reads its halo inside its own kernels, and option
  * "update_exchange" = 1 makes mfb_update_dev sum grad_x_ / rhs_ over ranks itself, overlapped with the interior elements. */
 int mfb_comm_set_partition(mfb_ctx* ctx, const mfb_partition* p);
+/* With a partition set and all ranks on one node, the distributed mfb_pcg_dev (preconditioners 0..2) leaves NCCL out of
+ * the iteration: every rank exports one mailbox (cudaMalloc + CUDA IPC, opened by the others on first use), the SpMV
+ * kernel stores its interface rows straight into the neighbours' mailboxes over NVLink, the last block of each kernel
+ * posts the rank's partial dot products and a sequence number to every rank, and the next kernel of the iteration waits
+ * for the sequence numbers in its own memory and adds the partial sums in rank order (bit-identical on all ranks).
+ * Spins are bounded; a timeout makes mfb_pcg_dev return MFB_ERR_CUDA.  Option "peer" = 0 keeps the NCCL exchange; so
+ * does any rank that cannot export or open a mailbox (decided collectively).  1: in use, -1: unavailable, 0: not tried. */
+int mfb_comm_peer_state(mfb_ctx* ctx);
 /* a (ncomp_a doubles per local free vertex) and optionally b <- sum over ranks at interface vertices, one collective */
 int mfb_interface_sum_dev(mfb_ctx* ctx, double* a_dev, int ncomp_a, double* b_dev, int ncomp_b);
 int mfb_allreduce_dev(mfb_ctx* ctx, double* v_dev, int n, int op);   /* op 0 sum, 1 max; stream-ordered */
@@ -310,7 +318,8 @@ int mfb_num_kernel_launches(mfb_ctx* ctx, int64_t* n, int reset);   /* kernels t
 int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs" (default 1), "profile" (0), "cg_zero_guess" (0:
                                                                        mfb_newton_step starts CG from the reference's guess),
                                                                        "update_exchange" (0; multi-GPU, see mfb_comm_set_partition),
-                                                                       "p2p" (1: use the neighbour exchange when a partition is set).
+                                                                       "p2p" (1: use the neighbour exchange when a partition is set),
+                                                                       "peer" (1: peer mailboxes, see mfb_comm_peer_state).
                                                                        Solver / optimizer: "cg_graph" (0), "cheb_degree" (6),
                                                                        "cheb_ratio" (120), "convergence_log" (0: fill
                                                                        mfb_newton_log.fem_gradient_norm, one GPU).

@@ -34,7 +34,7 @@ EXPORTS = [
     "mfb_kkt_size", "mfb_kkt_product", "mfb_kkt_rhs", "mfb_kkt_layout_dev", "mfb_kkt_product_dev", "mfb_kkt_solve_minres",
     "mfb_dual_product", "mfb_dual_product_dev", "mfb_dual_rhs", "mfb_dual_solve_cg",
     "mfb_stretch_update", "mfb_stretch_update_dev", "mfb_stretch_lhs_values", "mfb_stretch_gradient", "mfb_stretch_dev", "mfb_stretch_energy",
-    "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_comm_set_partition", "mfb_interface_sum_dev", "mfb_allreduce_dev",
+    "mfb_comm_unique_id", "mfb_comm_init", "mfb_comm_set_interface", "mfb_comm_set_partition", "mfb_comm_peer_state", "mfb_interface_sum_dev", "mfb_allreduce_dev",
     "mfb_partition_create", "mfb_partition_destroy", "mfb_partition_sizes", "mfb_partition_get",
     "mfb_energy_noalloc_dev", "mfb_noalloc_max_elements",
 ]
@@ -575,6 +575,12 @@ class MixedStretch:
         ipos = np.ascontiguousarray(local.if_pos, dtype=np.int32)
         w = _f64(local.dot_weight)
         self._check(self.L.mfb_comm_set_interface(self.h, _ip(il), _ip(ipos), int(il.size), int(local.n_shared), _dp(w)))
+
+    def peer_state(self):
+        """1: the CG exchanges through peer mailboxes (CUDA IPC), -1: unavailable on this node (NCCL), 0: not tried yet"""
+        self.L.mfb_comm_peer_state.argtypes = [C.c_void_p]
+        self.L.mfb_comm_peer_state.restype = C.c_int
+        return int(self.L.mfb_comm_peer_state(self.h))
 
     def interface_sum_dev(self, a_ptr, ncomp_a, b_ptr=None, ncomp_b=0):
         self._check(self.L.mfb_interface_sum_dev(self.h, C.c_void_p(a_ptr), ncomp_a, C.c_void_p(b_ptr) if b_ptr else None, ncomp_b))

@@ -27,6 +27,8 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "p2p")) { c->use_p2p = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "cg_graph")) { c->cg_graph = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "convergence_log")) { c->convergence_log = value ? 1 : 0; return MFB_OK; }
+  if (!strcmp(name, "cg_persist")) { c->cg_persist = value; return MFB_OK; }      // persistent cooperative CG kernel: 2 (default) below 64 Ki block-rows, 1 always, 0 never (three launches per iteration)
+  if (!strcmp(name, "peer")) { c->use_peer = value != 0; return MFB_OK; }      // 1 (default): CG halo + dot products through peer mailboxes (CUDA IPC) when every rank can open them; 0: NCCL
   if (!strcmp(name, "stage_finalize")) { c->stage_finalize = value != 0; return MFB_OK; }   // 1: k_finalize_rows per element chunk on a side stream under the next chunks (default 0: measured slower)
   if (!strcmp(name, "pipe")) { c->pipe = value; return MFB_OK; }       // 0 off, n > 0: persistent pipelined update kernel, n CTAs per SM slot
   if (!strcmp(name, "cheb_degree")) { if (value < 1 || value > 16) return MFB_ERR_INVALID; c->cheb_degree = value; return MFB_OK; }

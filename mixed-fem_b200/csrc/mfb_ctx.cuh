@@ -43,6 +43,31 @@ struct DBuf {   // plain device buffer
 struct mfb_ctx;
 struct mfb_partition;
 namespace mfb {
+// ---- peer mailboxes (mfb_dist.cu: peer_setup; used inside the CG kernels of mfb_pcg.cu) -----------------------------
+// One cudaMalloc'ed mailbox per rank, opened by every other rank of the node through CUDA IPC (NVLink / NVSwitch peer
+// memory).  A rank STORES its interface rows of t = L p straight into its neighbours' mailboxes from inside the SpMV
+// kernel, and the last block of a kernel stores the rank's partial dot products into EVERY rank's mailbox followed by a
+// sequence number; the consuming kernel of the same CG iteration polls its OWN mailbox (local L2) until all sequence
+// numbers have arrived and adds the partial sums in rank order - the same bits on every rank.  No NCCL call and no host
+// round trip inside the iteration.  Layout in 8-byte words:
+//   [0, 16)   flag[stage][src rank]         sequence number of the last exchange src has posted for this stage
+//   [16, 80)  sc[stage][parity][src rank][2] partial sums (stage 0: p.Lp ; stage 1: r.r, r.z)
+//   [80, 96)  bc[stage][parity][4]           local: the sums block 0 has collected (sum0, sum1, ok) for this GPU's other blocks
+//   [96, 98)  go[stage]                      local: sequence number block 0 has published
+//   [128, ..) halo[parity][n_ent * 3]       this rank's receive segments, one per neighbour, in its own entry order
+// Spins are bounded (kPeerSpinLimit polls of >= 128 ns): on a timeout the kernel raises scal[13] and the stop flag.
+constexpr int kPeerMax = 8;
+constexpr int kPeerFlagWords = 2 * kPeerMax, kPeerScWords = 2 * 2 * kPeerMax * 2, kPeerHaloWord0 = 128;
+constexpr long long kPeerSpinLimit = 1LL << 24;
+struct PeerView {
+  int world, rank, n_ent;
+  unsigned long long* flag_at[2][kPeerMax];     // [stage][r]: &flag[stage][me] in rank r's mailbox (r == me: the local one)
+  double* sc_at[2][kPeerMax];                   // [stage][r]: &sc[stage][0][me][0] in rank r's mailbox
+  unsigned long long* my_flag;                  // local mailbox
+  double* my_sc;
+  double* my_halo;                              // halo[0]; parity 1 follows at 3 n_ent doubles
+  double* const* dst;                           // [parity][n_ent]: where entry s of this rank's send list lands (peer memory)
+};
 // mfb_dist.cu (no-ops when world == 1)
 int interface_sum(mfb_ctx* c, double* a, int na, double* b, int nb, double* scal, int ns);
 int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop);
@@ -65,6 +90,7 @@ void phase_begin(mfb_ctx* c, int key);                            // mfb_api.cu
 void phase_end(mfb_ctx* c, int key);
 int partition_view(const mfb_partition* p, PartitionView* v);      // mfb_partition.cu
 int build_det_lists(mfb_ctx* c);                                  // mfb_create.cu (asm_mode 2)
+int peer_setup(mfb_ctx* c);                                       // mfb_dist.cu: collective; sets c->peer_state
 // point-to-point halo of the CG (mfb_dist.cu): group{ send/recv of the packed interface rows ; all-reduce of `ns` scalars }
 int halo_exchange(mfb_ctx* c, int ncomp, double* scal, int ns);
 int halo_buffers(mfb_ctx* c, int ncomp, double** send, double** recv);
@@ -117,6 +143,9 @@ struct mfb_ctx {
   mfb::DBuf<double> xdev, vecF, partials, scal, aos, soa_tmp, soa_tmp2;
   // pcg work vectors
   mfb::DBuf<double> pcg_r, pcg_p, pcg_z, pcg_t, pcg_dinv, pcg_part, pcg_lhs;
+  mfb::DBuf<int> pcg_abort;
+  mfb::DBuf<long long> pcg_prof;
+  int cg_persist = 2;        // option: the CG loop as one persistent cooperative kernel (mfb_pcg.cu: k_pcg_persist); 2 = for small systems
   mfb::DBuf<double> pcg_res, pcg_d;          // Chebyshev preconditioner (precond 3): inner residual and correction
   int cheb_degree = 6, cheb_ratio = 120;       // options "cheb_degree", "cheb_ratio" (lambda_max / lambda_min of the target interval)
   double* h_scal = nullptr;   // pinned
@@ -192,6 +221,13 @@ struct mfb_ctx {
   mfb::DBuf<int> ent_local, rowif_ptr, rowif_idx;
   mfb::DBuf<double> xsend, xrecv;
   int xbuf_comp = 0;
+  // peer mailboxes (option "peer", default 1; state: 0 not tried, 1 in use, -1 unavailable on this node -> NCCL path)
+  int use_peer = 1, peer_state = 0;
+  void* peer_box = nullptr;                      // this rank's mailbox (cudaMalloc, exported)
+  void* peer_base[mfb::kPeerMax] = {nullptr};    // the others', opened with cudaIpcOpenMemHandle
+  mfb::DBuf<double*> peer_dst;
+  mfb::DBuf<mfb::PeerView> peer_view;
+  unsigned long long peer_seq = 0;               // sequence numbers handed out so far (same on every rank)
   cudaStream_t xstream = 0;                   // side stream of the overlapped exchange in mfb_update_dev
   cudaEvent_t ev_x0 = 0, ev_x1 = 0;
 

@@ -208,7 +208,115 @@ int allreduce_scalars(mfb_ctx* c, double* v, int n, bool maxop) {
   return MFB_OK;
 }
 
+// ---- peer mailboxes: see PeerView in mfb_ctx.cuh --------------------------------------------------------------------
+static void peer_free(mfb_ctx* c) {
+  for (int r = 0; r < kPeerMax; ++r) if (c->peer_base[r]) { cudaIpcCloseMemHandle(c->peer_base[r]); c->peer_base[r] = nullptr; }
+  if (c->peer_box) { cudaFree(c->peer_box); c->peer_box = nullptr; }
+  c->peer_state = 0;
+  (void)cudaGetLastError();
+}
+
+// Collective over the communicator (every rank calls it at the same point: the first distributed mfb_pcg_dev after
+// mfb_comm_set_partition).  Allocates and exports this rank's mailbox, gathers everybody's IPC handle and receive offsets
+// (grouped ncclSend / ncclRecv), opens the others' mailboxes and builds the destination table of the halo stores.  Any
+// failure on any rank (no IPC in this container, no peer access between two devices) leaves peer_state = -1 on EVERY
+// rank - the decision is taken from gathered data - and the CG stays on the NCCL exchange.
+int peer_setup(mfb_ctx* c) {
+  if (c->peer_state != 0) return MFB_OK;
+  c->peer_state = -1;
+  if (c->world <= 1 || c->world > kPeerMax || !c->use_peer || !c->ent_local.p) return MFB_OK;
+  NcclApi* api = nccl();
+  cudaStream_t st = c->stream;
+  const int W = c->world, me = c->rank;
+  const size_t words = (size_t)kPeerHaloWord0 + 2 * (size_t)c->n_ent * 3 + 8;
+  long long ok = 1;
+  void* box = nullptr;
+  cudaIpcMemHandle_t h;
+  memset(&h, 0, sizeof(h));
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  if (cudaMalloc(&box, words * 8) != cudaSuccess) { ok = 0; box = nullptr; }
+  if (ok && cudaMemset(box, 0, words * 8) != cudaSuccess) ok = 0;
+  if (ok && cudaIpcGetMemHandle(&h, box) != cudaSuccess) ok = 0;
+  (void)cudaGetLastError();
+  // blob per rank: [0,8) handle, [8] ok, [9] n_ent, [10 + r] first entry of the segment this rank receives from rank r (-1: none)
+  const int bw = 10 + W;
+  std::vector<long long> mine((size_t)bw, -1), all((size_t)bw * W, 0);
+  memcpy(mine.data(), &h, 64);
+  mine[8] = ok; mine[9] = c->n_ent;
+  for (int q = 0; q < c->n_nbr; ++q) mine[10 + c->nbr_rank[q]] = c->nbr_off[q];
+  DBuf<long long> dm, da;
+  int rc;
+  if ((rc = dm.alloc((size_t)bw)) || (rc = da.alloc((size_t)bw * W))) { if (box) cudaFree(box); return rc; }
+  MFB_CUDA(cudaMemcpyAsync(dm.p, mine.data(), (size_t)bw * 8, cudaMemcpyHostToDevice, st));
+  ncclResult_t r = api->GroupStart();
+  if (r != ncclSuccess) return nccl_fail("ncclGroupStart", r);
+  for (int q = 0; q < W; ++q) {
+    if (q == me) continue;
+    if ((r = api->Send(dm.p, (size_t)bw, ncclInt64, q, (ncclComm_t)c->comm, st)) != ncclSuccess) return nccl_fail("ncclSend", r);
+    if ((r = api->Recv(da.p + (size_t)q * bw, (size_t)bw, ncclInt64, q, (ncclComm_t)c->comm, st)) != ncclSuccess) return nccl_fail("ncclRecv", r);
+  }
+  if ((r = api->GroupEnd()) != ncclSuccess) return nccl_fail("ncclGroupEnd", r);
+  MFB_CUDA(cudaMemcpyAsync(all.data(), da.p, (size_t)bw * W * 8, cudaMemcpyDeviceToHost, st));
+  MFB_CUDA(cudaStreamSynchronize(st));
+  memcpy(&all[(size_t)me * bw], mine.data(), (size_t)bw * 8);
+  bool all_ok = true;
+  for (int q = 0; q < W; ++q) all_ok = all_ok && all[(size_t)q * bw + 8] == 1;
+  // the two sides of every cut must describe the same segment
+  for (int q = 0; q < c->n_nbr && all_ok; ++q) all_ok = all[(size_t)c->nbr_rank[q] * bw + 10 + me] >= 0;
+  if (!all_ok) { if (box) cudaFree(box); (void)cudaGetLastError(); return MFB_OK; }
+  c->peer_box = box;
+  double opened = 1.0;
+  for (int q = 0; q < W; ++q) {
+    if (q == me) continue;
+    cudaIpcMemHandle_t hq;
+    memcpy(&hq, &all[(size_t)q * bw], 64);
+    if (cudaIpcOpenMemHandle(&c->peer_base[q], hq, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peer_base[q] = nullptr; opened = 0.0; (void)cudaGetLastError(); }
+  }
+  {   // did everybody open everything?  min over ranks = -max(-x)
+    DBuf<double> flag;
+    if ((rc = flag.alloc(1))) return rc;
+    const double neg = -opened;
+    MFB_CUDA(cudaMemcpyAsync(flag.p, &neg, 8, cudaMemcpyHostToDevice, st));
+    if ((rc = allreduce_scalars(c, flag.p, 1, true))) return rc;
+    double res = 0.0;
+    MFB_CUDA(cudaMemcpyAsync(&res, flag.p, 8, cudaMemcpyDeviceToHost, st));
+    MFB_CUDA(cudaStreamSynchronize(st));
+    if (res != -1.0) { peer_free(c); c->peer_state = -1; return MFB_OK; }
+  }
+  PeerView pv;
+  memset(&pv, 0, sizeof(pv));
+  pv.world = W; pv.rank = me; pv.n_ent = c->n_ent;
+  for (int q = 0; q < W; ++q) {
+    unsigned long long* b = (unsigned long long*)(q == me ? c->peer_box : c->peer_base[q]);
+    for (int stg = 0; stg < 2; ++stg) {
+      pv.flag_at[stg][q] = b + stg * kPeerMax + me;
+      pv.sc_at[stg][q] = (double*)b + kPeerFlagWords + (size_t)stg * 2 * kPeerMax * 2 + (size_t)me * 2;
+    }
+  }
+  pv.my_flag = (unsigned long long*)c->peer_box;
+  pv.my_sc = (double*)c->peer_box + kPeerFlagWords;
+  pv.my_halo = (double*)c->peer_box + kPeerHaloWord0;
+  std::vector<double*> dst((size_t)2 * c->n_ent + 1, nullptr);
+  for (int q = 0; q < c->n_nbr; ++q) {
+    const int rr = c->nbr_rank[q];
+    const long long off = all[(size_t)rr * bw + 10 + me], n_ent_r = all[(size_t)rr * bw + 9];
+    double* halo_r = (double*)c->peer_base[rr] + kPeerHaloWord0;
+    for (int sidx = c->nbr_off[q]; sidx < c->nbr_off[q + 1]; ++sidx)
+      for (int par = 0; par < 2; ++par)
+        dst[(size_t)par * c->n_ent + sidx] = halo_r + (size_t)par * 3 * n_ent_r + (size_t)(off + (sidx - c->nbr_off[q])) * c->dim;
+  }
+  if ((rc = c->peer_dst.alloc(dst.size())) || (rc = c->peer_view.alloc(1))) return rc;
+  MFB_CUDA(cudaMemcpyAsync(c->peer_dst.p, dst.data(), dst.size() * sizeof(double*), cudaMemcpyHostToDevice, st));
+  pv.dst = c->peer_dst.p;
+  MFB_CUDA(cudaMemcpyAsync(c->peer_view.p, &pv, sizeof(pv), cudaMemcpyHostToDevice, st));
+  MFB_CUDA(cudaStreamSynchronize(st));
+  c->peer_seq = 0;
+  c->peer_state = 1;
+  return MFB_OK;
+}
+
 void comm_free(mfb_ctx* c) {
+  peer_free(c);
   if (c->xstream) { cudaStreamDestroy(c->xstream); c->xstream = 0; }
   if (c->ev_x0) { cudaEventDestroy(c->ev_x0); cudaEventDestroy(c->ev_x1); c->ev_x0 = c->ev_x1 = 0; }
   if (c->comm && nccl()->ok) nccl()->CommDestroy((ncclComm_t)c->comm);
@@ -288,6 +396,7 @@ extern "C" int mfb_comm_set_partition(mfb_ctx* c, const mfb_partition* p) {
   c->n_ent = c->nbr_off[c->n_nbr];
   c->n_if_elems = v.n_if_elems;
   c->xbuf_comp = 0;
+  peer_free(c);                  // sized and addressed for the previous partition, if any
   // per local free row: its entries
   std::vector<int> ptr((size_t)c->nF + 1, 0), idx((size_t)c->n_ent);
   for (int i = 0; i < c->n_ent; ++i) {
@@ -307,6 +416,8 @@ extern "C" int mfb_comm_set_partition(mfb_ctx* c, const mfb_partition* p) {
   MFB_CUDA(cudaStreamSynchronize(c->stream));
   return MFB_OK;
 }
+
+extern "C" int mfb_comm_peer_state(mfb_ctx* c) { return c ? c->peer_state : 0; }
 
 extern "C" int mfb_interface_sum_dev(mfb_ctx* c, double* a_dev, int ncomp_a, double* b_dev, int ncomp_b) {
   CHECK_CTX(c);

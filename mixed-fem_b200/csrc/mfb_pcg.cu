@@ -7,6 +7,7 @@
 // SpMV is HBM-bound: 8 B per stored value (+8 B when M is given) + 4/d^2 B of column index per value (one block-column
 // index per d x d block, not one per scalar entry) + the vectors.
 #include "mfb_ctx.cuh"
+#include <cooperative_groups.h>
 #include <algorithm>
 #include <cmath>
 #include <vector>
@@ -219,14 +220,84 @@ __device__ __forceinline__ bool last_block_done(unsigned* ticket) {
   return last;
 }
 
+// ---- peer mailboxes (PeerView, mfb_ctx.cuh) ----
+// ONE block (the last to arrive of its kernel; every block has fenced its peer stores at system scope before taking its
+// ticket): thread q hands this rank's partial sums to rank q, fences, then raises the sequence number there.
+__device__ __forceinline__ void peer_post(const PeerView* pv, int stage, int par, unsigned long long seq, double v0, double v1) {
+  const int q = threadIdx.x;
+  if (q < pv->world) {
+    volatile double* d = pv->sc_at[stage][q] + par * kPeerMax * 2;
+    d[0] = v0; d[1] = v1;
+    // release at system scope: the two values above, and (cumulatively) the halo rows the other blocks stored and fenced
+    // before the barrier / ticket this thread has passed
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pv->flag_at[stage][q]), "l"(seq) : "memory");
+  }
+}
+// EVERY block calls it; only BLOCK 0 looks at the mailbox: its threads q < world wait (bounded) for rank q's sequence
+// number with system-scope acquire loads, thread 0 adds the partial sums in rank order (identical bits on all ranks) and
+// publishes (sum0, sum1, ok) in a local slot, then releases a local go-word at GPU scope; the other blocks watch that word.
+// (All blocks polling the mailbox themselves was measured: 1.2 k pollers at 2 GPUs made an exchange cost 5.5 us, 4.7 k at
+// 8 GPUs 19 us - the peers' flag writes queue behind the polls on the same line.)  False on a timeout.
+__device__ __forceinline__ bool peer_collect(const PeerView* pv, int stage, int par, unsigned long long seq, double* v0, double* v1) {
+  __shared__ int ok_sh;
+  __shared__ double bc_sh[2];
+  double* bc = pv->my_sc + kPeerScWords + (stage * 2 + par) * 4;                  // local broadcast slot: sum0, sum1, ok
+  unsigned long long* go = pv->my_flag + kPeerFlagWords + kPeerScWords + 16 + stage;
+  if (threadIdx.x == 0) ok_sh = 1;
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < pv->world) {
+      const unsigned long long* f = pv->my_flag + stage * kPeerMax + threadIdx.x;
+      long long spins = 0;
+      for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+        if (v >= seq) break;
+        if (++spins > 64) __nanosleep(64);              // the first polls back to back: the usual wait is a few microseconds
+        if (spins > kPeerSpinLimit) { ok_sh = 0; break; }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const volatile double* sc = pv->my_sc + (size_t)stage * 2 * kPeerMax * 2 + (size_t)par * kPeerMax * 2;
+      double a = 0.0, b = 0.0;
+      for (int q = 0; q < pv->world; ++q) { a += sc[2 * q]; b += sc[2 * q + 1]; }
+      bc_sh[0] = a; bc_sh[1] = b;
+      ((volatile double*)bc)[0] = a; ((volatile double*)bc)[1] = b; ((volatile double*)bc)[2] = (double)ok_sh;
+      asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(go), "l"(seq) : "memory");
+    }
+    __syncthreads();
+  } else {
+    if (threadIdx.x == 0) {
+      long long spins = 0;
+      for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(go) : "memory");
+        if (v >= seq) break;
+        __nanosleep(100);
+        if (++spins > kPeerSpinLimit) { ok_sh = 0; break; }
+      }
+      if (ok_sh) {
+        bc_sh[0] = ((volatile double*)bc)[0]; bc_sh[1] = ((volatile double*)bc)[1];
+        if (((volatile double*)bc)[2] == 0.0) ok_sh = 0;
+      }
+    }
+    __syncthreads();
+  }
+  *v0 = bc_sh[0]; *v1 = bc_sh[1];
+  return ok_sh != 0;
+}
+
 template <int DIM>
 __global__ void __launch_bounds__(256) k_pcg_spmv_dot(const int* __restrict__ blockptr, const int* __restrict__ bcol, int nF,
                                                       const double* __restrict__ A, const double* __restrict__ p,
                                                       double* __restrict__ t, double* __restrict__ scal,
                                                       double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                       const int* __restrict__ rowif_ptr, const int* __restrict__ rowif_idx,
-                                                      double* __restrict__ send) {
-  // multi-GPU (rowif_ptr != nullptr): an interface row also goes straight into the send buffer of the halo exchange
+                                                      double* __restrict__ send, const PeerView* __restrict__ pv = nullptr,
+                                                      unsigned long long seq = 0, int par = 0) {
+  // multi-GPU (rowif_ptr != nullptr): an interface row also goes straight into the send buffer of the halo exchange -
+  // or, with peer mailboxes (pv), over NVLink into the neighbour's receive segment itself
   __shared__ double sh[8];
   if (scal[2] != 0.0) return;
   const int lane = threadIdx.x & 31, hl = lane & 15;
@@ -264,11 +335,14 @@ __global__ void __launch_bounds__(256) k_pcg_spmv_dot(const int* __restrict__ bl
 #pragma unroll
       for (int r = 0; r < DIM; ++r) { t[DIM * row + r] = acc[r]; dot = fma(acc[r], p[DIM * row + r], dot); }
       if (rowif_ptr) {
-        for (int j = rowif_ptr[row]; j < rowif_ptr[row + 1]; ++j) {
-          const int64_t s0 = (int64_t)DIM * rowif_idx[j];
+        const int j0 = rowif_ptr[row], j1 = rowif_ptr[row + 1];
+        for (int j = j0; j < j1; ++j) {
+          double* d = pv ? pv->dst[(size_t)par * pv->n_ent + rowif_idx[j]] : send + (int64_t)DIM * rowif_idx[j];
 #pragma unroll
-          for (int r = 0; r < DIM; ++r) send[s0 + r] = acc[r];
+          for (int r = 0; r < DIM; ++r) d[r] = acc[r];
         }
+        // no system-scope fence here (14 k of them per SpMV at 10M tets on 2 GPUs cost 45 us): the block's __threadfence() and
+        // ticket order these stores before the last block's st.release.sys, which is cumulative
       }
     }
     b0 = n0; b1 = n1;
@@ -277,7 +351,12 @@ __global__ void __launch_bounds__(256) k_pcg_spmv_dot(const int* __restrict__ bl
   if (threadIdx.x == 0) partials[blockIdx.x] = s;
   if (last_block_done(ticket)) {
     const double pt = sum_partials_all(partials, sh);
-    if (threadIdx.x == 0) scal[7] = pt;
+    if (pv) {
+      __shared__ double ptb;
+      if (threadIdx.x == 0) ptb = pt;
+      __syncthreads();
+      peer_post(pv, 0, par, seq, ptb, 0.0);
+    } else if (threadIdx.x == 0) scal[7] = pt;
   }
 }
 
@@ -288,11 +367,22 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
                                                     const double* __restrict__ dinv, int nF, int mode,
                                                     double* __restrict__ part_out, const double* __restrict__ w, int dist,
                                                     const int* __restrict__ rowif_ptr, const int* __restrict__ rowif_idx,
-                                                    const double* __restrict__ recv) {
+                                                    const double* __restrict__ recv, const PeerView* __restrict__ pv = nullptr,
+                                                    unsigned long long seq = 0) {
   // multi-GPU (rowif_ptr != nullptr): the neighbours' parts of an interface row of t = L p arrive in recv
+  // peer mailboxes (pv, dist == 2): wait for exchange `seq` (halo rows + p.Lp of every rank), post r.r / r.z as seq + 1
   __shared__ double sh[8];
   if (scal[2] != 0.0) return;
-  const double alpha = scal[(iter + 1) & 1] / scal[7];
+  double pt = 0.0;
+  if (pv) {
+    double dummy;
+    if (!peer_collect(pv, 0, iter & 1, seq, &pt, &dummy)) {
+      if (threadIdx.x == 0) { scal[13] = 1.0; scal[2] = 2.0; }
+      return;
+    }
+    recv = pv->my_halo + (size_t)(iter & 1) * 3 * pv->n_ent;
+  } else pt = scal[7];
+  const double alpha = scal[(iter + 1) & 1] / pt;
   double rr = 0.0, rz = 0.0;
   for (int gi = blockIdx.x * 256 + threadIdx.x; gi < nF; gi += gridDim.x * 256) {
     double rv[DIM], zv[DIM], tv[DIM];
@@ -302,7 +392,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
       for (int j = rowif_ptr[gi]; j < rowif_ptr[gi + 1]; ++j) {
         const int64_t s0 = (int64_t)DIM * rowif_idx[j];
 #pragma unroll
-        for (int k = 0; k < DIM; ++k) tv[k] += recv[s0 + k];
+        for (int k = 0; k < DIM; ++k) tv[k] += __ldcg(&recv[s0 + k]);      // L2: written by NCCL or by a peer, never cached in L1
       }
     }
 #pragma unroll
@@ -338,7 +428,12 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
   if (last_block_done(ticket)) {
     const double rr2 = sum_partials_all(part_out, sh);
     const double rz2 = sum_partials_all(part_out + kPcgBlocks, sh);
-    if (threadIdx.x == 0) {
+    if (dist == 2) {
+      __shared__ double pb[2];
+      if (threadIdx.x == 0) { pb[0] = rr2; pb[1] = rz2; }
+      __syncthreads();
+      peer_post(pv, 1, iter & 1, seq + 1, pb[0], pb[1]);
+    } else if (threadIdx.x == 0) {
       if (dist) { scal[8] = rr2; scal[9] = rz2; }     // local sums: all-reduced, then k_pcg_dir_dist decides
       else {
         scal[5] = rr2;
@@ -347,6 +442,195 @@ __global__ void __launch_bounds__(256) k_pcg_update(double* __restrict__ scal, i
         else scal[3] += 1.0;                    // completed iterations, counted on the device (CUDA-graph replays)
       }
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// The whole CG loop as ONE persistent cooperative kernel (option "cg_persist", default 1; preconditioners 0..2, one GPU or
+// several with peer mailboxes): the three phases of an iteration are separated by grid barriers instead of kernel
+// boundaries, every block adds the block partials itself (fixed order: the same bits in every block), and on several
+// GPUs block 0 posts the rank's partial sums to every rank's mailbox while all blocks wait for the sequence numbers -
+// compute and collective in one kernel, no launch and no NCCL call per iteration.  Measured on B200 (C3 split for 1 / 2 /
+// 4 / 8 GPUs, per-rank sizes on ONE GPU): the three-launch iteration costs 66 / 44 / 30 / 28 us - a floor of ~9 us per
+// dependent launch - see DESIGN.md section 6 for this kernel's numbers.
+// Same recurrence and same scal[] protocol as the three kernels above (the host may continue a solve with either).
+// A peer timeout in some block raises *abort; every block sees it after the next grid barrier and leaves.
+// ---------------------------------------------------------------------------------------------------------------
+struct PcgPersist {
+  const int* blockptr; const int* bcol; int nF; const double* L;
+  double *p, *t, *x, *r, *z;
+  const double* dinv; int mode; const double* w;
+  double* scal; double* part;                      // part: 3 x gridDim.x
+  const int* rowif_ptr; const int* rowif_idx; const PeerView* pv; unsigned long long seq0;
+  int iter0, niter; int* abort;
+  long long* prof;                                 // option "profile": block 0's SM cycles per phase, 12 slots (null: off)
+};
+#define PCG_TICK(i) do { if (a.prof && blockIdx.x == 0 && tid == 0) { const long long c_ = clock64(); tacc[i] += c_ - tlast; tlast = c_; } } while (0)
+
+template <int DIM>
+__global__ void __launch_bounds__(256, 4) k_pcg_persist(const PcgPersist a) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double sh[8];
+  const int G = gridDim.x, tid = threadIdx.x;
+  double* part0 = a.part; double* part1 = a.part + G; double* part2 = a.part + 2 * G;
+  if (a.scal[2] != 0.0) return;                    // uniform: written before the launch
+  const int lane = tid & 31, hl = lane & 15;
+  const double thr = a.scal[6];
+  double rz_prev = a.scal[(a.iter0 + 1) & 1], rr = a.scal[5];
+  int completed = 0;
+  bool conv = false, aborted = false;
+  const PeerView* pv = a.pv;
+  long long tacc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+  for (int k = a.iter0; k < a.iter0 + a.niter; ++k) {
+    const int par = k & 1;
+    const unsigned long long seqA = a.seq0 + 2ull * (unsigned long long)k + 1ull;
+    // ---- phase 1: t = L p, block partials of p.t; interface rows also go to the neighbours' mailboxes
+    {
+      const int stride = G * 16;
+      double dot = 0.0;
+      int row = (blockIdx.x * 8 + (tid >> 5)) * 2 + (lane >> 4);
+      int b0 = 0, b1 = 0;
+      if (row < a.nF) { b0 = a.blockptr[row]; b1 = a.blockptr[row + 1]; }
+      for (int row0 = row - (lane >> 4); row0 < a.nF; row0 += stride, row += stride) {
+        const int nxt = row + stride;
+        int n0 = 0, n1 = 0;
+        if (nxt < a.nF) { n0 = a.blockptr[nxt]; n1 = a.blockptr[nxt + 1]; }
+        const int nbr = (row < a.nF) ? b1 - b0 : 0;
+        const int rowlen = DIM * nbr;
+        const double* Ar = a.L + (int64_t)DIM * DIM * b0;
+        double acc[DIM];
+#pragma unroll
+        for (int r = 0; r < DIM; ++r) acc[r] = 0.0;
+        for (int q = hl; q < nbr; q += 16) {
+          const int col = DIM * a.bcol[b0 + q];
+          double xv[DIM];
+#pragma unroll
+          for (int c = 0; c < DIM; ++c) xv[c] = __ldcg(&a.p[col + c]);      // p changes inside this kernel: not through the read-only path
+#pragma unroll
+          for (int r = 0; r < DIM; ++r)
+#pragma unroll
+            for (int c = 0; c < DIM; ++c) acc[r] = fma(__ldg(&Ar[(int64_t)r * rowlen + DIM * q + c]), xv[c], acc[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < DIM; ++r) {
+#pragma unroll
+          for (int o = 8; o > 0; o >>= 1) acc[r] += __shfl_down_sync(0xffffffffu, acc[r], o, 16);
+        }
+        if (hl == 0 && row < a.nF) {
+#pragma unroll
+          for (int r = 0; r < DIM; ++r) { a.t[DIM * row + r] = acc[r]; dot = fma(acc[r], __ldcg(&a.p[DIM * row + r]), dot); }
+          if (a.rowif_ptr) {
+            const int j0 = a.rowif_ptr[row], j1 = a.rowif_ptr[row + 1];
+            for (int j = j0; j < j1; ++j) {
+              double* d = pv->dst[(size_t)par * pv->n_ent + a.rowif_idx[j]];
+#pragma unroll
+              for (int r = 0; r < DIM; ++r) d[r] = acc[r];
+            }
+            (void)j0; (void)j1;      // no fence here: the grid barrier orders these stores before block 0's release at system scope (cumulativity)
+          }
+        }
+        b0 = n0; b1 = n1;
+      }
+      const double s = block_sum_256(dot, sh);
+      if (tid == 0) part0[blockIdx.x] = s;
+    }
+    PCG_TICK(0);
+    grid.sync();
+    PCG_TICK(1);
+    if (*(volatile int*)a.abort) { aborted = true; break; }
+    double pt = sum_partials_all(part0, sh);
+    PCG_TICK(2);
+    if (pv) {
+      if (blockIdx.x == 0) peer_post(pv, 0, par, seqA, pt, 0.0);
+      PCG_TICK(3);
+      double dummy;
+      if (!peer_collect(pv, 0, par, seqA, &pt, &dummy) && tid == 0) *(volatile int*)a.abort = 1;
+      PCG_TICK(4);
+    }
+    const double alpha = rz_prev / pt;
+    // ---- phase 2: x += alpha p ; r -= alpha (t + halo) ; z = Dinv r ; block partials of r.r, r.z
+    {
+      const double* recv = pv ? pv->my_halo + (size_t)par * 3 * pv->n_ent : nullptr;
+      double prr = 0.0, prz = 0.0;
+      for (int gi = blockIdx.x * 256 + tid; gi < a.nF; gi += G * 256) {
+        double rv[DIM], zv[DIM], tv[DIM];
+#pragma unroll
+        for (int q = 0; q < DIM; ++q) tv[q] = __ldcg(&a.t[DIM * gi + q]);
+        if (a.rowif_ptr) {
+          for (int j = a.rowif_ptr[gi]; j < a.rowif_ptr[gi + 1]; ++j) {
+            const int64_t s0 = (int64_t)DIM * a.rowif_idx[j];
+#pragma unroll
+            for (int q = 0; q < DIM; ++q) tv[q] += __ldcg(&recv[s0 + q]);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < DIM; ++q) {
+          const int i = DIM * gi + q;
+          a.x[i] += alpha * __ldcg(&a.p[i]);
+          rv[q] = a.r[i] - alpha * tv[q];
+          a.r[i] = rv[q];
+        }
+        if (a.mode == 0) {
+#pragma unroll
+          for (int q = 0; q < DIM; ++q) zv[q] = rv[q];
+        } else {
+#pragma unroll
+          for (int c = 0; c < DIM; ++c) {
+            double s = 0.0;
+#pragma unroll
+            for (int q = 0; q < DIM; ++q) s += __ldg(&a.dinv[(int64_t)gi * DIM * DIM + c * DIM + q]) * rv[q];
+            zv[c] = s;
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < DIM; ++q) a.z[DIM * gi + q] = zv[q];
+        double lr = 0.0, lz = 0.0;
+#pragma unroll
+        for (int q = 0; q < DIM; ++q) { lr += rv[q] * rv[q]; lz += rv[q] * zv[q]; }
+        const double wi = a.w ? a.w[gi] : 1.0;
+        prr += wi * lr; prz += wi * lz;
+      }
+      const double s0 = block_sum_256(prr, sh);
+      const double s1 = block_sum_256(prz, sh);
+      if (tid == 0) { part1[blockIdx.x] = s0; part2[blockIdx.x] = s1; }
+    }
+    PCG_TICK(5);
+    grid.sync();
+    PCG_TICK(6);
+    if (*(volatile int*)a.abort) { aborted = true; break; }
+    rr = sum_partials_all(part1, sh);
+    double rz = sum_partials_all(part2, sh);
+    PCG_TICK(7);
+    if (pv) {
+      if (blockIdx.x == 0) peer_post(pv, 1, par, seqA + 1ull, rr, rz);
+      PCG_TICK(8);
+      if (!peer_collect(pv, 1, par, seqA + 1ull, &rr, &rz) && tid == 0) *(volatile int*)a.abort = 1;
+      PCG_TICK(9);
+    }
+    if (rr < thr) { conv = true; break; }           // the reference breaks before counting this iteration
+    // ---- phase 3: p = z + beta p (the thread that wrote z[i] reads it back: same index map as phase 2)
+    {
+      const double beta = rz / rz_prev;
+      for (int gi = blockIdx.x * 256 + tid; gi < a.nF; gi += G * 256) {
+#pragma unroll
+        for (int q = 0; q < DIM; ++q) { const int i = DIM * gi + q; a.p[i] = fma(beta, __ldcg(&a.p[i]), a.z[i]); }
+      }
+    }
+    rz_prev = rz;
+    ++completed;
+    PCG_TICK(10);
+    grid.sync();
+    PCG_TICK(11);
+    if (*(volatile int*)a.abort) { aborted = true; break; }
+  }
+  if (blockIdx.x == 0 && tid == 0) {
+    if (a.prof) for (int i = 0; i < 12; ++i) a.prof[i] += tacc[i];
+    a.scal[5] = rr;
+    a.scal[3] += (double)completed;
+    a.scal[(a.iter0 + completed + 1) & 1] = rz_prev;
+    if (conv) a.scal[2] = 1.0;
+    if (aborted) { a.scal[13] = 1.0; a.scal[2] = 2.0; }
   }
 }
 
@@ -360,9 +644,17 @@ __global__ void __launch_bounds__(256) k_pcg_dir(const double* __restrict__ scal
 // multi-GPU: scal[8], scal[9] = global r.r, r.z of this iteration (all-reduced).  Every block takes the same decision; a
 // block that starts after block 0 has set the flag returns early, which is harmless (the flag means: converged).
 __global__ void __launch_bounds__(256) k_pcg_dir_dist(double* __restrict__ scal, int iter, const double* __restrict__ z,
-                                                      double* __restrict__ p, int n) {
+                                                      double* __restrict__ p, int n, const PeerView* __restrict__ pv = nullptr,
+                                                      unsigned long long seq = 0) {
   if (scal[2] != 0.0) return;
-  const double rr = scal[8], rz = scal[9], absOld = scal[(iter + 1) & 1];
+  double rr, rz;
+  if (pv) {                                           // r.r / r.z of every rank, posted by k_pcg_update as exchange `seq`
+    if (!peer_collect(pv, 1, iter & 1, seq, &rr, &rz)) {
+      if (threadIdx.x == 0) { scal[13] = 1.0; scal[2] = 2.0; }
+      return;
+    }
+  } else { rr = scal[8]; rz = scal[9]; }
+  const double absOld = scal[(iter + 1) & 1];
   const bool conv = rr < scal[6];
   if (!conv) {
     const double beta = rz / absOld;
@@ -586,7 +878,7 @@ __global__ void k_sum_values(const double* __restrict__ a, const double* __restr
 }
 // scal[4] = |b|^2, scal[5] = |r|^2, scal[0] = r.z are in place; "iteration -1" has parity 1
 __global__ void k_pcg_init(double* scal, double tol, unsigned* tickets) {
-  scal[1] = scal[0]; scal[2] = 0.0; scal[3] = 0.0; scal[6] = tol * tol * scal[4]; scal[7] = 0.0;
+  scal[1] = scal[0]; scal[2] = 0.0; scal[3] = 0.0; scal[6] = tol * tol * scal[4]; scal[7] = 0.0; scal[13] = 0.0;
   tickets[0] = 0u; tickets[1] = 0u;
 }
 
@@ -621,6 +913,19 @@ extern "C" int mfb_spmv_dev(mfb_ctx* c, const double* M_vals_dev, const double* 
   CHECK_CTX(c);
   if (!x_dev || !y_dev) return MFB_ERR_INVALID;
   return spmv(c, M_vals_dev, x_dev, y_dev);
+}
+
+// block 0's SM cycles per phase of k_pcg_persist, accumulated while option "profile" is 1 (12 slots: phase 1, barrier, sum,
+// post, collect, phase 2, barrier, sums, post, collect, phase 3, barrier); reset != 0 clears them.  Debug aid, not in the header.
+extern "C" int mfb_debug_pcg_cycles(mfb_ctx* c, long long* out12, int reset) {
+  if (!c || !out12) return MFB_ERR_INVALID;
+  cudaSetDevice(c->device);
+  for (int i = 0; i < 12; ++i) out12[i] = 0;
+  if (!c->pcg_prof.p) return MFB_OK;
+  MFB_CUDA(cudaMemcpyAsync(out12, c->pcg_prof.p, 12 * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  if (reset) MFB_CUDA(cudaMemsetAsync(c->pcg_prof.p, 0, 16 * sizeof(long long), c->stream));
+  MFB_CUDA(cudaStreamSynchronize(c->stream));
+  return MFB_OK;
 }
 
 extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double* x, int precond, double tol, int max_iters,
@@ -771,6 +1076,14 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
     k_pcg_init<<<1, 1, 0, st>>>(c->scal.p, tol, tickets); c->launches += 1;
     // multi-GPU with a partition set: the halo of t = L p goes point-to-point, written / read inside the CG kernels
     const bool p2p = dist && c->use_p2p && c->ent_local.p;
+    // ... and with peer mailboxes (all GPUs on one node, CUDA IPC available) without NCCL at all: the SpMV kernel stores the
+    // interface rows into the neighbours' memory, the last block of each kernel posts the rank's partial sums to everybody,
+    // the next kernel waits for the sequence number (two exchanges per iteration: seq0 + 2k + 1, seq0 + 2k + 2)
+    bool peer = false;
+    if (p2p && !cheb) { if ((rc = peer_setup(c))) return rc; peer = c->peer_state == 1; }
+    const PeerView* pvd = peer ? c->peer_view.p : nullptr;
+    const unsigned long long seq0 = c->peer_seq;
+    if (peer) c->peer_seq += 2ull * (unsigned long long)max_iters + 2ull;      // the same on every rank, whatever the iteration count
     double *hsend = nullptr, *hrecv = nullptr;
     const int *rif_ptr = nullptr, *rif_idx = nullptr;
     if (p2p) {
@@ -783,12 +1096,14 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
     // tets: 68 us per iteration enqueued from the host against ~15 us of kernels).  The first iterations run eagerly (NCCL
     // sets up its connections on first use, which cannot be captured); a failed capture falls back to the eager loop.
     auto enqueue_iteration = [&](int k) -> int {
-      if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
-      else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend);
+      const unsigned long long seqA = seq0 + 2ull * (unsigned long long)k + 1ull;
+      if (c->dim == 3) k_pcg_spmv_dot<3><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend, pvd, seqA, k & 1);
+      else k_pcg_spmv_dot<2><<<gs, 256, 0, st>>>(c->blockptr.p, c->bcol.p, c->nF, L, p, t, c->scal.p, part, tickets, rif_ptr, rif_idx, hsend, pvd, seqA, k & 1);
       // multi-GPU: t <- sum over ranks at the interface and p.t <- sum of the local p.(L_r p): one NCCL group
       // (neighbour send / recv + the scalar), or one all-reduce over every shared vertex without a partition
       int e = MFB_OK;
-      if (p2p) e = halo_exchange(c, c->dim, c->scal.p + 7, 1);
+      if (peer) e = MFB_OK;
+      else if (p2p) e = halo_exchange(c, c->dim, c->scal.p + 7, 1);
       else if (dist) e = interface_sum(c, t, c->dim, nullptr, 0, c->scal.p + 7, 1);
       if (e) return e;
       if (cheb) {
@@ -810,20 +1125,70 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
         k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
         return MFB_OK;
       }
-      if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
-      else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dist ? 1 : 0, rif_ptr, rif_idx, hrecv);
+      const int dmode = dist ? (peer ? 2 : 1) : 0;
+      if (c->dim == 3) k_pcg_update<3><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dmode, rif_ptr, rif_idx, hrecv, pvd, seqA);
+      else k_pcg_update<2><<<gv, 256, 0, st>>>(c->scal.p, k, tickets + 1, p, t, x, r, z, c->pcg_dinv.p, c->nF, precond, part + kPcgBlocks, w, dmode, rif_ptr, rif_idx, hrecv, pvd, seqA);
       if (dist) {
-        if ((e = allreduce_scalars(c, c->scal.p + 8, 2, false))) return e;
-        k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
+        if (!peer && (e = allreduce_scalars(c, c->scal.p + 8, 2, false))) return e;
+        k_pcg_dir_dist<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n, pvd, seqA + 1ull);
       } else {
         k_pcg_dir<<<gn, 256, 0, st>>>(c->scal.p, k, z, p, n);
       }
       return MFB_OK;
     };
-    int launched = 0, batch = 8;
+    // the whole loop as one persistent cooperative kernel (k_pcg_persist) when nothing in it needs the host: one GPU, or
+    // several with peer mailboxes
+    // cg_persist 2 (default) = below 64 Ki block-rows, where the iteration is latency-bound (one GPU, per-rank sizes of C3 over
+    // 8 / 4 / 2 / 1 GPUs: 24.4 / 28.9 / 43.2 / 73.2 us per iteration against 28.2 / 31.0 / 43.9 / 65.8 for three launches -
+    // a kernel boundary lets the SpMV gather p through the L1, the persistent kernel must read it from the L2)
+    bool persist = (c->cg_persist == 1 || (c->cg_persist == 2 && c->nF <= (1 << 16))) && !cheb && (!dist || peer) && c->nF > 0;
+    if (persist) {
+      static int coop_dev[64], gmax_dev[64][2];
+      static bool coop_known[64] = {false};
+      const int dv = c->device & 63;
+      if (!coop_known[dv]) {
+        int coop = 0, sms = 0, nb3 = 0, nb2 = 0;
+        MFB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
+        MFB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+        MFB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb3, k_pcg_persist<3>, 256, 0));
+        MFB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, k_pcg_persist<2>, 256, 0));
+        coop_dev[dv] = coop; gmax_dev[dv][0] = nb2 * sms; gmax_dev[dv][1] = nb3 * sms;
+        coop_known[dv] = true;
+      }
+      const int gmax = std::min(gmax_dev[dv][c->dim == 3], kPcgBlocks);
+      if (!coop_dev[dv] || gmax < 1) persist = false;
+      else {
+        if (!c->pcg_abort.p && (rc = c->pcg_abort.alloc(1))) return rc;
+        MFB_CUDA(cudaMemsetAsync(c->pcg_abort.p, 0, sizeof(int), st));
+        PcgPersist pa;
+        pa.blockptr = c->blockptr.p; pa.bcol = c->bcol.p; pa.nF = c->nF; pa.L = L;
+        pa.p = p; pa.t = t; pa.x = x; pa.r = r; pa.z = z;
+        pa.dinv = c->pcg_dinv.p; pa.mode = precond; pa.w = w;
+        pa.scal = c->scal.p; pa.part = part;
+        pa.rowif_ptr = rif_ptr; pa.rowif_idx = rif_idx; pa.pv = pvd; pa.seq0 = seq0;
+        pa.iter0 = 0; pa.niter = max_iters; pa.abort = c->pcg_abort.p;
+        pa.prof = nullptr;
+        if (c->profile) {
+          if (!c->pcg_prof.p) { if ((rc = c->pcg_prof.alloc(16))) return rc; MFB_CUDA(cudaMemsetAsync(c->pcg_prof.p, 0, 16 * sizeof(long long), st)); }
+          pa.prof = c->pcg_prof.p;
+        }
+        const unsigned G = (unsigned)std::max(1, std::min(gmax, (int)nblk((int64_t)c->nF * 16)));
+        void* kargs[] = {(void*)&pa};
+        if (c->dim == 3) MFB_CUDA(cudaLaunchCooperativeKernel((void*)k_pcg_persist<3>, dim3(G), dim3(256), kargs, 0, st));
+        else MFB_CUDA(cudaLaunchCooperativeKernel((void*)k_pcg_persist<2>, dim3(G), dim3(256), kargs, 0, st));
+        c->launches += 1;
+        MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 14 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        MFB_CUDA(cudaStreamSynchronize(st));
+        if (c->h_scal[13] != 0.0) {
+          g_last_error = "mfb_pcg_dev: a peer-mailbox exchange timed out (a rank of the communicator stopped, or peer memory is not coherent on this node); set option peer = 0 to use NCCL";
+          return MFB_ERR_CUDA;
+        }
+      }
+    }
+    int launched = persist ? max_iters : 0, batch = 8;
     cudaGraphExec_t gexec = nullptr;
     const int gbatch = 32;                           // iterations per graph launch (even)
-    bool try_graph = c->cg_graph != 0 && max_iters >= 3 * gbatch;
+    bool try_graph = c->cg_graph != 0 && max_iters >= 3 * gbatch && !peer;      // the sequence numbers are launch parameters
     while (launched < max_iters) {
       if (try_graph && !gexec && launched >= 8 && max_iters - launched >= gbatch) {
         cudaGraph_t graph = nullptr;
@@ -850,8 +1215,13 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
       }
       launched += nb;
       c->launches += 3 * nb;
-      MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      MFB_CUDA(cudaMemcpyAsync(c->h_scal, c->scal.p, 14 * sizeof(double), cudaMemcpyDeviceToHost, st));
       MFB_CUDA(cudaStreamSynchronize(st));
+      if (peer && c->h_scal[13] != 0.0) {
+        if (gexec) cudaGraphExecDestroy(gexec);
+        g_last_error = "mfb_pcg_dev: a peer-mailbox exchange timed out (a rank of the communicator stopped, or peer memory is not coherent on this node); set option peer = 0 to use NCCL";
+        return MFB_ERR_CUDA;
+      }
       if (c->h_scal[2] != 0.0) break;
       if (batch < 64) batch *= 2;
     }

@@ -43,6 +43,34 @@ def main():
         xl = torch.zeros(3 * nFl, dtype=torch.float64, device=dev)
         it, rel = ms.pcg_dev(bl.data_ptr(), xl.data_ptr(), M_ptr=Mptr, precond=precond, tol=1e-10, max_iters=3000)
         out[precond] = (it, rel, xl.cpu().numpy())
+    # the default path above is the peer-mailbox one when CUDA IPC works on this node (peer_state 1; -1: NCCL fallback, same
+    # on every rank).  The NCCL exchange on the same system: same iteration count, and the same solution to rounding
+    # (the partial sums are added in rank order in one path and by NCCL's tree in the other)
+    state = ms.peer_state()
+    states = [None] * world
+    dist.all_gather_object(states, state)
+    assert state in (1, -1) and len(set(states)) == 1, states
+    print("rank", rank, "peer_state", state, flush=True)
+    if os.environ.get("MFB_REQUIRE_PEER") == "1":
+        assert state == 1
+    # (this system is small: the default above is also the persistent cooperative CG kernel; cg_persist 0 = the three
+    # launches per iteration with the same mailboxes, peer 0 = three launches and NCCL)
+    for name, val, label in (("cg_persist", 0, "peer, 3 launches"), ("peer", 0, "nccl")):
+        ms.set_option(name, val)
+        for precond in (1, 2):
+            xl = torch.zeros(3 * nFl, dtype=torch.float64, device=dev)
+            it, rel = ms.pcg_dev(bl.data_ptr(), xl.data_ptr(), M_ptr=Mptr, precond=precond, tol=1e-10, max_iters=3000)
+            a = out[precond]
+            d = np.abs(xl.cpu().numpy() - a[2]).max() / np.abs(a[2]).max()
+            print("rank", rank, "precond", precond, "iters default /", label, a[0], it, "max rel diff", d, flush=True)
+            assert abs(it - a[0]) <= 2 and d <= 1e-9, (it, a[0], d)
+    ms.set_option("peer", 1)
+    ms.set_option("cg_persist", 2)
+    # and again through the mailboxes: sequence numbers carry on across solves
+    for precond in (1,):
+        xl = torch.zeros(3 * nFl, dtype=torch.float64, device=dev)
+        it, rel = ms.pcg_dev(bl.data_ptr(), xl.data_ptr(), M_ptr=Mptr, precond=precond, tol=1e-10, max_iters=3000)
+        assert it == out[precond][0] and np.array_equal(xl.cpu().numpy(), out[precond][2]), (it, out[precond][0])
     # gather the distributed solution on rank 0 (interface copies must agree between ranks)
     sol = {}
     for precond in (1, 2):

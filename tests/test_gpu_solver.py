@@ -44,10 +44,14 @@ def test_spmv_matches_scipy(built, dim, n):
     gpu.close()
 
 
+@pytest.mark.parametrize("persist", [1, 0])
 @pytest.mark.parametrize("dim,n,precond", [(3, (7, 5, 4), 1), (3, (7, 5, 4), 2), (3, (6, 4, 3), 0), (2, (15, 11, 0), 1), (2, (15, 11, 0), 2)])
-def test_pcg_matches_eigen_cg_recurrence(built, dim, n, precond):
+def test_pcg_matches_eigen_cg_recurrence(built, dim, n, precond, persist):
+    """persist 1: the loop as one persistent cooperative kernel (grid barriers between the phases; what small systems get by
+    default), 0: three launches per iteration - the same recurrence, each against Eigen's"""
     import torch
     gpu, cpu, st, A, M, Mv_d, dev = _setup(dim, n)
+    gpu.set_option("cg_persist", persist)
     K = (A + M).tocsr()
     b = cpu.rhs()
     x0 = 1e-3 * np.random.default_rng(1).standard_normal(b.size)
@@ -68,6 +72,33 @@ def test_pcg_matches_eigen_cg_recurrence(built, dim, n, precond):
     it0, rr0 = gpu.pcg_dev(zd.data_ptr(), xd.data_ptr(), M_ptr=Mv_d.data_ptr(), precond=precond, tol=tol, max_iters=maxit)
     torch.cuda.synchronize()
     assert it0 == 0 and not xd.cpu().numpy().any()
+    gpu.close()
+
+
+def test_persistent_cg_continues_and_stops_like_the_three_launch_loop(built):
+    """same system, tight and loose tolerance, an iteration cap that is hit, and a warm start from the other path's result:
+    iteration counts equal to +-1, solutions to 1e-9 (the partial sums are grouped differently)"""
+    import torch
+    gpu, cpu, st, A, M, Mv_d, dev = _setup(3, (12, 8, 6))
+    b = cpu.rhs()
+    bd = torch.as_tensor(b, device=dev)
+    res = {}
+    for persist in (1, 0):
+        gpu.set_option("cg_persist", persist)
+        for tol, maxit in ((1e-10, 2000), (1e-3, 2000), (1e-10, 7)):
+            xd = torch.zeros_like(bd)
+            it, rr = gpu.pcg_dev(bd.data_ptr(), xd.data_ptr(), M_ptr=Mv_d.data_ptr(), precond=1, tol=tol, max_iters=maxit)
+            res[(persist, tol, maxit)] = (it, rr, xd.cpu().numpy())
+    for tol, maxit in ((1e-10, 2000), (1e-3, 2000), (1e-10, 7)):
+        a, c = res[(1, tol, maxit)], res[(0, tol, maxit)]
+        assert abs(a[0] - c[0]) <= 1 and (maxit != 7 or a[0] == c[0] == 7), (a[0], c[0])
+        # same iterates up to the grouping of the partial sums; one iteration more or less moves x by about tol
+        assert vec_rel(a[2], c[2]) <= (1e-9 if a[0] == c[0] else 10 * tol), (tol, maxit, vec_rel(a[2], c[2]))
+    # warm start: the converged solution of one path is a zero-iteration start for the other
+    gpu.set_option("cg_persist", 1)
+    xd = torch.as_tensor(res[(0, 1e-10, 2000)][2], device=dev).clone()
+    it, rr = gpu.pcg_dev(bd.data_ptr(), xd.data_ptr(), M_ptr=Mv_d.data_ptr(), precond=1, tol=1e-8, max_iters=100)
+    assert it == 0 and rr <= 1e-8
     gpu.close()
 
 
