@@ -540,7 +540,8 @@ def newton_leg(args, grid, material, label, rank=0, world=1, local_rank=0, steps
            "ms_per_cg_iteration": cg_ms,
            "cg_persistent_kcycles_per_iteration": cgcyc,
            "cg_exchange": (None if world == 1 else {1: "peer mailboxes (CUDA IPC over NVLink, inside the CG kernels; no NCCL call per iteration)",
-                                                    -1: "NCCL (peer mailboxes unavailable on this node)", 0: "NCCL"}[ms.peer_state()]),
+                                                    -1: "NCCL (peer mailboxes unavailable on this node)", 0: "NCCL (option peer = 0)"}[ms.peer_state()]
+                           if "peer=0" not in args.opt else "NCCL (option peer = 0)"),
            "phase_ms_per_newton_iteration": {k: v[0] / n for k, v in ph.items()},
            "roofline_cg": {"bound": "hbm", "unit": "GB/s", "peak": peak, "achieved": cgb / (cg_ms * 1e-3) / 1e9,
                            "frac": cgb / (cg_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_iteration": cgb,

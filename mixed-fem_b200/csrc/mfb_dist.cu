@@ -222,9 +222,9 @@ static void peer_free(mfb_ctx* c) {
 // failure on any rank (no IPC in this container, no peer access between two devices) leaves peer_state = -1 on EVERY
 // rank - the decision is taken from gathered data - and the CG stays on the NCCL exchange.
 int peer_setup(mfb_ctx* c) {
-  if (c->peer_state != 0) return MFB_OK;
+  if (c->peer_state != 0 || !c->use_peer) return MFB_OK;        // option peer = 0: not tried (state stays 0)
   c->peer_state = -1;
-  if (c->world <= 1 || c->world > kPeerMax || !c->use_peer || !c->ent_local.p) return MFB_OK;
+  if (c->world <= 1 || c->world > kPeerMax || !c->ent_local.p) return MFB_OK;
   NcclApi* api = nccl();
   cudaStream_t st = c->stream;
   const int W = c->world, me = c->rank;

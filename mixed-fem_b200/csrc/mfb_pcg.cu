@@ -1080,7 +1080,7 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
     // interface rows into the neighbours' memory, the last block of each kernel posts the rank's partial sums to everybody,
     // the next kernel waits for the sequence number (two exchanges per iteration: seq0 + 2k + 1, seq0 + 2k + 2)
     bool peer = false;
-    if (p2p && !cheb) { if ((rc = peer_setup(c))) return rc; peer = c->peer_state == 1; }
+    if (p2p && !cheb) { if ((rc = peer_setup(c))) return rc; peer = c->use_peer && c->peer_state == 1; }
     const PeerView* pvd = peer ? c->peer_view.p : nullptr;
     const unsigned long long seq0 = c->peer_seq;
     if (peer) c->peer_seq += 2ull * (unsigned long long)max_iters + 2ull;      // the same on every rank, whatever the iteration count
