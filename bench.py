@@ -647,7 +647,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-newton", action="store_true", help="skip the ms-per-Newton-iteration leg (config C3)")
     ap.add_argument("--newton-grid", type=int, nargs=3, default=[55, 55, 55])
-    ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): 3 v4 (default), 0 register B, 1 shared-memory B, 2 single fused launch")
+    ap.add_argument("--variant", type=int, default=None, help="kernel variant (library option smem_b): only 3 (k_update_tet_v4) exists; the round-1 kernels were removed")
     ap.add_argument("--asm", type=int, default=None, help="v4 assembly mode (library option asm_mode): 1 bulk reductions into block-CSR (default), 0 FP64 RED into scalar CSR")
     args = ap.parse_args()
     args.cpu_grid_given = args.cpu_grid is not None

@@ -329,8 +329,9 @@ int mfb_set_option(mfb_ctx* ctx, const char* name, int value);      /* "fuse_rhs
                                                                        2 deterministic gather, bit-stable), "stage_finalize"
                                                                        (0; 1 = finalize per element chunk on a side stream,
                                                                        measured slower), "pipe" (0; persistent pipelined kernel,
-                                                                       measured slower), "smem_b" (3 = v4; 0..2 the round-1
-                                                                       kernels), "exp" (what-if timing bits, WRONG results).
+                                                                       measured slower), "exp" (what-if timing bits, WRONG
+                                                                       results); "cg_persist" (2: persistent cooperative CG
+                                                                       kernel for small systems, 1 always, 0 never).
                                                                        Unknown names return MFB_ERR_INVALID. */
 /* device time of the update kernel alone, CUDA events on the ctx stream, accumulated while option "profile" is 1 */
 int mfb_kernel_time_ms(mfb_ctx* ctx, double* total_ms, int* count);

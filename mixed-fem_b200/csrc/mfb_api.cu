@@ -2,7 +2,6 @@
 #include "mfb_ctx.cuh"
 #include <cstdlib>
 #include <algorithm>
-#include "mfb_kernels3.cuh"
 #include <cstring>
 
 using namespace mfb;
@@ -33,7 +32,10 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "pipe")) { c->pipe = value; return MFB_OK; }       // 0 off, n > 0: persistent pipelined update kernel, n CTAs per SM slot
   if (!strcmp(name, "cheb_degree")) { if (value < 1 || value > 16) return MFB_ERR_INVALID; c->cheb_degree = value; return MFB_OK; }
   if (!strcmp(name, "cheb_ratio")) { if (value < 2) return MFB_ERR_INVALID; c->cheb_ratio = value; return MFB_OK; }
-  if (!strcmp(name, "smem_b")) { c->smem_b = value; return MFB_OK; }   // 0 register B, 1 shared-memory B, 2 fused single launch, 3 v4 (default)
+  if (!strcmp(name, "smem_b")) {      // 3 = k_update_tet_v4, the only tet update kernel left (0 / 1 / 2: the round-1 kernels, removed)
+    if (value != 3) { g_last_error = "option smem_b: only 3 (k_update_tet_v4) exists; the round-1 kernels 0 / 1 / 2 were removed"; return MFB_ERR_INVALID; }
+    c->smem_b = 3; return MFB_OK;
+  }
   if (!strcmp(name, "exp")) { c->exp = value; return MFB_OK; }
   if (!strcmp(name, "cg_zero_guess")) { c->cg_zero_guess = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "asm_mode")) {   // v4: 1 bulk reductions into block-CSR, 0 RED into scalar CSR, 2 deterministic gather
@@ -335,34 +337,10 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
     if (c->fuse_rhs) k_update_shell<true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_shell<false><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
   } else if (c->dim == 3) {
-    if (c->smem_b == 2) {
-      static bool attr2_done_dev[64] = {false};
-      bool& attr2_done = attr2_done_dev[c->device & 63];
-      if (!attr2_done) {
-        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
-        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
-        attr2_done = true;
-      }
-      if (c->fuse_rhs) k_update_tet_fused<true><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
-      else k_update_tet_fused<false><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
-    } else if (c->smem_b) {
-      k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
-      LAUNCHED(c, 1);
-      static bool attr_done_dev[64] = {false};
-      bool& attr_done = attr_done_dev[c->device & 63];
-      if (!attr_done) {
-        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_sm<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
-        MFB_CUDA(cudaFuncSetAttribute(k_update_tet_sm<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmBytes));
-        attr_done = true;
-      }
-      if (c->fuse_rhs) k_update_tet_sm<true><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
-      else k_update_tet_sm<false><<<c->grid(), kSmThreads, kSmBytes, st>>>(m, s, x_dev, h2);
-    } else {
-      k_material_psd6<<<c->grid(), 128, 0, st>>>(m, s, h2);
-      LAUNCHED(c, 1);
-      if (c->fuse_rhs) k_update_tet<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
-      else k_update_tet<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
-    }
+    // (the round-1 tet kernels - register B, shared-memory B, single fused launch: option smem_b 0 / 1 / 2 - were removed in
+    // round 2; mfb_set_option rejects those values)
+    g_last_error = "mfb_update_dev: no tet update kernel selected";
+    return MFB_ERR_UNSUPPORTED;
   } else {
     if (c->fuse_rhs) k_update_tri2d<true, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);
     else k_update_tri2d<false, true><<<c->grid(), 128, 0, st>>>(m, s, x_dev, h2);

@@ -442,7 +442,6 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   const size_t N = c->N, M = c->M, NP = c->NP;
   TRY(c->R.alloc(M * ld)); TRY(c->s.alloc(N * ld)); TRY(c->la.alloc(N * ld)); TRY(c->ds.alloc(N * ld)); TRY(c->S.alloc(N * ld));
   TRY(c->dSdF.alloc(M * N * ld)); TRY(c->g.alloc(N * ld)); TRY(c->H.alloc(NP * ld)); TRY(c->Hinv.alloc(NP * ld));
-  if (c->kind == MFB_TET) TRY(c->Lfac.alloc(NP * ld));
   TRY(c->evals.alloc(ld)); TRY(c->gl.alloc(N * ld)); TRY(c->grad_la.alloc(N * ld)); TRY(c->iters.alloc(ld));
   TRY(c->grad_x.alloc((size_t)dim * nF + 1)); TRY(c->rhs.alloc((size_t)dim * nF + 1)); TRY(c->Avals.alloc(c->nnz > 0 ? c->nnz : 1));
   if (c->kind == MFB_TET) { TRY(c->Ablk.alloc((size_t)c->nbu * 9 + 32 * kV4SinkSlots)); TRY(c->gxrh.alloc((size_t)6 * nF + 32 * kV4SinkSlots));   /* + the reduction sinks */ TRY(c->slow_list.alloc((size_t)nE + 1)); }

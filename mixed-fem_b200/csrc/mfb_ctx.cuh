@@ -111,7 +111,7 @@ struct mfb_ctx {
   // options
   int fuse_rhs = 1;
   int assembly = 0;
-  int smem_b = 3;       // update kernel variant: 3 = k_update_tet_v4 (default), 0/1/2 = the earlier register / shared-memory / fused variants
+  int smem_b = 3;       // tet update kernel: 3 = k_update_tet_v4, the only one (the round-1 variants 0 / 1 / 2 were removed in round 2)
   int exp = 0;
   int asm_mode = 1;     // v4 assembly: 1 = warp-cooperative coalesced RED into the block-CSR upper triangle, 0 = FP64 RED into the scalar CSR,
                         // 2 = deterministic owner-computes gather (no atomics; bit-identical from run to run)
@@ -136,7 +136,7 @@ struct mfb_ctx {
   bool det_ready = false;
   int nbu = 0;
   // state (device)
-  mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals, Lfac;
+  mfb::DBuf<double> R, s, la, ds, S, dSdF, g, H, Hinv, evals, gl, grad_la, grad_x, rhs, Avals;
   mfb::DBuf<int> iters;
   mfb::DBuf<unsigned long long> counters;
   // scratch
@@ -243,7 +243,7 @@ struct mfb_ctx {
     mfb::DevState st;
     st.R = R.p; st.s = s.p; st.la = la.p; st.ds = ds.p; st.S = S.p; st.dSdF = dSdF.p; st.g = g.p; st.H = H.p;
     st.Hinv = Hinv.p; st.evals = evals.p; st.gl = gl.p; st.grad_la = grad_la.p; st.iters = iters.p;
-    st.grad_x = grad_x.p; st.rhs = rhs.p; st.Avals = Avals.p; st.counters = counters.p; st.Lfac = Lfac.p;
+    st.grad_x = grad_x.p; st.rhs = rhs.p; st.Avals = Avals.p; st.counters = counters.p;
     return st;
   }
   mfb::DevAsm asmdesc() const {

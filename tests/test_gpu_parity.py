@@ -87,11 +87,12 @@ def test_update_parity_irregular_mesh_heterogeneous_materials(built):
     gpu.close()
 
 
-@pytest.mark.parametrize("variant,asm", [(3, 1), (3, 2), (3, 0), (1, 0), (0, 0), (2, 0)])
+@pytest.mark.parametrize("variant,asm", [(3, 1), (3, 2), (3, 0)])
 def test_update_kernel_variants_agree_with_oracle(built, variant, asm):
-    """every update-kernel variant the library can select (option smem_b / asm_mode): default = v4 with bulk-reduction
-    assembly; the mesh is irregular with pinned vertices; about a third of the elements get an indefinite Hessian so
-    both the Cholesky fast path and the Jacobi tail are exercised (status psd_slow counts the latter)."""
+    """every assembly mode of the tet update kernel (option asm_mode; smem_b 3 = k_update_tet_v4 is the only kernel since the
+    round-1 variants were removed): default = bulk reductions into the block-CSR upper triangle; the mesh is irregular with
+    pinned vertices; about a third of the elements get an indefinite Hessian so both the Cholesky fast path and the Jacobi
+    tail are exercised (status psd_slow counts the latter)."""
     V, T, fm, h = mesh(3, (9, 6, 5), shuffle=True, jitter=0.12, pin=0.12)
     gpu, cpu, st = pair(V, T, fm, [("Stable-Neohookean", MU, LA)], h=h)
     gpu.set_option("smem_b", variant)
@@ -111,6 +112,17 @@ def test_update_kernel_variants_agree_with_oracle(built, variant, asm):
         assert 0 < nslow < gpu.nE, stt
         ev = np.linalg.eigvalsh(cpu.get("H").reshape(-1, 6, 6))
         assert nslow >= int(sel.sum()) // 4
+    gpu.close()
+
+
+def test_removed_kernel_variants_are_rejected(built):
+    import mixed_fem_b200 as mf
+    V, T, fm, h = mesh(3, (3, 2, 2))
+    gpu = mf.MixedStretch(V, T, fm, [("ARAP", MU, LA)])
+    for v in (0, 1, 2):
+        with pytest.raises(mf.MfbError):
+            gpu.set_option("smem_b", v)
+    gpu.set_option("smem_b", 3)
     gpu.close()
 
 
