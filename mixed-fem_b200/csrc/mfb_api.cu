@@ -28,6 +28,7 @@ extern "C" int mfb_set_option(mfb_ctx* c, const char* name, int value) {
   if (!strcmp(name, "convergence_log")) { c->convergence_log = value ? 1 : 0; return MFB_OK; }
   if (!strcmp(name, "cg_persist")) { c->cg_persist = value; return MFB_OK; }      // persistent cooperative CG kernel: 2 (default) below 64 Ki block-rows, 1 always, 0 never (three launches per iteration)
   if (!strcmp(name, "peer")) { c->use_peer = value != 0; return MFB_OK; }      // 1 (default): CG halo + dot products through peer mailboxes (CUDA IPC) when every rank can open them; 0: NCCL
+  if (!strcmp(name, "zero_overlap")) { c->zero_overlap = value != 0; return MFB_OK; }   // 1: double-buffered accumulator, the other half cleared on a side stream during the element kernel (default 0: no gain measured)
   if (!strcmp(name, "stage_finalize")) { c->stage_finalize = value != 0; return MFB_OK; }   // 1: k_finalize_rows per element chunk on a side stream under the next chunks (default 0: measured slower)
   if (!strcmp(name, "pipe")) { c->pipe = value; return MFB_OK; }       // 0 off, n > 0: persistent pipelined update kernel, n CTAs per SM slot
   if (!strcmp(name, "cheb_degree")) { if (value < 1 || value > 16) return MFB_ERR_INVALID; c->cheb_degree = value; return MFB_OK; }
@@ -135,12 +136,14 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
   const bool chunk_x = bulk && c->x_host_chunked && big;
   const bool staged = bulk && c->stage_finalize && c->fin_rows.p && big && !multi_x && c->pipe == 0 && c->nb > 0;
   MFB_CUDA(cudaMemsetAsync(c->counters.p, 0, 64, st));
+  bool flip_ablk = false;
   if (det) {
     // every CSR value and every vertex entry is WRITTEN by the gather kernels: nothing to zero
   } else if (bulk) {
     MFB_CUDA(cudaMemsetAsync(c->gxrh.p, 0, (size_t)6 * c->nF * 8, st));
     const size_t ablk_bytes = (size_t)c->nbu * 9 * 8;
-    if (staged) {
+    const bool pingpong = staged || (c->zero_overlap && big && c->Ablk2.p);
+    if (pingpong) {
       if (!c->fin_stream) {
         int lo = 0, hi = 0;
         MFB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -158,8 +161,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
         else MFB_CUDA(cudaMemsetAsync(c->ablk(cur), 0, ablk_bytes, st));
         // the other accumulator is cleared for the NEXT update while this one runs: its last reader (the finalize of the
         // previous update) was joined into this stream before anything queued here
-        static const int zero_overlap = getenv("MFB_ZERO_OVERLAP") ? atoi(getenv("MFB_ZERO_OVERLAP")) : 1;
-        if (!zero_overlap) { c->ablk_clean[oth] = false; goto zero_done; }
+        if (!c->zero_overlap) { c->ablk_clean[oth] = false; goto zero_done; }
         MFB_CUDA(cudaEventRecord(c->ev_upd, st));
         MFB_CUDA(cudaStreamWaitEvent(c->zero_stream, c->ev_upd, 0));
         MFB_CUDA(cudaMemsetAsync(c->ablk(oth), 0, ablk_bytes, c->zero_stream));
@@ -168,7 +170,8 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       }
       zero_done:
       c->ablk_clean[cur] = false;
-      MFB_CUDA(cudaMemsetAsync(c->chunk_cnt.p, 0, 2 * mfb_ctx::kChunks * sizeof(unsigned long long), st));
+      if (staged) MFB_CUDA(cudaMemsetAsync(c->chunk_cnt.p, 0, 2 * mfb_ctx::kChunks * sizeof(unsigned long long), st));
+      flip_ablk = !staged;           // the staged loop flips it itself
     } else {
       // (a pending clear of this buffer on the zero stream, if any, is ordered before this one: same event)
       if (c->ablk_clean[c->ablk_cur] && c->ev_zero[c->ablk_cur]) MFB_CUDA(cudaStreamWaitEvent(st, c->ev_zero[c->ablk_cur], 0));
@@ -327,6 +330,7 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
       if (c->ev_vec) { MFB_CUDA(cudaEventRecord(c->ev_vec, st)); vec_recorded = true; }
       if (c->nb > 0 && !staged) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, nullptr, c->nF, a.Ablk, c->Avals.p);
+      if (flip_ablk) c->ablk_cur ^= 1;          // the next update reduces into the half that is being cleared beside this one
       LAUNCHED(c, staged ? 1 : 3);
     } else {
       if (c->fuse_rhs) { k_update_tet_v4<true, 0><<<grid4, kV4Threads, smem, st>>>(m, s, a, x_dev, h2, 0); k_update_tet_v4_tail<true, 0><<<tail_grid, kV4Threads, smem, st>>>(m, s, a, x_dev, h2); }
