@@ -1172,7 +1172,15 @@ extern "C" int mfb_pcg_dev(mfb_ctx* c, const double* Mv, const double* b, double
           if (!c->pcg_prof.p) { if ((rc = c->pcg_prof.alloc(16))) return rc; MFB_CUDA(cudaMemsetAsync(c->pcg_prof.p, 0, 16 * sizeof(long long), st)); }
           pa.prof = c->pcg_prof.p;
         }
-        const unsigned G = (unsigned)std::max(1, std::min(gmax, (int)nblk((int64_t)c->nF * 16)));
+        static const int gcap = getenv("MFB_PCG_G") ? atoi(getenv("MFB_PCG_G")) : 0;          // experiments: cap on the cooperative grid
+        // blocks per SM by size: one per 9 472 block-rows (= 64 rows per block of 256 threads), 1 .. 4.  Measured on one GPU
+        // (tools/run_cgsize.sh): 24 k rows 24.5 us per iteration at 4 blocks per SM, 21.6 at 2, 24.6 at 1; 48 k rows 29.3 / 28.6 /
+        // 38.7 - fewer blocks make the barriers and the partial sums cheaper, more blocks hide the SpMV's latency
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+        const int per_sm = std::max(1, std::min(4, c->nF / (64 * sms)));
+        const int gwant = gcap > 0 ? gcap : per_sm * sms;
+        const unsigned G = (unsigned)std::max(1, std::min(std::min(gmax, gwant), (int)nblk((int64_t)c->nF * 16)));
         void* kargs[] = {(void*)&pa};
         if (c->dim == 3) MFB_CUDA(cudaLaunchCooperativeKernel((void*)k_pcg_persist<3>, dim3(G), dim3(256), kargs, 0, st));
         else MFB_CUDA(cudaLaunchCooperativeKernel((void*)k_pcg_persist<2>, dim3(G), dim3(256), kargs, 0, st));
