@@ -13,6 +13,10 @@
 // (2) point-to-point path (mfb_comm_set_partition, default when set): every rank packs only ITS cuts, one grouped
 // ncclSend / ncclRecv per neighbour (<= 2 for slabs), arrivals are added to the local values - a + b on one side, b + a
 // on the other, bit-identical copies for vertices shared by two parts; scalar sums ride in the same NCCL group.
+// (3) peer mailboxes (peer_setup below; default for the CG when a partition is set and all ranks sit on one node): one
+// cudaMalloc'ed buffer per rank, opened by the others through CUDA IPC; the CG kernels of mfb_pcg.cu store halo rows and
+// partial dot products into each other's memory over NVLink and synchronise on sequence numbers - no NCCL call inside
+// the iteration.  NCCL is still what sets it up (handle exchange) and what everything else uses.
 #include "mfb_ctx.cuh"
 #include <dlfcn.h>
 #if __has_include(<nccl.h>)

@@ -6,6 +6,11 @@
 //
 // SpMV is HBM-bound: 8 B per stored value (+8 B when M is given) + 4/d^2 B of column index per value (one block-column
 // index per d x d block, not one per scalar entry) + the vectors.
+//
+// Two forms of the loop: three launches per iteration (k_pcg_spmv_dot, k_pcg_update, k_pcg_dir[_dist]) and, for small
+// systems, ONE persistent cooperative kernel per solve (k_pcg_persist).  On several GPUs both exchange the halo rows of
+// t = L p and the dot products through peer mailboxes from inside the kernels (peer_post / peer_collect below, set up by
+// mfb_dist.cu); NCCL (halo_exchange / allreduce_scalars between the launches) is the fallback.
 #include "mfb_ctx.cuh"
 #include <cooperative_groups.h>
 #include <algorithm>
