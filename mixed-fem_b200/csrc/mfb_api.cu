@@ -328,6 +328,13 @@ extern "C" int mfb_update_dev(mfb_ctx* c, const double* x_dev, double dt) {
       // vertex vectors first: grad_x_ / rhs_ are final after this launch (a host reader copies them out while the
       // CSR values are still being written, see mfb_rhs)
       if (c->nF > 0) k_deinterleave_vec<<<nblk((int64_t)c->nF * 3), 256, 0, st>>>(c->gxrh.p, c->nF, c->grad_x.p, c->rhs.p, c->fuse_rhs);
+      if (c->world > 1 && c->update_exchange && !exchanged) {
+        // no overlap with the interior elements on this path (host positions arriving in chunks): the interface sum still goes
+        // BEFORE the CSR values, so that a host reader of rhs_ does not wait for k_finalize_rows
+        int rcx = interface_sum(c, c->grad_x.p, c->dim, c->fuse_rhs ? c->rhs.p : nullptr, c->dim, nullptr, 0);
+        if (rcx) return rcx;
+        exchanged = true;
+      }
       if (c->ev_vec) { MFB_CUDA(cudaEventRecord(c->ev_vec, st)); vec_recorded = true; }
       if (c->nb > 0 && !staged) k_finalize_rows<<<nblk((int64_t)c->nF * 16), 256, 0, st>>>(c->blockptr.p, c->diagblk.p, c->fcode.p, nullptr, c->nF, a.Ablk, c->Avals.p);
       if (flip_ablk) c->ablk_cur ^= 1;          // the next update reduces into the half that is being cleared beside this one

@@ -394,6 +394,9 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   {   // element chunks (multiples of the 128-thread CTA) and the vertices each one needs
     const int ctas = (nE + kV4Threads - 1) / kV4Threads;
     int vmax = -1;
+    // one chunk per 1.25M elements, 1 .. 8: a rank of an 8-way split (1.26M tets, 0.6 ms of kernels) gains nothing from
+    // pipelining a 5 MB upload and pays for the 8 x (copy, event, wait, launch) on the host
+    c->nchunks = std::max(1, std::min(8, nE / 1250000));
     if (getenv("MFB_CHUNKS")) c->nchunks = std::max(1, std::min((int)mfb_ctx::kChunks, atoi(getenv("MFB_CHUNKS"))));   // experiments
     for (int k = 0; k < c->nchunks; ++k) {
       c->chunk_e0[k] = (int)((int64_t)ctas * k / c->nchunks) * kV4Threads;

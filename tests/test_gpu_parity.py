@@ -401,14 +401,15 @@ def test_deterministic_assembly_is_bit_stable_and_matches_the_oracle(built):
 
 
 @pytest.mark.parametrize("shuffle", [False, True])
-def test_staged_finalize_matches_the_single_pass(built, shuffle):
-    """Above 2^18 tets update() runs in 16 element chunks and finalizes, behind each one on a side stream, the block-rows
+def test_staged_finalize_matches_the_single_pass(built, shuffle, monkeypatch):
+    """Above 2^18 tets update() can run in element chunks (8 here) and finalize, behind each one on a side stream, the block-rows
     whose last element lies in it (option stage_finalize, default 1; per-chunk Jacobi tails; double-buffered accumulator).
     Same CSR values, vectors and status as the single pass (stage_finalize 0) - to rounding, the reductions are atomic in
     both - on a coherent element order and on a shuffled one (every row final in the last chunks), through the host-x entry
     (chunked upload) and the device-x one, three updates in a row (both accumulators in use), a third of the Hessians slow."""
     import torch
     import mixed_fem_b200 as mf
+    monkeypatch.setenv("MFB_CHUNKS", "8")        # a mesh of this size would get one chunk (one per 1.25M tets); read at mfb_create
     V, T, fm, h = mesh(3, (40, 40, 30), shuffle=shuffle, jitter=0.1, pin=0.02)
     assert T.shape[0] >= (1 << 18)
     mats = [("Stable-Neohookean", MU, LA)]
