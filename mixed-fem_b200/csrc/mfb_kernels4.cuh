@@ -48,6 +48,9 @@ namespace mfb {
 #ifndef MFB_V4_SYNC
 #define MFB_V4_SYNC 0
 #endif
+#ifndef MFB_V4_TAIL_SYNC
+#define MFB_V4_TAIL_SYNC 0
+#endif
 #define MFB_V4_SYNCPT() do { if (MFB_V4_SYNC && !TAIL && !PIPE) __syncthreads(); } while (0)
 #ifdef MFB_V4_MAXNREG
 #define MFB_V4_BOUNDS __maxnreg__(MFB_V4_MAXNREG)
@@ -667,11 +670,26 @@ __global__ void MFB_V4_BOUNDS k_update_tet_v4_tail(DevMesh m, DevState st, DevAs
   // list entries [counters[6], counters[5]): counters[6] is 0 unless an earlier tail launch of the same update() has
   // already processed a prefix (interface elements first, see mfb_update_dev / k_mark_tail)
   const long long n = (long long)as.slow_cnt[0];
+#if MFB_V4_TAIL_SYNC
+  // experiment: a CTA barrier per trip keeps the four warps in the same region of the instruction stream (the persistent
+  // pipelined kernel lost 22 % of its samples to instruction-cache misses once its warps drifted apart).  The trip count is
+  // CTA-uniform; whole warps past the end skip the body but stay in the loop.
+  for (long long b0 = (long long)as.slow_cnt[1] + (long long)blockIdx.x * blockDim.x; b0 < n; b0 += (long long)gridDim.x * blockDim.x) {
+    __syncthreads();
+    const long long i0 = b0 + (threadIdx.x & ~31);
+    if (i0 < n) {
+      const long long i = i0 + (threadIdx.x & 31);
+      const bool in = i < n;
+      update_tet_v4_body<FUSE_RHS, true, ASM>(m, st, as, x, as.slow_list[in ? i : n - 1], in, h2, smem4, sW, sC);
+    }
+  }
+#else
   for (long long i0 = (long long)as.slow_cnt[1] + (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += (long long)gridDim.x * blockDim.x) {
     const long long i = i0 + (threadIdx.x & 31);
     const bool in = i < n;
     update_tet_v4_body<FUSE_RHS, true, ASM>(m, st, as, x, as.slow_list[in ? i : n - 1], in, h2, smem4, sW, sC);
   }
+#endif
 }
 
 // Block-CSR upper triangle -> reference-layout scalar CSR values (sparse_utils.cpp:155-163), every entry written once.
