@@ -296,6 +296,61 @@ static int upload(DBuf<T>& d, const std::vector<T>& h, cudaStream_t st) {
 
 using namespace mfb;
 
+// Everything about a descriptor that can be checked WITHOUT a device, so that a bad mesh is an error message and not an
+// out-of-bounds read in a kernel or a NaN three calls later (the reference checks none of this: igl / Eigen index with the
+// values as given).  Runs before the library touches CUDA: tests/test_abi_and_device_math.py calls it on the CPU box.
+static int validate_desc(const mfb_mesh_desc* d) {
+  const int dim = d->elem_kind == MFB_TRI2D ? 2 : 3, npe = d->elem_kind == MFB_TET ? 4 : 3;
+  for (int64_t i = 0; i < (int64_t)dim * d->nV; ++i)
+    if (!std::isfinite(d->Vref[i])) { g_last_error = "mfb_create: vertex " + std::to_string(i / dim) + " has a non-finite coordinate"; return MFB_ERR_INVALID; }
+  // free_map: -1 = pinned, the other values are the ids 0 .. nF-1, each exactly once (mesh.cpp:25-50 builds it that way)
+  int nF = 0;
+  for (int v = 0; v < d->nV; ++v) {
+    if (d->free_map[v] < -1) { g_last_error = "mfb_create: free_map[" + std::to_string(v) + "] < -1"; return MFB_ERR_INVALID; }
+    nF = std::max(nF, d->free_map[v] + 1);
+  }
+  {
+    std::vector<char> seen((size_t)nF, 0);
+    int cnt = 0;
+    for (int v = 0; v < d->nV; ++v) {
+      const int f = d->free_map[v];
+      if (f < 0) continue;
+      if (seen[f]) { g_last_error = "mfb_create: free id " + std::to_string(f) + " appears twice in free_map"; return MFB_ERR_INVALID; }
+      seen[f] = 1; ++cnt;
+    }
+    if (cnt != nF) { g_last_error = "mfb_create: free_map skips ids (" + std::to_string(cnt) + " free vertices, largest id " + std::to_string(nF - 1) + ")"; return MFB_ERR_INVALID; }
+  }
+  for (int e = 0; e < d->nE; ++e) {
+    const int32_t* t = &d->T[(size_t)e * npe];
+    for (int k = 0; k < npe; ++k)
+      if (t[k] < 0 || t[k] >= d->nV) { g_last_error = "element references a vertex out of range"; return MFB_ERR_INVALID; }
+    if (d->mat_id && (d->mat_id[e] < 0 || d->mat_id[e] >= d->n_mat)) { g_last_error = "mat_id out of range"; return MFB_ERR_INVALID; }
+    // rest shape: the inverse of Dm (tets, 2D) / of T^T T (shells) must exist
+    double det;
+    if (d->elem_kind == MFB_TET) {
+      double A[3][3];
+      for (int k = 0; k < 3; ++k) for (int l = 0; l < 3; ++l) A[l][k] = d->Vref[3 * (size_t)t[k + 1] + l] - d->Vref[3 * (size_t)t[0] + l];
+      det = A[0][0] * (A[1][1] * A[2][2] - A[2][1] * A[1][2]) - A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+            A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+    } else if (d->elem_kind == MFB_TRI2D) {
+      const double* a = &d->Vref[2 * (size_t)t[0]]; const double* b = &d->Vref[2 * (size_t)t[1]]; const double* c = &d->Vref[2 * (size_t)t[2]];
+      det = (b[0] - a[0]) * (c[1] - a[1]) - (c[0] - a[0]) * (b[1] - a[1]);
+    } else {
+      const double* a = &d->Vref[3 * (size_t)t[0]]; const double* b = &d->Vref[3 * (size_t)t[1]]; const double* c = &d->Vref[3 * (size_t)t[2]];
+      double t0[3], t1[3];
+      for (int l = 0; l < 3; ++l) { t0[l] = b[l] - a[l]; t1[l] = c[l] - a[l]; }
+      const double g00 = t0[0] * t0[0] + t0[1] * t0[1] + t0[2] * t0[2], g01 = t0[0] * t1[0] + t0[1] * t1[1] + t0[2] * t1[2],
+                   g11 = t1[0] * t1[0] + t1[1] * t1[1] + t1[2] * t1[2];
+      det = g00 * g11 - g01 * g01;
+    }
+    if (!(std::fabs(det) > 0.0) || !std::isfinite(1.0 / det)) {
+      g_last_error = "mfb_create: element " + std::to_string(e) + " is degenerate (zero rest volume / area)";
+      return MFB_ERR_INVALID;
+    }
+  }
+  return MFB_OK;
+}
+
 extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   if (!out || !d || !d->T || !d->Vref || !d->free_map || d->nV <= 0 || d->nE <= 0 || d->n_mat <= 0 || !d->materials) {
     g_last_error = "mfb_create: invalid descriptor";
@@ -303,6 +358,15 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   }
   if (d->elem_kind != MFB_TET && d->elem_kind != MFB_TRI2D && d->elem_kind != MFB_SHELL) { g_last_error = "unsupported elem_kind"; return MFB_ERR_UNSUPPORTED; }
   if (d->elem_kind == MFB_SHELL && (!d->normals || !(d->thickness > 0))) { g_last_error = "MFB_SHELL needs per-face normals and a positive thickness"; return MFB_ERR_INVALID; }
+  for (int i = 0; i < d->n_mat; ++i) {
+    const int mdl = d->materials[i].model;
+    if (mdl < 0 || mdl > 5) { g_last_error = "unknown material model"; return MFB_ERR_INVALID; }
+    if (d->elem_kind == MFB_TRI2D && (mdl == MFB_NH || mdl == MFB_FUNG)) {
+      g_last_error = "Neohookean/Fung have no 3-vector (2D) form in the reference (src/energies/*.cpp)";
+      return MFB_ERR_UNSUPPORTED;
+    }
+  }
+  { const int rv = validate_desc(d); if (rv) return rv; }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     g_last_error = "no CUDA device visible: this library has no CPU fallback";
@@ -310,14 +374,6 @@ extern "C" int mfb_create(mfb_ctx** out, const mfb_mesh_desc* d) {
   }
   if (d->device < 0 || d->device >= ndev) { g_last_error = "bad device ordinal"; return MFB_ERR_INVALID; }
   const int dim = d->elem_kind == MFB_TRI2D ? 2 : 3;
-  for (int i = 0; i < d->n_mat; ++i) {
-    const int mdl = d->materials[i].model;
-    if (mdl < 0 || mdl > 5) { g_last_error = "unknown material model"; return MFB_ERR_INVALID; }
-    if (dim == 2 && (mdl == MFB_NH || mdl == MFB_FUNG)) {
-      g_last_error = "Neohookean/Fung have no 3-vector (2D) form in the reference (src/energies/*.cpp)";
-      return MFB_ERR_UNSUPPORTED;
-    }
-  }
   MFB_CUDA(cudaSetDevice(d->device));
   mfb_ctx* c = new mfb_ctx();
   c->device = d->device;

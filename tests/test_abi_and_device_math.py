@@ -50,6 +50,72 @@ def test_no_cpu_fallback_without_device(built):
     assert "no CUDA device" in str(ei.value) or "error -" in str(ei.value)
 
 
+def _create_outcome(V, T, fm, mats, **kw):
+    """'ok' (a device is present and the context was built), 'nodev' (valid descriptor, no device) or the error text"""
+    try:
+        ms = mf.MixedStretch(V, T, fm, mats, **kw)
+    except mf.MfbError as e:
+        return "nodev" if "no CUDA device" in str(e) else str(e)
+    ms.close()
+    return "ok"
+
+
+def test_create_validates_the_descriptor_before_touching_the_device(built):
+    """mfb_create checks, on the host and before any CUDA call, everything a kernel would otherwise index with or divide by:
+    vertex ids, material ids, the free map (ids 0..nF-1 exactly once, -1 = pinned), finite coordinates, non-degenerate
+    rest shapes.  Runs without a GPU: a VALID descriptor gets as far as the no-device error."""
+    from mixed_fem_b200 import meshgen
+    mats = [("Stable-Neohookean", 1.0, 2.0), ("ARAP", 1.0, 1.0)]
+    for dim in (3, 2):
+        V, T = meshgen.kuhn_grid(3, 2, 2) if dim == 3 else meshgen.tri_grid(4, 3)
+        fm = meshgen.pinned_free_map(V)
+        assert _create_outcome(V, T, fm, mats[:1]) in ("ok", "nodev")
+        assert _create_outcome(V, T, np.full(V.shape[0], -1, np.int32), mats[:1]) in ("ok", "nodev")      # everything pinned is a mesh too
+        bad = T.copy(); bad[1, 2] = V.shape[0]
+        assert "vertex out of range" in _create_outcome(V, bad, fm, mats[:1])
+        bad = T.copy(); bad[0, 0] = -1
+        assert "vertex out of range" in _create_outcome(V, bad, fm, mats[:1])
+        mid = np.zeros(T.shape[0], np.int32); mid[-1] = 2
+        assert "mat_id out of range" in _create_outcome(V, T, fm, mats, mat_id=mid)
+        f2 = fm.copy(); free = np.flatnonzero(f2 >= 0); f2[free[1]] = f2[free[0]]
+        assert "appears twice" in _create_outcome(V, T, f2, mats[:1]) or "skips ids" in _create_outcome(V, T, f2, mats[:1])
+        f2 = fm.copy(); f2[free[-1]] += 3
+        assert "skips ids" in _create_outcome(V, T, f2, mats[:1])
+        f2 = fm.copy(); f2[0] = -2
+        assert "< -1" in _create_outcome(V, T, f2, mats[:1])
+        V2 = V.copy(); V2[3, 0] = np.nan
+        assert "non-finite" in _create_outcome(V2, T, fm, mats[:1])
+        V2 = V.copy(); V2[T[2, 1]] = V2[T[2, 0]]              # two vertices of element 2 coincide
+        msg = _create_outcome(V2, T, fm, mats[:1])
+        assert "degenerate" in msg and "element" in msg
+    with pytest.raises(mf.MfbError) as ei:
+        mf.MixedStretch(V[:0], T[:0], fm[:0], mats[:1])
+    assert "invalid descriptor" in str(ei.value)
+    assert "unknown material model" in _create_outcome(V, T, fm, [(9, 1.0, 1.0)])
+    # shells: a sliver with collinear vertices
+    Vs = np.array([[0, 0, 0], [1, 0, 0], [2, 0, 0], [0, 1, 0]], float)
+    Ts = np.array([[0, 1, 3], [0, 1, 2]], np.int32)
+    msg = _create_outcome(Vs, Ts, np.arange(4, dtype=np.int32), mats[:1], normals=np.tile([0.0, 0.0, 1.0], (2, 1)), thickness=1e-3)
+    assert "element 1 is degenerate" in msg
+
+
+def test_reference_input_meshes_pass_the_descriptor_checks(built):
+    """the reference's own meshes (tests/golden/ref_inputs) have no degenerate element and consistent free maps under the
+    rules of mfb_create - i.e. the checks above reject nothing the reference could run"""
+    from tests import refinputs as ri
+    from mixed_fem_b200 import sceneio
+    for rel in ("models/mesh/beam_20k.mesh", "models/mesh/boat.mesh", "models/mesh/coarse_bunny.mesh", "models/mesh/gummy_bear.mesh"):
+        path = os.path.join(ri.RI, rel)
+        if not (os.path.exists(path) or os.path.exists(path + ".gz")):
+            continue
+        V, T, _ = sceneio.read_mesh(path)
+        V, T = sceneio.remove_unreferenced(V, T)[:2]
+        fm = np.arange(V.shape[0], dtype=np.int32)
+        assert _create_outcome(V, T, fm, [("Stable-Neohookean", 1.0, 2.0)]) in ("ok", "nodev"), rel
+    sc = ri.scene("scenes/2D/trampoline.json", 2)
+    assert _create_outcome(sc.V, sc.T, sc.free_map, sc.materials, mat_id=sc.mat_id) in ("ok", "nodev")
+
+
 def test_product_never_imports_oracle():
     for dirpath, _, files in os.walk(os.path.join(ROOT, "mixed-fem_b200")):
         for f in files:
