@@ -94,6 +94,23 @@ extern "C" int mfb_partition_create(mfb_partition** out, int32_t dim, int32_t np
   }
   for (int64_t i = 0; i < (int64_t)nE * npe; ++i)
     if (T[i] < 0 || T[i] >= nV) { g_last_error = "mfb_partition_create: vertex id out of range"; return MFB_ERR_INVALID; }
+  if (nparts > nE) { g_last_error = "mfb_partition_create: more parts (" + std::to_string(nparts) + ") than elements (" + std::to_string(nE) + ")"; return MFB_ERR_INVALID; }
+  {   // free_map: -1 = pinned, otherwise the ids 0 .. nF-1 each exactly once (the same rule as mfb_create)
+    int nFg = 0;
+    for (int v = 0; v < nV; ++v) {
+      if (free_map[v] < -1) { g_last_error = "mfb_partition_create: free_map[" + std::to_string(v) + "] < -1"; return MFB_ERR_INVALID; }
+      nFg = std::max(nFg, free_map[v] + 1);
+    }
+    std::vector<char> seen((size_t)nFg, 0);
+    int cnt = 0;
+    for (int v = 0; v < nV; ++v) {
+      const int f = free_map[v];
+      if (f < 0) continue;
+      if (seen[f]) { g_last_error = "mfb_partition_create: free id " + std::to_string(f) + " appears twice in free_map"; return MFB_ERR_INVALID; }
+      seen[f] = 1; ++cnt;
+    }
+    if (cnt != nFg) { g_last_error = "mfb_partition_create: free_map skips ids"; return MFB_ERR_INVALID; }
+  }
   mfb_partition* p = new mfb_partition();
   p->dim = dim; p->npe = npe; p->nparts = nparts; p->rank = rank; p->method = method;
   p->part_of_elem.assign((size_t)nE, 0);

@@ -224,3 +224,37 @@ def test_distributed_cg_with_owner_weights_matches_global_solve(world):
     assert len(its) == 1 and 0 < its.pop() < 2000          # same control flow on every rank
     for rank, l2g, x, it, _ in res:
         assert np.linalg.norm(x.reshape(-1, 3) - xg[l2g]) <= 1e-7 * np.linalg.norm(xg)
+
+
+def test_partitioner_rejects_bad_arguments_and_handles_the_smallest_cases(built):
+    """mfb_partition_create (host code behind the C ABI): argument errors come back as messages; as many parts as elements is
+    the limit (every part one element), one more is an error rather than an empty rank"""
+    from mixed_fem_b200 import meshgen, partition
+    V, T = meshgen.kuhn_grid(1, 1, 1)            # 6 tets
+    fm = meshgen.pinned_free_map(V, ratio=0.3)
+    for rank in range(6):
+        loc, _, _ = partition.make_local(V, T, fm, 6, rank)
+        assert np.asarray(loc.T).shape == (1, 4)
+    cases = {
+        "more parts": dict(nparts=7, rank=0),
+        "bad arguments": dict(nparts=2, rank=2),
+        "bad arguments ": dict(nparts=65, rank=0),
+    }
+    for key, kw in cases.items():
+        with pytest.raises(RuntimeError) as ei:
+            partition.make_local(V, T, fm, kw["nparts"], kw["rank"])
+        assert key.strip() in str(ei.value), str(ei.value)
+    bad = T.copy(); bad[3, 1] = V.shape[0]
+    with pytest.raises(RuntimeError) as ei:
+        partition.make_local(V, bad, fm, 2, 0)
+    assert "vertex id out of range" in str(ei.value)
+    free = np.flatnonzero(fm >= 0)
+    assert free.size >= 2
+    f2 = fm.copy(); f2[free[1]] = f2[free[0]]
+    with pytest.raises(RuntimeError) as ei:
+        partition.make_local(V, T, f2, 2, 0)
+    assert "appears twice" in str(ei.value) or "skips ids" in str(ei.value)
+    f2 = fm.copy(); f2[0] = -7
+    with pytest.raises(RuntimeError) as ei:
+        partition.make_local(V, T, f2, 2, 0)
+    assert "< -1" in str(ei.value)
